@@ -1,0 +1,213 @@
+"""ctypes binding of oracle/liborb_oracle.so -- TEST INFRASTRUCTURE ONLY.
+
+May be imported from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs. The product package (orb-slam2-_b200/) never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+ORACLE_DIR = ROOT / "oracle"
+LIB_PATH = ORACLE_DIR / "liborb_oracle.so"
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+_u8p = C.POINTER(C.c_uint8)
+_i32p = C.POINTER(C.c_int32)
+_f32p = C.POINTER(C.c_float)
+
+
+def build(force=False):
+    """Compile the oracle with its Makefile (gcc only; seconds)."""
+    srcs = list(ORACLE_DIR.glob("*.cpp")) + list(ORACLE_DIR.glob("*.h"))
+    stale = (not LIB_PATH.exists()) or any(s.stat().st_mtime > LIB_PATH.stat().st_mtime for s in srcs)
+    if force or stale:
+        subprocess.check_call(["make", "-C", str(ORACLE_DIR), "-j8"], stdout=subprocess.DEVNULL)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(str(LIB_PATH))
+        L = _lib
+        L.orb_oracle_fast_atan2.restype = C.c_float
+        L.orb_oracle_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orb_oracle_sincosf_port.argtypes = [C.c_float, _f32p, _f32p]
+        L.orb_oracle_sincosf_libm.argtypes = [C.c_float, _f32p, _f32p]
+        L.orb_oracle_cv_round.argtypes = [C.c_double]
+        L.orb_oracle_sincosf_sweep.restype = C.c_int64
+        L.orb_oracle_sincosf_sweep.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.POINTER(C.c_uint32)]
+        L.orb_oracle_extractor_create.restype = C.c_void_p
+        L.orb_oracle_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orb_oracle_extractor_destroy.argtypes = [C.c_void_p]
+        L.orb_oracle_extractor_set_tie_mode.argtypes = [C.c_void_p, C.c_int]
+        L.orb_oracle_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.c_int]
+        L.orb_oracle_extractor_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+        L.orb_oracle_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orb_oracle_get_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.orb_oracle_get_blurred_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.orb_oracle_level_candidates.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.orb_oracle_level_kept.argtypes = [C.c_void_p, C.c_int]
+        L.orb_oracle_level_tie_sensitive.argtypes = [C.c_void_p, C.c_int]
+        L.orb_oracle_distribute.argtypes = [C.c_void_p, C.c_int] + [C.c_int] * 6 + [C.c_void_p, C.c_int]
+        L.orb_oracle_resize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.orb_oracle_blur7.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orb_oracle_fast.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orb_oracle_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p]
+        L.orb_oracle_match_bf2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_float, C.c_int,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    return _lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _img(a):
+    a = np.asarray(a)
+    assert a.dtype == np.uint8 and a.ndim == 2 and a.strides[1] == 1
+    return a
+
+
+# ---- primitives ------------------------------------------------------------------------------
+def resize(src, dw, dh):
+    src = _img(src)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().orb_oracle_resize(_ptr(src), src.shape[1], src.shape[0], src.strides[0], _ptr(dst), dw, dh, dw)
+    return dst
+
+
+def blur7(src):
+    src = _img(src)
+    dst = np.empty(src.shape, np.uint8)
+    lib().orb_oracle_blur7(_ptr(src), src.shape[1], src.shape[0], src.strides[0], _ptr(dst), src.shape[1])
+    return dst
+
+
+def fast(img, threshold, nms=True):
+    img = _img(img)
+    cap = max(16, img.size)
+    out = np.empty((cap, 3), np.int32)
+    n = lib().orb_oracle_fast(_ptr(img), img.shape[1], img.shape[0], img.strides[0], threshold, int(nms), _ptr(out), cap)
+    return out[:n].copy()
+
+
+def fast_atan2(y, x):
+    return lib().orb_oracle_fast_atan2(float(y), float(x))
+
+
+def sincosf_port(a):
+    s, c = C.c_float(), C.c_float()
+    lib().orb_oracle_sincosf_port(float(a), C.byref(s), C.byref(c))
+    return s.value, c.value
+
+
+def sincosf_libm(a):
+    s, c = C.c_float(), C.c_float()
+    lib().orb_oracle_sincosf_libm(float(a), C.byref(s), C.byref(c))
+    return s.value, c.value
+
+
+def sincosf_sweep(lo_bits, hi_bits, nthreads=None):
+    first = C.c_uint32(0)
+    n = lib().orb_oracle_sincosf_sweep(lo_bits, hi_bits, nthreads or os.cpu_count() or 1, C.byref(first))
+    return n, first.value
+
+
+def descriptor_distance(a, b):
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return lib().orb_oracle_descriptor_distance(_ptr(a), _ptr(b))
+
+
+def match_bf2(q, db, ratio, th, nthreads=None):
+    q = np.ascontiguousarray(q, np.uint8)
+    db = np.ascontiguousarray(db, np.uint8)
+    nq, ndb = q.shape[0], db.shape[0]
+    idx = np.empty(nq, np.int32)
+    d1 = np.empty(nq, np.int32)
+    d2 = np.empty(nq, np.int32)
+    acc = np.empty(nq, np.uint8)
+    lib().orb_oracle_match_bf2(_ptr(q), nq, _ptr(db), ndb, ratio, th, _ptr(idx), _ptr(d1), _ptr(d2), _ptr(acc),
+                               nthreads or os.cpu_count() or 1)
+    return idx, d1, d2, acc
+
+
+def distribute(xys, minX, maxX, minY, maxY, N, tie_mode=0):
+    xys = np.ascontiguousarray(xys, np.int32).reshape(-1, 3)
+    out = np.empty(max(1, len(xys)), np.int32)
+    n = lib().orb_oracle_distribute(_ptr(xys), len(xys), minX, maxX, minY, maxY, N, tie_mode, _ptr(out), len(out))
+    return out[:n].copy()
+
+
+# ---- extractor -------------------------------------------------------------------------------
+class Extractor:
+    """Mirror of ORB_SLAM2::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self._h = lib().orb_oracle_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        if not self._h:
+            raise ValueError("bad extractor parameters")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orb_oracle_extractor_destroy(self._h)
+            self._h = None
+
+    def set_tie_mode(self, m):
+        lib().orb_oracle_extractor_set_tie_mode(self._h, m)
+
+    def tables(self):
+        n = self.nlevels
+        sc, isc, s2, is2 = (np.empty(n, np.float32) for _ in range(4))
+        feats = np.empty(n, np.int32)
+        umax = np.empty(16, np.int32)
+        lib().orb_oracle_extractor_tables(self._h, _ptr(sc), _ptr(isc), _ptr(s2), _ptr(is2), _ptr(feats), _ptr(umax))
+        return dict(scale=sc, inv_scale=isc, sigma2=s2, inv_sigma2=is2, feats=feats, umax=umax)
+
+    def __call__(self, img, cap=None):
+        img = _img(img)
+        cap = cap or (self.nfeatures * 2 + 4096)
+        kps = np.empty(cap, KP_DTYPE)
+        desc = np.empty((cap, 32), np.uint8)
+        n = lib().orb_oracle_extract(self._h, _ptr(img), img.shape[1], img.shape[0], img.strides[0],
+                                     _ptr(kps), _ptr(desc), cap)
+        if n < 0:
+            return self(img, cap=-n)
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l, blurred=False):
+        w, h = C.c_int(), C.c_int()
+        lib().orb_oracle_level_size(self._h, l, C.byref(w), C.byref(h))
+        out = np.empty((h.value, w.value), np.uint8)
+        if blurred:
+            lib().orb_oracle_get_blurred_level(self._h, l, _ptr(out), w.value)
+        else:
+            lib().orb_oracle_get_level(self._h, l, _ptr(out), w.value)
+        return out
+
+    def candidates(self, l):
+        n = lib().orb_oracle_level_candidates(self._h, l, None, 0)
+        out = np.empty((max(n, 1), 3), np.int32)
+        lib().orb_oracle_level_candidates(self._h, l, _ptr(out), n)
+        return out[:n]
+
+    def kept(self, l):
+        return lib().orb_oracle_level_kept(self._h, l)
+
+    def tie_sensitive(self, l):
+        return lib().orb_oracle_level_tie_sensitive(self._h, l)
