@@ -1,0 +1,160 @@
+/* orbx.h -- C ABI of liborbx.so: the B200-native (sm_100a) ORB front-end hot path.
+ *
+ * This is the drop-in boundary for the ONE data-parallel path of ORB-SLAM2 that this repository
+ * replaces: ORBextractor::operator() and ORBmatcher's Hamming searches. The reference has no FFI;
+ * its boundary is two C++ classes (R/include/ORBextractor.h:45-123, R/include/ORBmatcher.h:37-143).
+ * The C++ mirror classes under orb-slam2-_b200/host/ keep those declarations and call only the
+ * functions below. Plain pointers and sizes, no CUDA/torch types in any signature. There is no CPU
+ * fallback: every entry point fails with ORBX_ERR_CUDA when no sm_100 device is usable.
+ *
+ * Conventions: return 0 (ORBX_OK) on success, <0 on error; orbx_last_error() returns a
+ * thread-local message for the last failing call on this thread. Handles are thread-compatible:
+ * one thread per handle at a time, different handles concurrently (the reference runs two
+ * extractor instances on two std::threads per stereo frame, R/src/Frame.cpp:86-89).
+ * "host" pointers may be pageable or pinned; "device" pointers must be device memory on the
+ * handle's device. `stream` arguments are a cudaStream_t passed as void* (NULL = the handle's own
+ * stream).
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBX_OK 0
+#define ORBX_ERR_ARG (-1)      /* bad argument / unsupported size */
+#define ORBX_ERR_CUDA (-2)     /* CUDA runtime/driver failure, or no usable device */
+#define ORBX_ERR_CAPACITY (-3) /* caller buffer too small; *n holds the needed count */
+#define ORBX_ERR_STATE (-4)    /* call order (e.g. orbx_get_level before any extract) */
+
+#define ORBX_MAX_LEVELS 16
+#define ORBX_DESC_BYTES 32
+
+/* Same 28-byte layout as cv::KeyPoint {Point2f pt; float size, angle, response; int octave, class_id}
+ * so the C++ wrapper can memcpy rows straight into std::vector<cv::KeyPoint>
+ * (fields written by R/src/ORBextractor.cpp:905-915, 1178-1184; FAST sets class_id = -1). */
+typedef struct orbx_keypoint {
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} orbx_keypoint;
+
+/* ORBextractor ctor arguments (R/src/ORBextractor.cpp:418-421; YAML keys ORBextractor.nFeatures,
+ * .scaleFactor, .nLevels, .iniThFAST, .minThFAST read at R/src/Tracking.cpp:130-138) plus the
+ * sizing the device buffers need. */
+typedef struct orbx_params {
+  int32_t nfeatures;
+  float scale_factor;
+  int32_t nlevels;
+  int32_t ini_th_fast;
+  int32_t min_th_fast;
+  int32_t device;      /* CUDA device ordinal */
+  int32_t max_width;   /* largest frame this handle will see */
+  int32_t max_height;
+  int32_t max_batch;   /* frames per orbx_extract_batch* call (>= 1) */
+} orbx_params;
+
+typedef struct orbx_extractor orbx_extractor;
+
+const char* orbx_last_error(void);
+/* "orbx <version> sm_100a" */
+const char* orbx_version(void);
+/* number of usable CUDA devices (0 when none: the library does not fall back to the CPU) */
+int orbx_device_count(void);
+
+/* ---- ORBextractor (replaces R/src/ORBextractor.cpp:418-502 ctor, :1120-1188 operator()) ---- */
+int orbx_extractor_create(const orbx_params* params, orbx_extractor** out);
+void orbx_extractor_destroy(orbx_extractor* h);
+
+/* The six getters' tables (R/include/ORBextractor.h:66-86) + per-level quotas and umax;
+ * any output pointer may be NULL. Arrays hold nlevels entries (umax16: 16). */
+int orbx_extractor_tables(const orbx_extractor* h, float* scale_factors, float* inv_scale_factors,
+                          float* level_sigma2, float* inv_level_sigma2, int32_t* features_per_level,
+                          int32_t* umax16);
+
+/* One frame, host buffers: the body of operator() (R/src/ORBextractor.cpp:1120-1188).
+ * img: CV_8UC1 rows of `stride` bytes. kps/desc: capacity `cap` rows. *n = keypoints found.
+ * Synchronous. ORBX_ERR_CAPACITY if cap is too small (nothing written but *n). */
+int orbx_extract(orbx_extractor* h, const uint8_t* img, int32_t width, int32_t height, size_t stride,
+                 orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n);
+
+/* `count` same-sized frames, host buffers (frame f at imgs[f]); outputs are count x cap rows,
+ * n[f] per frame. Used for image sequences / stereo pairs (BASELINE.json configs 2-4). */
+int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width,
+                       int32_t height, size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap,
+                       int32_t* n);
+
+/* Same, frames and outputs resident in device memory; asynchronous on `stream`.
+ * Frame f starts at d_imgs + f*frame_stride. d_n[f] may exceed cap: rows beyond cap are dropped. */
+int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_imgs, int32_t count, int32_t width,
+                              int32_t height, size_t row_stride, size_t frame_stride,
+                              orbx_keypoint* d_kps, uint8_t* d_desc, int32_t cap, int32_t* d_n,
+                              void* stream);
+
+/* mvImagePyramid (public member, R/include/ORBextractor.h:88; read by Frame::ComputeStereoMatches,
+ * R/src/Frame.cpp:558,675-695): size of level `level` for the last extracted shape, and a lazy
+ * device->host copy of level `level` of frame `frame` of the last batch. */
+int orbx_level_size(const orbx_extractor* h, int32_t level, int32_t* width, int32_t* height);
+int orbx_get_level(orbx_extractor* h, int32_t frame, int32_t level, uint8_t* dst, size_t dst_stride);
+
+/* Introspection for the parity tests (not used by the C++ mirror classes). */
+int orbx_get_blurred_level(orbx_extractor* h, int32_t frame, int32_t level, uint8_t* dst, size_t dst_stride);
+/* FAST candidates handed to the octree, (x, y, score) triples relative to minBorder; unordered. */
+int orbx_get_level_candidates(orbx_extractor* h, int32_t frame, int32_t level, int32_t* xys, int32_t cap,
+                              int32_t* n);
+/* number of kernels launched by this handle since creation (bench.py's gpu_launches) */
+int64_t orbx_launch_count(const orbx_extractor* h);
+/* device time in ms of the stages of the last extract call (single or batch) when profiling is enabled
+ * with orbx_set_profiling(h, 1): [0]=pyramid [1]=fast [2]=octree [3]=blur [4]=orient+describe [5]=total */
+int orbx_set_profiling(orbx_extractor* h, int32_t enable);
+int orbx_last_stage_ms(orbx_extractor* h, float* ms6);
+
+/* ---- stand-alone primitives on host buffers (parity tests of each kernel; synchronous) ---- */
+int orbx_resize_u8(int32_t device, const uint8_t* src, int32_t sw, int32_t sh, size_t sstride,
+                   uint8_t* dst, int32_t dw, int32_t dh, size_t dstride);
+int orbx_blur7_u8(int32_t device, const uint8_t* src, int32_t w, int32_t h, size_t sstride, uint8_t* dst,
+                  size_t dstride);
+/* cv::fastAtan2 and the glibc-exact sincosf on arrays */
+int orbx_fast_atan2(int32_t device, const float* y, const float* x, float* out_deg, int64_t n);
+int orbx_sincosf(int32_t device, const float* a, float* out_sin, float* out_cos, int64_t n);
+/* sin/cos of every float whose bit pattern lies in [lo_bits, hi_bits) (exhaustive device-vs-libm
+ * comparison); out arrays hold hi_bits-lo_bits floats */
+int orbx_sincosf_sweep(int32_t device, uint32_t lo_bits, uint32_t hi_bits, float* out_sin, float* out_cos);
+/* DistributeOctTree (R/src/ORBextractor.cpp:571-817) on arbitrary candidates: (x,y,score) triples
+ * relative to (min_x,min_y). cell_w/cell_h = the FAST cell size the candidates came from; it defines
+ * cv::FAST's emission order (cell row, cell col, y, x), the tie-break between equal responses in a
+ * node. out_xys receives the kept triples in the reference's list order. */
+int orbx_distribute(int32_t device, const int32_t* xys, int32_t n, int32_t min_x, int32_t max_x,
+                    int32_t min_y, int32_t max_y, int32_t n_features, int32_t cell_w, int32_t cell_h,
+                    int32_t* out_xys, int32_t cap, int32_t* n_out);
+
+/* ---- ORBmatcher (replaces R/src/ORBmatcher.cpp DescriptorDistance :1901-1917 and the search loops) ---- */
+typedef struct orbx_matcher orbx_matcher;
+int orbx_matcher_create(int32_t device, orbx_matcher** out);
+void orbx_matcher_destroy(orbx_matcher* h);
+int64_t orbx_matcher_launch_count(const orbx_matcher* h);
+
+/* DescriptorDistance for n pairs of 32-byte rows (a[i] vs b[i]) */
+int orbx_descriptor_distance(orbx_matcher* h, const uint8_t* a, const uint8_t* b, int32_t* dist, int64_t n);
+
+/* Brute-force top-2 + ratio test (inner loop of R/src/ORBmatcher.cpp:266-300, :526-556 over the
+ * whole database in index order): idx/d1 = first-minimum index and distance, d2 = second-smallest
+ * distance of the multiset, accepted = d1 <= th && d1 < ratio*d2. Host buffers, synchronous. */
+int orbx_match_bf2(orbx_matcher* h, const uint8_t* q, int32_t nq, const uint8_t* db, int64_t ndb,
+                   float ratio, int32_t th, int32_t* idx, int32_t* d1, int32_t* d2, uint8_t* accepted);
+/* Device-resident, asynchronous; idx_base is added to every index (database shards). */
+int orbx_match_bf2_device(orbx_matcher* h, const uint8_t* d_q, int32_t nq, const uint8_t* d_db, int64_t ndb,
+                          int64_t idx_base, int32_t* d_idx, int32_t* d_d1, int32_t* d_d2, void* stream);
+/* Merge `nshards` per-shard results laid out [shard][nq] (e.g. after an all-gather) with the
+ * sequential rule of :282-291 (equal minima in two shards => d2 = d1; lowest index wins) and apply
+ * threshold + ratio. Device-resident, asynchronous. */
+int orbx_match_merge_device(orbx_matcher* h, const int32_t* d_idx, const int32_t* d_d1, const int32_t* d_d2,
+                            int32_t nshards, int32_t nq, float ratio, int32_t th, int32_t* d_out_idx,
+                            int32_t* d_out_d1, int32_t* d_out_d2, uint8_t* d_accepted, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */

@@ -1,0 +1,117 @@
+// Shared declarations for the liborbx.so translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/orbx.h"
+
+namespace orbx {
+
+constexpr int kEdge = 19;         // EDGE_THRESHOLD  (R/src/ORBextractor.cpp:76)
+constexpr int kMinBorder = 16;    // EDGE_THRESHOLD-3 (:831)
+constexpr int kHalfPatch = 15;    // HALF_PATCH_SIZE (:75)
+constexpr int kPatch = 31;        // PATCH_SIZE      (:74)
+constexpr int kMaxLevels = ORBX_MAX_LEVELS;
+constexpr int kMaxCellDim = 64;   // wCell/hCell upper bound handled by the FAST kernel (< 60 by construction)
+constexpr int kMaxNodes = 2048;   // per-level octree quota + slack the selection kernel can hold in smem
+
+// Geometry of one pyramid level, fixed per (frame shape, extractor parameters).
+struct LevelGeom {
+  int w, h;            // level size (:1203)
+  int pitch;           // row pitch in bytes of our own planes (multiple of 16)
+  int maxBX, maxBY;    // w-16, h-16 (:833-834); minBorder is 16
+  int nCols, nRows;    // cell grid (:844-845)
+  int wCell, hCell;    // (:846-847)
+  int nfeat;           // mnFeaturesPerLevel[level]
+  int nIni;            // octree roots (:577)
+  float hX;            // root width (:580)
+  int candCap;         // capacity of the candidate list of one (frame, level)
+  int keptCap;         // capacity of the kept list of one (frame, level)
+  int cellBase;        // first flat cell id of this level in the FAST grid
+  int tileBase;        // first flat tile id of this level in the blur grid
+  int tilesX, tilesY;
+  float scale;         // mvScaleFactor[level]
+  float patchSize;     // (float)(int)(31*scale)  (:905,914)
+  long long planeOff;  // byte offset of frame 0 of this level in the pyramid / blur arenas
+  long long planeBytes;  // pitch*h
+  long long candOff;   // element offset of (frame 0, level) in the candidate arena
+  long long keptOff;   // element offset in the kept arena
+};
+
+struct FrameSetGeom {
+  int nlevels;
+  int iniTh, minTh;
+  int totalCells;      // FAST grid x-dimension
+  int totalTiles;      // blur grid x-dimension
+  long long pyrFrameStride;   // bytes between the same level of consecutive frames is planeBytes; arenas are [level][frame]
+  int candPerFrame;    // sum of candCap
+  int keptPerFrame;    // sum of keptCap
+  LevelGeom lv[kMaxLevels];
+};
+
+// candidate packing: x | y<<12 | score<<24, coordinates relative to minBorder (what the octree sees)
+__host__ __device__ inline uint32_t pack_cand(int x, int y, int score) {
+  return (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)score << 24);
+}
+__host__ __device__ inline int cand_x(uint32_t c) { return (int)(c & 0xfff); }
+__host__ __device__ inline int cand_y(uint32_t c) { return (int)((c >> 12) & 0xfff); }
+__host__ __device__ inline int cand_score(uint32_t c) { return (int)(c >> 24); }
+
+// Host-side error plumbing (thread-local message).
+void set_error(const char* fmt, ...);
+#define ORBX_CUDA_TRY(expr)                                                              \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      ::orbx::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return ORBX_ERR_CUDA;                                                              \
+    }                                                                                    \
+  } while (0)
+
+// ---- kernel launchers (defined in the .cu files) ------------------------------------------------
+struct ResizeTap { short p0, p1, c0, c1; };  // two source indices and their 11-bit weights
+struct ResizeTables {      // per destination level, device pointers
+  const ResizeTap* xt;     // [dw]
+  const ResizeTap* yt;     // [dh]
+};
+
+// level `l` (l>=1) of every frame from level l-1
+void launch_resize(const uint8_t* src, long long srcFrameStride, int srcPitch, int sw, int sh,
+                   uint8_t* dst, long long dstFrameStride, int dstPitch, int dw, int dh,
+                   const ResizeTables& t, int nframes, cudaStream_t s);
+
+struct PyramidPtrs {
+  const uint8_t* lvl[kMaxLevels];   // frame-0 base of each level
+  long long frameStride[kMaxLevels];
+  int pitch[kMaxLevels];
+};
+
+void launch_fast(const PyramidPtrs& pyr, const FrameSetGeom* dGeom, const FrameSetGeom& hGeom,
+                 uint32_t* cand, int* candCount, int* overflow, int nframes, cudaStream_t s);
+
+// returns 0 or a cudaError_t
+int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const uint32_t* cand,
+                  const int* candCount, uint16_t* nodeScratch, uint32_t* kept, int* keptCount,
+                  int nframes, cudaStream_t s);
+
+void launch_blur(const PyramidPtrs& pyr, const FrameSetGeom* dGeom, const FrameSetGeom& hGeom,
+                 uint8_t* blurArena, int nframes, cudaStream_t s);
+
+void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const FrameSetGeom* dGeom,
+                     const FrameSetGeom& hGeom, const uint32_t* kept, const int* keptCount,
+                     orbx_keypoint* outKps, uint8_t* outDesc, int cap, int* outN, int nframes,
+                     cudaStream_t s);
+
+// stand-alone octree on one candidate set (orbx_distribute); returns 0 or a cudaError_t
+int launch_octree_single(const uint32_t* cand, int n, int width, int height, int nfeat, int wCell, int hCell,
+                         int nCols, uint16_t* nodeScratch, uint32_t* kept, int* keptCount, int keptCap,
+                         cudaStream_t s);
+size_t octree_smem_bytes(int cap);
+
+void blur_tiles_for(int w, int h, int* tilesX, int* tilesY);
+void launch_blur_single(const uint8_t* src, int srcPitch, uint8_t* dst, int dstPitch, int w, int h, cudaStream_t s);
+void launch_atan2(const float* y, const float* x, float* out, long long n, cudaStream_t s);
+void launch_sincosf(const float* a, float* s_out, float* c_out, long long n, cudaStream_t s);
+void launch_sincosf_sweep(uint32_t lo, uint32_t hi, float* s_out, float* c_out, cudaStream_t s);
+
+}  // namespace orbx

@@ -1,0 +1,59 @@
+// Host-side state behind the C ABI (not installed; include/orbx.h is the public surface).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "orbx_common.cuh"
+
+namespace orbx {
+
+// ORBextractor ctor tables (R/src/ORBextractor.cpp:435-500), computed with the reference's types.
+struct CtorTables {
+  std::vector<float> scale, invScale, sigma2, invSigma2;
+  std::vector<int> featsPerLevel;
+  int umax[16];
+};
+void build_ctor_tables(int nfeatures, float scaleFactor, int nlevels, CtorTables* t);
+
+// cv::resize INTER_LINEAR coefficient tables for one axis (OpenCV imgproc resize.cpp semantics).
+void build_resize_axis(int srcLen, int dstLen, std::vector<ResizeTap>* taps);    // x: clamp + zero fraction
+void build_resize_axis_y(int srcLen, int dstLen, std::vector<ResizeTap>* taps);  // y: rows clipped, fraction kept
+const char* last_error();
+
+// Fill the per-level geometry for a (w,h) frame and `batchCap` frames per arena.
+// Returns 0, or ORBX_ERR_ARG with set_error() when a level is too small for the reference's grid.
+int build_geometry(const orbx_params& p, const CtorTables& t, int w, int h, int batchCap, FrameSetGeom* g);
+
+struct DeviceBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  int ensure(size_t need);  // grow-only; returns ORBX_OK / ORBX_ERR_CUDA
+  void release();
+};
+
+}  // namespace orbx
+
+struct orbx_extractor {
+  orbx_params params;
+  orbx::CtorTables tables;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[8] = {};
+  bool profiling = false;
+  float stageMs[6] = {};
+  long long launches = 0;
+
+  // current shape
+  int w = 0, h = 0, batchCap = 0;
+  orbx::FrameSetGeom geom;            // host copy
+  orbx::DeviceBuf dGeom;              // FrameSetGeom on device
+  orbx::DeviceBuf pyrArena, blurArena, candArena, nodeArena, keptArena, counts, tapArena;
+  orbx::DeviceBuf outKps, outDesc, outN;         // staging for the host-buffer entry points
+  void* hostStage = nullptr;                     // pinned: kps | desc | n | counts
+  size_t hostStageBytes = 0;
+  orbx::ResizeTables taps[orbx::kMaxLevels];
+  int lastCount = 0;                  // frames in the last batch
+  const uint8_t* lastLevel0 = nullptr;  // device pointer of level 0 of the last batch
+  long long lastL0FrameStride = 0;
+  int lastL0Pitch = 0;
+  bool haveResult = false;
+};

@@ -1,0 +1,147 @@
+"""GPU parity: every CUDA stage of the extractor against the CPU oracle, through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(640, 480), (752, 480), (1241, 376), (533, 400), (200, 150)]
+
+
+@pytest.mark.parametrize("w,h", SHAPES)
+def test_resize_bit_exact(pkg, oracle, w, h):
+    img = pkg.synth.frame(w, h, 11)
+    for s in (1.2, 1.44, 1.7):
+        dw, dh = int(round(w / s)), int(round(h / s))
+        assert np.array_equal(pkg.resize_u8(img, dw, dh), oracle.resize(img, dw, dh))
+
+
+@pytest.mark.parametrize("w,h", SHAPES + [(37, 29), (64, 32), (65, 33), (4, 4)])
+def test_blur_bit_exact(pkg, oracle, w, h):
+    for kind in ("shapes", "noise"):
+        img = pkg.synth.frame(w, h, 12, kind)
+        assert np.array_equal(pkg.blur7_u8(img), oracle.blur7(img))
+
+
+def test_fast_atan2_bit_exact(pkg, oracle):
+    rng = np.random.default_rng(0)
+    y = rng.integers(-70000, 70000, 200000).astype(np.float32)
+    x = rng.integers(-70000, 70000, 200000).astype(np.float32)
+    y[:8] = [0, 0, 5, -5, 1, -1, 0, 3]
+    x[:8] = [0, 5, 0, 0, 1, -1, -7, 3]
+    got = pkg.fast_atan2(y, x)
+    exp = np.array([oracle.fast_atan2(a, b) for a, b in zip(y[:20000], x[:20000])], np.float32)
+    assert np.array_equal(got[:20000].view(np.uint32), exp.view(np.uint32))
+
+
+def test_sincosf_matches_host_libm_sample(pkg, oracle):
+    rng = np.random.default_rng(1)
+    a = (rng.random(100000) * 360.0).astype(np.float32) * np.float32(np.pi / 180.0)
+    s, c = pkg.sincosf(a)
+    for i in range(0, 100000, 7):
+        es, ec = oracle.sincosf_libm(a[i])
+        assert np.float32(es).view(np.uint32) == s[i].view(np.uint32)
+        assert np.float32(ec).view(np.uint32) == c[i].view(np.uint32)
+
+
+def test_sincosf_exhaustive_block_vs_port(pkg, oracle):
+    """2^24 consecutive float bit patterns around pi (the port is itself pinned to libm exhaustively
+    on the CPU side); the full [0, 2pi] sweep is tools/sincosf_exhaustive.py."""
+    import struct
+    lo = struct.unpack("<I", struct.pack("<f", 3.0))[0]
+    hi = lo + (1 << 22)
+    s, c = pkg.sincosf_sweep(lo, hi)
+    bits = np.arange(lo, hi, dtype=np.uint32)
+    a = bits.view(np.float32)
+    idx = np.random.default_rng(2).integers(0, hi - lo, 3000)
+    for i in idx:
+        es, ec = oracle.sincosf_libm(a[i])
+        assert np.float32(es).view(np.uint32) == s[i].view(np.uint32)
+        assert np.float32(ec).view(np.uint32) == c[i].view(np.uint32)
+
+
+def _cands_set(a):
+    return set(map(tuple, np.asarray(a).tolist()))
+
+
+@pytest.mark.parametrize("w,h,nf,kind", [(640, 480, 1000, "shapes"), (640, 480, 1000, "noise"),
+                                         (640, 480, 1000, "lowcontrast"), (752, 480, 1200, "shapes"),
+                                         (1241, 376, 2000, "shapes")])
+def test_pyramid_blur_and_fast_candidates(pkg, oracle, w, h, nf, kind):
+    img = pkg.synth.frame(w, h, 21, kind)
+    ex = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    ox = oracle.Extractor(nf, 1.2, 8, 20, 7)
+    ex(img)
+    ox(img)
+    for l in range(8):
+        assert np.array_equal(ex.image_pyramid_level(l), ox.level(l)), f"pyramid level {l}"
+        gc, oc = ex.level_candidates(l), ox.candidates(l)
+        assert len(gc) == len(oc), f"level {l}: {len(gc)} vs {len(oc)} candidates"
+        assert _cands_set(gc) == _cands_set(oc), f"level {l} candidate set"
+        if ox.kept(l) > 0:
+            assert np.array_equal(ex.image_pyramid_level(l, blurred=True), ox.level(l, blurred=True)), f"blur {l}"
+
+
+def test_octree_matches_oracle_in_order(pkg, oracle):
+    ox = oracle.Extractor(1000, 1.2, 8, 20, 7)
+    for seed, kind in [(31, "shapes"), (32, "shapes"), (33, "noise")]:
+        img = pkg.synth.frame(640, 480, seed, kind)
+        ox(img)
+        feats = ox.tables()["feats"]
+        for l in range(8):
+            lv = ox.level(l)
+            hh, ww = lv.shape
+            minB, maxBX, maxBY = 16, ww - 16, hh - 16
+            width, height = maxBX - minB, maxBY - minB
+            wCell = int(np.ceil(width / (width // 30)))
+            hCell = int(np.ceil(height / (height // 30)))
+            c = ox.candidates(l)
+            exp_idx = oracle.distribute(c, minB, maxBX, minB, maxBY, int(feats[l]))
+            got = pkg.distribute(c, minB, maxBX, minB, maxBY, int(feats[l]), wCell, hCell)
+            assert np.array_equal(got, c[exp_idx]), f"seed {seed} level {l}"
+
+
+@pytest.mark.parametrize("w,h,nf,kind,seed", [
+    (640, 480, 1000, "shapes", 0), (640, 480, 1000, "shapes", 1), (640, 480, 1000, "noise", 2),
+    (640, 480, 1000, "lowcontrast", 3), (752, 480, 1200, "shapes", 4), (1241, 376, 2000, "shapes", 5),
+    (1920, 1080, 4000, "shapes", 6)])
+def test_extract_bit_exact(pkg, oracle, w, h, nf, kind, seed):
+    img = pkg.synth.frame(w, h, seed, kind)
+    ex = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    ox = oracle.Extractor(nf, 1.2, 8, 20, 7)
+    gk, gd = ex(img)
+    ok, od = ox(img)
+    assert len(gk) == len(ok)
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(gk[f], ok[f]), f
+    # north_star allows 1e-3 deg on the angle; we require bit equality
+    assert np.array_equal(gk["angle"].view(np.uint32), ok["angle"].view(np.uint32))
+    assert np.array_equal(gd, od)
+
+
+def test_constant_frame_gives_no_keypoints(pkg):
+    ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    k, d = ex(pkg.synth.frame(640, 480, 0, "constant"))
+    assert len(k) == 0 and d is None
+    k, d = ex(np.empty((0, 0), np.uint8))
+    assert len(k) == 0 and d is None
+
+
+def test_batch_equals_single(pkg, oracle):
+    imgs = [pkg.synth.frame(640, 480, 40 + i) for i in range(5)]
+    ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480, max_batch=8)
+    ox = oracle.Extractor(1000, 1.2, 8, 20, 7)
+    res = ex.extract_batch(imgs)
+    for im, (gk, gd) in zip(imgs, res):
+        ok, od = ox(im)
+        assert np.array_equal(gk.view(np.uint8), ok.view(np.uint8))
+        assert np.array_equal(gd, od)
+
+
+def test_errors_are_loud(pkg):
+    with pytest.raises(pkg.OrbxError):
+        pkg.ORBextractor(1000, 1.2, 8, 20, 7, max_width=64, max_height=48)  # top level too small for the grid
+    ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    with pytest.raises(pkg.OrbxError):
+        ex(np.zeros((1080, 1920), np.uint8))  # larger than the handle was sized for
+    with pytest.raises(TypeError):
+        ex(np.zeros((480, 640), np.float32))
