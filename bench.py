@@ -1,0 +1,357 @@
+#!/usr/bin/env python3
+"""bench.py -- the driver's measurement contract for the ORB front-end hot path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json `metric`): ORBextractor::operator() on 640x480 u8 frames, 1000 features,
+8 levels, scale 1.2, FAST 20/7 (TUM1.yaml; config C1 of SURVEY.md section 8). One "step" = one pass
+of the extraction pipeline over a batch of FRAMES_PER_STEP distinct synthetic frames (larger than
+the 126 MB L2). Frames shard across ranks with no data-path collective ("weak" scaling: the
+per-GPU batch is fixed).
+
+  value : frames/s, inputs and outputs resident in HBM (orbx_extract_batch_device)
+  e2e   : frames/s through the host-buffer C-ABI call a drop-in ORBextractor makes
+          (orbx_extract_batch: pinned host frames -> H2D -> kernels -> D2H keypoints+descriptors)
+  roofline / stages : per-stage CUDA-event times from inside the timed region
+  cpu_baseline : the CPU oracle on this box's host cores, bounded sample (rank 0, N=1 only)
+
+--impl reference times the CPU restatement of the reference (oracle/) with all host threads on the
+same config; this is the only place outside tests/ and smoke() where oracle/ is executed.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+W, H, NFEAT, NLEVELS, SCALE, INI_TH, MIN_TH = 640, 480, 1000, 8, 1.2, 20, 7
+FRAMES_PER_STEP = 512          # 512 x 307200 B = 157 MB of input per step (> 126 MB L2)
+E2E_FRAMES_PER_STEP = 128
+BASE_FRAMES = 32               # distinct numpy-generated frames; the rest are shifted/noised copies
+METRIC = "ORB frames/s (640x480, 1000 kp)"
+WORKLOAD = ("C1: ORBextractor::operator() on 640x480 u8 frames, 1000 features, 8 levels, scale 1.2, "
+            "FAST 20/7 (TUM1.yaml)")
+
+
+def level_sizes():
+    inv = [np.float32(1.0)]
+    sc = [np.float32(1.0)]
+    for _ in range(1, NLEVELS):
+        sc.append(np.float32(np.float64(sc[-1]) * np.float64(np.float32(SCALE))))
+    inv = [np.float32(1.0) / s for s in sc]
+    return [(int(np.rint(np.float32(W) * s)), int(np.rint(np.float32(H) * s))) for s in inv]
+
+
+def algorithmic_bytes():
+    """bytes per frame, per stage and total (5 702 474 B at C1)."""
+    A = [w * h for w, h in level_sizes()]
+    sA = sum(A)
+    st = {
+        "pyramid": (sA - A[-1]) + (sA - A[0]),
+        "fast": sA,
+        "blur": 2 * sA,
+        "describe": NFEAT * (709 + 512) + NFEAT * 60,
+        "octree": 0,
+    }
+    st["total"] = st["pyramid"] + st["fast"] + st["blur"] + st["describe"]
+    return st
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def base_frames(pkg, n=BASE_FRAMES, seed0=1000):
+    return np.stack([pkg.synth.frame(W, H, seed0 + i) for i in range(n)])
+
+
+def device_frames(torch, base, count, rank):
+    """count distinct frames on the device: base frames rolled by a per-copy offset plus +-1 noise
+    (deterministic torch generator). Generation happens outside every timed region."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    b = torch.from_numpy(base).to(dev)
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+    out = torch.empty((count, H, W), dtype=torch.uint8, device=dev)
+    nb = b.shape[0]
+    for k in range(0, count, nb):
+        m = min(nb, count - k)
+        rep = k // nb
+        fr = torch.roll(b[:m], shifts=(3 * rep, 5 * rep), dims=(1, 2)).to(torch.int16)
+        if rep:
+            fr = fr + torch.randint(-1, 2, fr.shape, generator=g, device=dev, dtype=torch.int16)
+        out[k:k + m] = fr.clamp_(0, 255).to(torch.uint8)
+    return out
+
+
+def time_cpu_oracle(frames, budget_s, nthreads):
+    """frames/s of the CPU oracle with `nthreads` threads, each with its own extractor instance
+    (the reference's own pattern: one ORBextractor per std::thread, R/src/Frame.cpp:86-89)."""
+    import oracle_lib
+    oracle_lib.lib()
+    nfr = len(frames)
+    exs = [oracle_lib.Extractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH) for _ in range(nthreads)]
+    exs[0](frames[0])  # warm caches / page in
+    done = [0] * nthreads
+    per_call = []
+    stop = time.perf_counter() + budget_s
+
+    def work(t):
+        i = t
+        while time.perf_counter() < stop:
+            t0 = time.perf_counter()
+            exs[t](frames[i % nfr])
+            if t == 0:
+                per_call.append(time.perf_counter() - t0)
+            done[t] += 1
+            i += nthreads
+
+    t0 = time.perf_counter()
+    ths = [threading.Thread(target=work, args=(t,)) for t in range(nthreads)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    dt = time.perf_counter() - t0
+    return sum(done) / dt, sum(done), float(np.median(per_call)) * 1e3 if per_call else None
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port; OpenCV C++ is not installable here, so
+    the primitives are the cv2-4.13-pinned restatements) on all host threads, same config/metric."""
+    import orbslam2_b200 as pkg  # synth only; no CUDA call is made on this path
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    frames = [pkg.synth.frame(W, H, 1000 + i) for i in range(BASE_FRAMES)]
+    budget = 4.0
+    for _ in range(min(args.warmup, 1)):
+        time_cpu_oracle(frames, 1.0, cores)
+    t0 = time.perf_counter()
+    tot_frames, vals = 0, []
+    for _ in range(args.steps):
+        fps, n, med_ms = time_cpu_oracle(frames, budget, cores)
+        vals.append(fps)
+        tot_frames += n
+    dt = time.perf_counter() - t0
+    value = float(np.mean(vals))
+    sample = f"{args.steps} steps x {budget:.0f} s of {W}x{H} frames on {cores} threads ({tot_frames} frames)"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "frames_per_step": "time-bounded sample"},
+            "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample,
+                             "single_thread_ms_per_frame": med_ms},
+            "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    import orbslam2_b200 as pkg
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device; liborbx has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    B = FRAMES_PER_STEP
+    ex = pkg.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_width=W, max_height=H, max_batch=B)
+    base = base_frames(pkg)
+    frames = device_frames(torch, base, B, rank)
+    cap = NFEAT + 64
+    d_kps = torch.empty((B, cap, 7), dtype=torch.float32, device="cuda")
+    d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(B, dtype=torch.int32, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        ex.extract_batch_device(frames.data_ptr(), B, W, H, W, W * H, d_kps.data_ptr(), d_desc.data_ptr(), cap,
+                                d_n.data_ptr(), stream)
+
+    # ---- device-resident throughput ("value") ----
+    for _ in range(max(args.warmup, 3)):
+        step()
+    ex.set_profiling(True)
+    stage_acc = {}
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    launches0 = ex.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+        for k, v in ex.last_stage_ms().items():  # CUDA events recorded on the launching stream
+            stage_acc[k] = stage_acc.get(k, 0.0) + v
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop() if rank == 0 else None
+    launches = ex.launch_count() - launches0
+    ex.set_profiling(False)
+    value = world * B * args.steps / (ms * 1e-3)
+    nkp = int(d_n.sum().item())
+
+    # ---- end to end through the host-buffer C ABI ("e2e") ----
+    Be = E2E_FRAMES_PER_STEP
+    host = torch.empty((Be, H, W), dtype=torch.uint8).pin_memory()
+    host.copy_(frames[:Be].cpu())
+    hnp = host.numpy()
+    himgs = [hnp[i] for i in range(Be)]
+    e2e_steps = 0 if args.skip_e2e else args.steps
+    for _ in range(0 if args.skip_e2e else 2):
+        ex.extract_batch(himgs)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ex.extract_batch(himgs)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e = world * Be * e2e_steps / e2e_s if e2e_steps else None
+    rows_per_frame = sum(max(max(f + 3, 4 * 1), 64) + 1 for f in ex.mnFeaturesPerLevel.tolist())
+    e2e_obj = {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": Be * W * H,
+               "d2h_bytes_per_step": Be * rows_per_frame * 60 + Be * 4, "frames_per_step": Be,
+               "api": "orbx_extract_batch (pinned host frames in, host keypoints+descriptors out)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant stage, from the event times of the timed region ----
+    peaks_path = ROOT / "MEASURED_PEAKS.json"
+    if peaks_path.exists():
+        peak, peak_src = json.loads(peaks_path.read_text())["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    ab = algorithmic_bytes()
+    stages = {}
+    for k in ("pyramid", "fast", "octree", "blur", "describe"):
+        t = stage_acc[k] / args.steps
+        gbs = ab[k] * B / (t * 1e-3) / 1e9 if t > 0 else 0.0
+        stages[k] = {"ms_per_step": t, "algorithmic_bytes_per_step": ab[k] * B, "gbs": gbs, "frac_of_hbm": gbs / peak}
+    dom = max(("pyramid", "fast", "octree", "blur", "describe"), key=lambda k: stages[k]["ms_per_step"])
+    kernel_names = {"pyramid": "resize_kernel (7 launches)", "fast": "fast_cells_kernel", "octree": "octree_kernel",
+                    "blur": "blur_kernel", "describe": "describe_kernel"}
+    roof = {"bound": "hbm", "kernel": kernel_names[dom], "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s",
+            "frac": stages[dom]["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+            "share_of_step": stages[dom]["ms_per_step"] / (stage_acc["total"] / args.steps),
+            "pipeline_achieved": ab["total"] * value / world / 1e9,
+            "pipeline_frac": ab["total"] * value / world / 1e9 / peak,
+            "algorithmic_bytes_per_frame": ab["total"]}
+
+    cpu = None
+    if world == 1 and not args.skip_cpu:
+        cores = os.cpu_count() or 1
+        sample_frames = [f for f in frames[:BASE_FRAMES].cpu().numpy()]
+        fps, n, med_ms = time_cpu_oracle(sample_frames, 12.0, cores)
+        cpu = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+               "sample": f"12 s of the same {W}x{H} frames on {cores} threads ({n} frames), one extractor per thread",
+               "single_thread_ms_per_frame": med_ms}
+
+    line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "input_bytes_per_step_per_gpu": B * W * H,
+                       "l2_policy": "inputs larger than L2 (157 MB of distinct frames per step)",
+                       "keypoints_per_frame": nkp / B, "parallelism": f"frame sharding x{world}, no collective"},
+            "clocks": clocks, "e2e": e2e_obj, "gpu_launches": launches, "roofline": roof, "stages": stages,
+            "cpu_baseline": cpu}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="orbx", choices=["orbx", "reference"])
+    ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg")
+    ap.add_argument("--skip-cpu", action="store_true", help="profiling runs only: skip the CPU baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
