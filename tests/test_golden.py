@@ -1,0 +1,38 @@
+"""Oracle vs the committed golden vectors (made by tools/make_golden.py with the real OpenCV 4.13)."""
+import hashlib
+from pathlib import Path
+
+import numpy as np
+
+G = Path(__file__).resolve().parent / "golden"
+
+
+def test_primitives_match_cv2_golden(oracle):
+    d = np.load(G / "prims_cv2.npz")
+    assert str(d["cv2_version"]).startswith("4.13")
+    for name in ("shapes", "noise"):
+        im = d[f"img_{name}"]
+        for key in d.files:
+            if key.startswith(f"resize_{name}_"):
+                dw, dh = map(int, key.split("_")[-1].split("x"))
+                assert np.array_equal(oracle.resize(im, dw, dh), d[key]), key
+        assert np.array_equal(oracle.blur7(im), d[f"blur_{name}"])
+        for th in (20, 7):
+            assert np.array_equal(oracle.fast(im, th, True), d[f"fast_{name}_{th}"]), (name, th)
+        assert np.array_equal(oracle.fast(im[11:49, 20:57], 7, True), d[f"fastcell_{name}_7"])
+    got = np.array([oracle.fast_atan2(a, b) for a, b in zip(d["atan2_y"], d["atan2_x"])], np.float32)
+    assert np.array_equal(got.view(np.uint32), d["atan2_deg"].view(np.uint32))
+
+
+def test_extractor_regression_hashes(oracle, pkg):
+    e = np.load(G / "extract_oracle.npz")
+    keys = sorted(k[:-4] for k in e.files if k.endswith("_sha"))
+    assert keys
+    for key in keys[:4]:  # the two largest shapes are covered by the first four; keep the CPU suite short
+        wh, nf, seed, kind = key.split("_")
+        w, h = map(int, wh.split("x"))
+        img = pkg.synth.frame(w, h, int(seed), kind)
+        assert hashlib.sha256(img.tobytes()).hexdigest() == str(e[key + "_imgsha"]), "synthetic generator drifted"
+        k, d = oracle.Extractor(int(nf), 1.2, 8, 20, 7)(img)
+        assert len(k) == int(e[key + "_n"])
+        assert hashlib.sha256(k.tobytes() + d.tobytes()).hexdigest() == str(e[key + "_sha"])
