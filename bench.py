@@ -307,7 +307,7 @@ def run_gpu(args):
         gbs = ab[k] * B / (t * 1e-3) / 1e9 if t > 0 else 0.0
         stages[k] = {"ms_per_step": t, "algorithmic_bytes_per_step": ab[k] * B, "gbs": gbs, "frac_of_hbm": gbs / peak}
     dom = max(("pyramid", "fast", "octree", "blur", "describe"), key=lambda k: stages[k]["ms_per_step"])
-    kernel_names = {"pyramid": "resize_kernel (7 launches)", "fast": "fast_cells_kernel", "octree": "octree_kernel",
+    kernel_names = {"pyramid": "resize4_kernel (7 launches)", "fast": "fast_cells_kernel", "octree": "octree_kernel",
                     "blur": "blur_kernel", "describe": "describe_kernel"}
     roof = {"bound": "hbm", "kernel": kernel_names[dom], "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s",
             "frac": stages[dom]["gbs"] / peak, "traffic": None, "peak_source": peak_src,

@@ -62,24 +62,36 @@ int ensure_shape(orbx_extractor* h, int w, int hh, int count) {
     ORBX_CUDA_TRY(cudaMallocHost(&h->hostStage, stageBytes));
     h->hostStageBytes = stageBytes;
   }
-  // resize coefficient tables, one x/y pair per destination level
-  size_t tapCount = 0;
-  for (int l = 1; l < nl; l++) tapCount += g.lv[l].w + g.lv[l].h;
-  if ((rc = h->tapArena.ensure(std::max<size_t>(tapCount, 1) * sizeof(ResizeTap)))) return rc;
+  // resize coefficient tables per destination level: x/y taps and (when they exist) 4-pixel groups
+  size_t tapCount = 0, groupCount = 0;
+  for (int l = 1; l < nl; l++) { tapCount += g.lv[l].w + g.lv[l].h; groupCount += (g.lv[l].w + 3) / 4; }
+  const size_t groupBytes = groupCount * sizeof(ResizeGroup);
+  if ((rc = h->tapArena.ensure(groupBytes + std::max<size_t>(tapCount, 1) * sizeof(ResizeTap)))) return rc;
+  std::vector<ResizeGroup> groups, xg;
   std::vector<ResizeTap> all, tx, ty;
+  groups.reserve(groupCount);
   all.reserve(tapCount);
+  const ResizeGroup* gbase = static_cast<const ResizeGroup*>(h->tapArena.p);
+  const ResizeTap* tbase = reinterpret_cast<const ResizeTap*>(static_cast<const uint8_t*>(h->tapArena.p) + groupBytes);
   for (int l = 1; l < nl; l++) {
     build_resize_axis(g.lv[l - 1].w, g.lv[l].w, &tx);
     build_resize_axis_y(g.lv[l - 1].h, g.lv[l].h, &ty);
-    const ResizeTap* base = static_cast<const ResizeTap*>(h->tapArena.p);
-    h->taps[l].xt = base + all.size();
+    h->taps[l].xt = tbase + all.size();
     all.insert(all.end(), tx.begin(), tx.end());
-    h->taps[l].yt = base + all.size();
+    h->taps[l].yt = tbase + all.size();
     all.insert(all.end(), ty.begin(), ty.end());
+    h->taps[l].xg = nullptr;
+    if (build_resize_groups(tx, &xg)) {
+      h->taps[l].xg = gbase + groups.size();
+      groups.insert(groups.end(), xg.begin(), xg.end());
+    }
   }
-  ORBX_CUDA_TRY(cudaMemcpyAsync(h->tapArena.p, all.data(), all.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice, h->stream));
+  if (!groups.empty())
+    ORBX_CUDA_TRY(cudaMemcpyAsync(h->tapArena.p, groups.data(), groups.size() * sizeof(ResizeGroup), cudaMemcpyHostToDevice, h->stream));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(h->tapArena.p) + groupBytes, all.data(), all.size() * sizeof(ResizeTap),
+                                cudaMemcpyHostToDevice, h->stream));
   ORBX_CUDA_TRY(cudaMemcpyAsync(h->dGeom.p, &g, sizeof(g), cudaMemcpyHostToDevice, h->stream));
-  ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));  // `all` and `g` are stack/heap temporaries
+  ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));  // `all`, `groups` and `g` are stack/heap temporaries
   h->geom = g;
   h->w = w; h->h = hh; h->batchCap = batchCap;
   h->haveResult = false;
@@ -115,7 +127,7 @@ int run_pipeline(orbx_extractor* h, const uint8_t* dL0, int l0Pitch, long long l
     h->launches++;
   }
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[1], s));
-  launch_fast(pyr, dG, g, static_cast<uint32_t*>(h->candArena.p), candCount, overflow, count, s);
+  launch_fast(pyr, g, static_cast<uint32_t*>(h->candArena.p), candCount, overflow, count, s);
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[2], s));
   int oe = launch_octree(dG, g, static_cast<const uint32_t*>(h->candArena.p), candCount,
@@ -124,10 +136,10 @@ int run_pipeline(orbx_extractor* h, const uint8_t* dL0, int l0Pitch, long long l
   if (oe) { set_error("octree kernel configuration failed: %s", cudaGetErrorString((cudaError_t)oe)); return ORBX_ERR_CUDA; }
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[3], s));
-  launch_blur(pyr, dG, g, static_cast<uint8_t*>(h->blurArena.p), count, s);
+  launch_blur(pyr, g, static_cast<uint8_t*>(h->blurArena.p), count, s);
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[4], s));
-  launch_describe(pyr, static_cast<const uint8_t*>(h->blurArena.p), dG, g, static_cast<const uint32_t*>(h->keptArena.p),
+  launch_describe(pyr, static_cast<const uint8_t*>(h->blurArena.p), g, static_cast<const uint32_t*>(h->keptArena.p),
                   keptCount, dKps, dDesc, cap, dN, count, s);
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[5], s));

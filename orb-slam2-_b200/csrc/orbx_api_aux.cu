@@ -138,14 +138,17 @@ int orbx_resize_u8(int32_t device, const uint8_t* src, int32_t sw, int32_t sh, s
   std::vector<ResizeTap> tx, ty;
   build_resize_axis(sw, dw, &tx);
   build_resize_axis_y(sh, dh, &ty);
-  TempBuf dS, dD, dT;
+  std::vector<ResizeGroup> xg;
+  const bool haveGroups = build_resize_groups(tx, &xg);
+  TempBuf dS, dD, dT, dG;
   const int sp = (sw + 15) & ~15, dp = (dw + 15) & ~15;
-  if ((rc = dS.alloc((size_t)sp * sh)) || (rc = dD.alloc((size_t)dp * dh)) ||
-      (rc = dT.alloc((tx.size() + ty.size()) * sizeof(ResizeTap)))) return rc;
+  if ((rc = dS.alloc((size_t)sp * sh + 64)) || (rc = dD.alloc((size_t)dp * dh)) ||
+      (rc = dT.alloc((tx.size() + ty.size()) * sizeof(ResizeTap))) || (rc = dG.alloc(xg.size() * sizeof(ResizeGroup)))) return rc;
   ORBX_CUDA_TRY(cudaMemcpy2D(dS.p, sp, src, sstride, sw, sh, cudaMemcpyHostToDevice));
   ORBX_CUDA_TRY(cudaMemcpy(dT.p, tx.data(), tx.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
   ORBX_CUDA_TRY(cudaMemcpy(dT.as<ResizeTap>() + tx.size(), ty.data(), ty.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
-  ResizeTables t{dT.as<ResizeTap>(), dT.as<ResizeTap>() + tx.size()};
+  if (haveGroups) ORBX_CUDA_TRY(cudaMemcpy(dG.p, xg.data(), xg.size() * sizeof(ResizeGroup), cudaMemcpyHostToDevice));
+  ResizeTables t{dT.as<ResizeTap>(), dT.as<ResizeTap>() + tx.size(), haveGroups ? dG.as<ResizeGroup>() : nullptr};
   launch_resize(dS.as<uint8_t>(), 0, sp, sw, sh, dD.as<uint8_t>(), 0, dp, dw, dh, t, 1, 0);
   ORBX_CUDA_TRY(cudaGetLastError());
   ORBX_CUDA_TRY(cudaMemcpy2D(dst, dstride, dD.p, dp, dw, dh, cudaMemcpyDeviceToHost));

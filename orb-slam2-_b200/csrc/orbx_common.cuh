@@ -70,9 +70,14 @@ void set_error(const char* fmt, ...);
 
 // ---- kernel launchers (defined in the .cu files) ------------------------------------------------
 struct ResizeTap { short p0, p1, c0, c1; };  // two source indices and their 11-bit weights
+// Four consecutive destination pixels of a row (resize4_kernel): the <= 8 source bytes they read start
+// at byte 4*word + shift/8 of the source row; sel01/sel23 are PRMT selectors gathering
+// (left0,right0,left1,right1) / (left2,right2,left3,right3) from those 8 bytes; c[j] = c0 | c1<<16.
+struct ResizeGroup { int word, shift; uint32_t sel01, sel23; uint32_t c[4]; };
 struct ResizeTables {      // per destination level, device pointers
   const ResizeTap* xt;     // [dw]
   const ResizeTap* yt;     // [dh]
+  const ResizeGroup* xg;   // [(dw+3)/4], or nullptr when a group would span more than 8 source bytes
 };
 
 // level `l` (l>=1) of every frame from level l-1
@@ -86,21 +91,19 @@ struct PyramidPtrs {
   int pitch[kMaxLevels];
 };
 
-void launch_fast(const PyramidPtrs& pyr, const FrameSetGeom* dGeom, const FrameSetGeom& hGeom,
-                 uint32_t* cand, int* candCount, int* overflow, int nframes, cudaStream_t s);
+void launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
+                 int nframes, cudaStream_t s);
 
 // returns 0 or a cudaError_t
 int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const uint32_t* cand,
                   const int* candCount, uint16_t* nodeScratch, uint32_t* kept, int* keptCount,
                   int nframes, cudaStream_t s);
 
-void launch_blur(const PyramidPtrs& pyr, const FrameSetGeom* dGeom, const FrameSetGeom& hGeom,
-                 uint8_t* blurArena, int nframes, cudaStream_t s);
+void launch_blur(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint8_t* blurArena, int nframes, cudaStream_t s);
 
-void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const FrameSetGeom* dGeom,
-                     const FrameSetGeom& hGeom, const uint32_t* kept, const int* keptCount,
-                     orbx_keypoint* outKps, uint8_t* outDesc, int cap, int* outN, int nframes,
-                     cudaStream_t s);
+void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const FrameSetGeom& hGeom,
+                     const uint32_t* kept, const int* keptCount, orbx_keypoint* outKps, uint8_t* outDesc, int cap,
+                     int* outN, int nframes, cudaStream_t s);
 
 // stand-alone octree on one candidate set (orbx_distribute); returns 0 or a cudaError_t
 int launch_octree_single(const uint32_t* cand, int n, int width, int height, int nfeat, int wCell, int hCell,

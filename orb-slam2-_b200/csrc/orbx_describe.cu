@@ -1,13 +1,18 @@
 // Orientation + rBRIEF descriptors + final keypoint records (SURVEY.md 8a rows E7, E9, E1;
 // R/src/ORBextractor.cpp IC_Angle :79-108, computeOrbDescriptor :113-155, operator() :1153-1186).
 //
-// One warp per kept keypoint.
-//  * IC_Angle: the 31 rows of the circular patch are walked with the lanes across u (one coalesced
-//    31-byte row segment per step) on the UNBLURRED level; m10/m01 are exact int32, reduced by
-//    shuffles; angle = cv::fastAtan2 (orbx_math.cuh).
-//  * Descriptor: lane b produces byte b (16 samples of the BLURRED level at the rotated pattern
-//    positions); the rotation uses glibc-exact sincosf and the fused forms the reference's
-//    -O3 -march=native build emits: row = fma(x,b,y*a), col = fma(x,a,-(y*b)), cvRound = rint.
+// One warp per kept keypoint, several keypoints per warp (v2).
+//  * IC_Angle on the UNBLURRED level: the 31x31 patch is cut into 31 rows x 8 chunks of 4 pixels;
+//    lane = chunk + 8*(row mod 4). A chunk is fetched as two aligned words realigned by a funnel
+//    shift, and the moments come from two IDP.4A per chunk against per-(row,chunk) weight words
+//    (u inside the disc, else 0 / 1 inside the disc, else 0) kept in shared memory:
+//    m10 += dot(px, u), m01 += v * dot(px, 1). Exact int32, reduced by shuffles;
+//    angle = cv::fastAtan2 (orbx_math.cuh).
+//  * Descriptor on the BLURRED level: lane b produces byte b (16 samples). The pattern sits in
+//    shared memory as float4 (x0,y0,x1,y1) per (bit, lane) -- conflict-free LDS.128 instead of
+//    the 32-way divergent constant loads of v1. Rotation uses glibc-exact sincosf and the fused forms
+//    the reference's -O3 -march=native build emits: row = fma(x,b,y*a), col = fma(x,a,-(y*b));
+//    cvRound = round-half-even done as (t + 1.5*2^23) - 1.5*2^23 on the FADD pipe instead of F2I.
 //  * Output row = (rows of lower levels) + list position: level-major like the reference's concat.
 #include "orbx_common.cuh"
 #include "orbx_math.cuh"
@@ -20,108 +25,143 @@ __constant__ int8_t cPattern[1024] = {
 // umax of the 15-radius patch (R/src/ORBextractor.cpp:480-500), a function of HALF_PATCH_SIZE only
 __constant__ int cUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
-__device__ __forceinline__ float ic_angle_warp(const uint8_t* __restrict__ center, int pitch, int lane) {
-  // lane -> u = lane-15 (lane 31 idle)
-  const int u = lane - kHalfPatch;
-  int m10 = 0, m01 = 0;
-  if (lane < 31) {
-#pragma unroll 1
-    for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
+constexpr int kDescWarps = 8;
+constexpr int kDescKpPerWarp = 4;
+constexpr int kDescKpPerCta = kDescWarps * kDescKpPerWarp;
+
+__device__ __forceinline__ int round_half_even_small(float t) {  // |t| < 2^22
+  return __float_as_int(__fadd_rn(t, 12582912.f)) - 0x4B400000;
+}
+
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
+  int r;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+
+__global__ void __launch_bounds__(kDescWarps * 32)
+describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restrict__ blurArena,
+                const __grid_constant__ FrameSetGeom g, const uint32_t* __restrict__ kept,
+                const int* __restrict__ keptCount, orbx_keypoint* __restrict__ outKps,
+                uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN) {
+  __shared__ float4 sPat[8 * 32];        // [bit][lane] = (x0, y0, x1, y1) of pattern pair lane*8+bit
+  __shared__ uint32_t sWU[32 * 8];       // [row v+15][chunk]: u (s8) inside the disc, else 0
+  __shared__ uint32_t sWO[32 * 8];       // [row][chunk]: 1 inside the disc, else 0
+  __shared__ int sStart[kMaxLevels + 1]; // first output row of each level in this frame
+
+  const int f = blockIdx.y;
+  const int nl = g.nlevels;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  {  // pattern pair p = lane*8 + bit -> sPat[bit*32 + lane]; thread tid handles pair tid
+    const int8_t* pp = &cPattern[tid * 4];
+    sPat[(tid & 7) * 32 + (tid >> 3)] = make_float4((float)pp[0], (float)pp[1], (float)pp[2], (float)pp[3]);
+    const int row = tid >> 3, chunk = tid & 7;  // 32 x 8 weight words (row 31 is unused padding)
+    uint32_t wu = 0, wo = 0;
+    if (row < 31) {
+      const int v = row - kHalfPatch;
       const int d = cUmax[v < 0 ? -v : v];
-      if (u >= -d && u <= d) {
-        const int val = center[(long long)v * pitch + u];
-        m10 += u * val;
-        m01 += v * val;
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int u = -16 + 4 * chunk + i;
+        if (u >= -d && u <= d) {
+          wu |= ((uint32_t)u & 0xffu) << (8 * i);
+          wo |= 1u << (8 * i);
+        }
       }
     }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-    m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-  }
-  return fast_atan2_deg((float)m01, (float)m10);
-}
-
-__device__ __forceinline__ uint8_t brief_byte(const uint8_t* __restrict__ center, int pitch, float a, float b,
-                                              int byteIdx) {
-  const int8_t* pat = &cPattern[byteIdx * 32];
-  int val = 0;
-#pragma unroll
-  for (int bit = 0; bit < 8; bit++) {
-    int t[2];
-#pragma unroll
-    for (int k = 0; k < 2; k++) {
-      const float px = (float)pat[4 * bit + 2 * k], py = (float)pat[4 * bit + 2 * k + 1];
-      const int r = __float2int_rn(__fmaf_rn(px, b, __fmul_rn(py, a)));
-      const int c = __float2int_rn(__fmaf_rn(px, a, -__fmul_rn(py, b)));
-      t[k] = center[(long long)r * pitch + c];
+    sWU[tid] = wu;
+    sWO[tid] = wo;
+    if (tid == 0) {
+      int total = 0;
+      for (int l = 0; l < nl; l++) {
+        sStart[l] = total;
+        total += max(0, min(keptCount[f * nl + l], g.lv[l].keptCap));
+      }
+      sStart[nl] = total;
+      if (blockIdx.x == 0) outN[f] = total;
     }
-    val |= (t[0] < t[1]) << bit;
   }
-  return (uint8_t)val;
-}
-
-__global__ void __launch_bounds__(256)
-describe_kernel(PyramidPtrs pyr, const uint8_t* __restrict__ blurArena, const FrameSetGeom* __restrict__ g,
-                const uint32_t* __restrict__ kept, const int* __restrict__ keptCount,
-                orbx_keypoint* __restrict__ outKps, uint8_t* __restrict__ outDesc, int cap,
-                int* __restrict__ outN, int keptPerFrameMax) {
-  const int f = blockIdx.y;
-  const int nl = g->nlevels;
-  const int lane = threadIdx.x & 31;
-  const int warpInFrame = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  // locate (level, position) of this warp's keypoint among the frame's kept lists
-  int level = 0, base = 0, total = 0;
-  int myLevel = -1, myPos = 0, myBase = 0;
-  for (level = 0; level < nl; level++) {
-    const int c = max(0, min(keptCount[f * nl + level], g->lv[level].keptCap));
-    if (myLevel < 0 && warpInFrame < total + c) { myLevel = level; myPos = warpInFrame - total; myBase = total; }
-    total += c;
-  }
-  (void)base; (void)myBase;
-  if (blockIdx.x == 0 && threadIdx.x == 0) outN[f] = total;
-  if (myLevel < 0) return;
-  const int row = warpInFrame;  // level-major concatenation
-  if (row >= cap) return;
-
-  const LevelGeom& L = g->lv[myLevel];
-  const uint32_t k = kept[L.keptOff + (long long)f * L.keptCap + myPos];
-  const int x = cand_x(k) + kMinBorder, y = cand_y(k) + kMinBorder;  // level coordinates (:909-910)
-  const int pitch = pyr.pitch[myLevel];
-  const uint8_t* plane = pyr.lvl[myLevel] + (long long)f * pyr.frameStride[myLevel];
-  const float angle = ic_angle_warp(plane + (long long)y * pitch + x, pitch, lane);
-
+  __syncthreads();
+  const int total = sStart[nl];
   const float factorPI = 0x1.1df46ap-6f;  // (float)(CV_PI/180.f)
-  float sn, cs;
-  sincosf_glibc(__fmul_rn(angle, factorPI), &sn, &cs);
-  const uint8_t* bplane = blurArena + L.planeOff + (long long)f * L.planeBytes;
-  const uint8_t d = brief_byte(bplane + (long long)y * L.pitch + x, L.pitch, cs, sn, lane);
-  outDesc[((long long)f * cap + row) * 32 + lane] = d;
 
-  if (lane == 0) {
-    orbx_keypoint kp;
-    const float fx = (float)x, fy = (float)y;
-    kp.x = myLevel ? __fmul_rn(fx, L.scale) : fx;  // pt *= scale for level != 0 (:1178-1184)
-    kp.y = myLevel ? __fmul_rn(fy, L.scale) : fy;
-    kp.size = L.patchSize;
-    kp.angle = angle;
-    kp.response = (float)cand_score(k);
-    kp.octave = myLevel;
-    kp.class_id = -1;
-    outKps[(long long)f * cap + row] = kp;
+#pragma unroll 1
+  for (int it = 0; it < kDescKpPerWarp; it++) {
+    const int row = blockIdx.x * kDescKpPerCta + it * kDescWarps + warp;  // level-major concatenation
+    if (row >= total || row >= cap) break;
+    int level = 0;
+    while (level + 1 < nl && row >= sStart[level + 1]) level++;
+    const LevelGeom& L = g.lv[level];
+    const uint32_t k = kept[L.keptOff + (long long)f * L.keptCap + (row - sStart[level])];
+    const int x = cand_x(k) + kMinBorder, y = cand_y(k) + kMinBorder;  // level coordinates (:909-910)
+
+    // ---- IC_Angle ----
+    const int pitch = pyr.pitch[level];
+    const uint8_t* center = pyr.lvl[level] + (long long)f * pyr.frameStride[level] + (long long)y * pitch + x;
+    const int chunk = lane & 7, sub = lane >> 3;
+    int m10 = 0, m01 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const int r = 4 * i + sub;  // row index 0..31, v = r - 15
+      if (r < 31) {
+        const uint8_t* p = center + (long long)(r - kHalfPatch) * pitch + (4 * chunk - 16);
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
+        const uint32_t* ap = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+        const uint32_t px = __funnelshift_r(ap[0], ap[1], (uint32_t)(addr & 3) * 8);
+        m10 = dp4a_us(px, sWU[r * 8 + chunk], m10);
+        m01 += (r - kHalfPatch) * (int)__dp4a(px, sWO[r * 8 + chunk], 0u);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+      m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // ---- rBRIEF byte `lane` ----
+    float sn, cs;
+    sincosf_glibc(__fmul_rn(angle, factorPI), &sn, &cs);
+    const float a = cs, b = sn;
+    const uint8_t* bc = blurArena + L.planeOff + (long long)f * L.planeBytes + (long long)y * L.pitch + x;
+    const int bp = L.pitch;
+    int val = 0;
+#pragma unroll
+    for (int bit = 0; bit < 8; bit++) {
+      const float4 q = sPat[bit * 32 + lane];
+      const int r0 = round_half_even_small(__fmaf_rn(q.x, b, __fmul_rn(q.y, a)));
+      const int c0 = round_half_even_small(__fmaf_rn(q.x, a, -__fmul_rn(q.y, b)));
+      const int r1 = round_half_even_small(__fmaf_rn(q.z, b, __fmul_rn(q.w, a)));
+      const int c1 = round_half_even_small(__fmaf_rn(q.z, a, -__fmul_rn(q.w, b)));
+      const int t0 = bc[r0 * bp + c0], t1 = bc[r1 * bp + c1];
+      val |= (t0 < t1) << bit;
+    }
+    outDesc[((long long)f * cap + row) * 32 + lane] = (uint8_t)val;
+
+    if (lane < 7) {  // the 28-byte record as 7 words, one per lane
+      const float fx = (float)x, fy = (float)y;
+      uint32_t wv;
+      switch (lane) {
+        case 0: wv = __float_as_uint(level ? __fmul_rn(fx, L.scale) : fx); break;  // pt *= scale (:1178-1184)
+        case 1: wv = __float_as_uint(level ? __fmul_rn(fy, L.scale) : fy); break;
+        case 2: wv = __float_as_uint(L.patchSize); break;
+        case 3: wv = __float_as_uint(angle); break;
+        case 4: wv = __float_as_uint((float)cand_score(k)); break;
+        case 5: wv = (uint32_t)level; break;
+        default: wv = 0xffffffffu; break;  // class_id = -1
+      }
+      reinterpret_cast<uint32_t*>(outKps + (long long)f * cap + row)[lane] = wv;
+    }
   }
 }
 
-void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const FrameSetGeom* dGeom,
-                     const FrameSetGeom& hGeom, const uint32_t* kept, const int* keptCount,
-                     orbx_keypoint* outKps, uint8_t* outDesc, int cap, int* outN, int nframes,
-                     cudaStream_t s) {
-  const int warpsPerBlock = 8;
+void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const FrameSetGeom& hGeom,
+                     const uint32_t* kept, const int* keptCount, orbx_keypoint* outKps, uint8_t* outDesc, int cap,
+                     int* outN, int nframes, cudaStream_t s) {
   const int maxKp = hGeom.keptPerFrame;
-  dim3 grid((maxKp + warpsPerBlock - 1) / warpsPerBlock, nframes);
-  describe_kernel<<<grid, warpsPerBlock * 32, 0, s>>>(pyr, blurArena, dGeom, kept, keptCount, outKps, outDesc, cap,
-                                                      outN, maxKp);
+  dim3 grid((maxKp + kDescKpPerCta - 1) / kDescKpPerCta, nframes);
+  describe_kernel<<<grid, kDescWarps * 32, 0, s>>>(pyr, blurArena, hGeom, kept, keptCount, outKps, outDesc, cap, outN);
 }
 
 // ---- array versions of the float helpers, for the unit parity tests ----------------------------

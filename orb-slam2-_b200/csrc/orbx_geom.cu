@@ -98,6 +98,28 @@ void build_resize_axis_y(int srcLen, int dstLen, std::vector<ResizeTap>* taps) {
   build_resize_axis(srcLen, dstLen, taps, false);
 }
 
+bool build_resize_groups(const std::vector<ResizeTap>& tx, std::vector<ResizeGroup>* groups) {
+  const int dw = (int)tx.size();
+  groups->assign((dw + 3) / 4, ResizeGroup());
+  for (int gi = 0; gi < (int)groups->size(); gi++) {
+    ResizeGroup& G = (*groups)[gi];
+    const int s0 = tx[4 * gi].p0;  // p0 is non-decreasing along the row
+    G.word = s0 >> 2;
+    G.shift = 8 * (s0 & 3);
+    uint32_t sel[4];
+    for (int j = 0; j < 4; j++) {
+      const ResizeTap& t = tx[std::min(4 * gi + j, dw - 1)];  // pixels past the row end repeat the last one
+      const int o0 = t.p0 - s0, o1 = t.p1 - s0;
+      if (o0 < 0 || o1 < 0 || o0 > 7 || o1 > 7 || t.c0 < 0 || t.c1 < 0) return false;
+      sel[j] = (uint32_t)o0 | ((uint32_t)o1 << 4);
+      G.c[j] = (uint32_t)(uint16_t)t.c0 | ((uint32_t)(uint16_t)t.c1 << 16);
+    }
+    G.sel01 = sel[0] | (sel[1] << 8);
+    G.sel23 = sel[2] | (sel[3] << 8);
+  }
+  return true;
+}
+
 int build_geometry(const orbx_params& p, const CtorTables& t, int w, int h, int batchCap, FrameSetGeom* g) {
   *g = FrameSetGeom();
   g->nlevels = p.nlevels;

@@ -1,0 +1,25 @@
+#!/bin/bash
+# One GPU-box cycle: parity tests, bench line, ncu launch list, ncu --set full of the pipeline kernels.
+# Usage (from the repo root, via gpurun): bash tools/gpu_cycle.sh <tag> [quick]
+TAG=${1:-r1}
+MODE=${2:-full}
+OUT=gpurun_out/$TAG
+mkdir -p $OUT
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > $OUT/gpu.txt 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q > $OUT/pytest.log 2>&1
+echo "pytest exit $?" >> $OUT/pytest.log
+tail -15 $OUT/pytest.log
+timeout 600 python bench.py > $OUT/bench.json 2> $OUT/bench.err
+echo "bench exit $?"; cat $OUT/bench.json; tail -3 $OUT/bench.err
+[ "$MODE" = quick ] && exit 0
+CMD="python bench.py --steps 1 --warmup 3 --skip-e2e --skip-cpu"
+KRE='fast_cells|describe_kernel|blur_kernel|resize4|resize_kernel|octree_kernel'
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"$KRE" --launch-skip 33 -c 11 --csv \
+  --log-file $OUT/launches.csv $CMD > $OUT/ncu_launches.log 2>&1
+echo "ncu launches exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on \
+  -k regex:"$KRE" --launch-skip 33 --launch-count 11 \
+  -o $OUT/pipeline_full -f $CMD > $OUT/ncu_full.log 2>&1
+echo "ncu full exit $?"
+ncu -i $OUT/pipeline_full.ncu-rep --page raw --csv > $OUT/pipeline_full_raw.csv 2>/dev/null
+ls -la $OUT
