@@ -69,6 +69,11 @@ struct KeyPoint {
       : pt(x, y), size(_size), angle(_angle), response(_response), octave(_octave), class_id(_class_id) {}
 };
 
+// cv::Mat::zeros returns a MatExpr; assigning it to a Mat of the same size and type fills that
+// matrix IN PLACE (this is how the reference's computeDescriptors zeroes a row-range view of the
+// output descriptors, R/src/ORBextractor.cpp:1113, without detaching it).
+struct MatZerosExpr { int rows, cols, type; };
+
 // 8-bit single-channel matrix header over a shared buffer (the only type the extractor uses).
 class Mat {
  public:
@@ -89,7 +94,13 @@ class Mat {
     rows = r; cols = c; step = (size_t)c; data = buf_->data();
   }
   void release() { buf_.reset(); rows = cols = 0; step = 0; data = nullptr; }
-  static Mat zeros(int r, int c, int type) { Mat m(r, c, type); if (m.data) std::memset(m.data, 0, (size_t)r * c); return m; }
+  static MatZerosExpr zeros(int r, int c, int type) { return MatZerosExpr{r, c, type}; }
+  Mat(const MatZerosExpr& z) { *this = z; }
+  Mat& operator=(const MatZerosExpr& z) {
+    create(z.rows, z.cols, z.type);
+    for (int r = 0; r < rows; r++) std::memset(ptr(r), 0, (size_t)cols);
+    return *this;
+  }
 
   int type() const { return CV_8UC1; }
   bool empty() const { return data == nullptr || rows == 0 || cols == 0; }

@@ -127,7 +127,8 @@ int run_pipeline(orbx_extractor* h, const uint8_t* dL0, int l0Pitch, long long l
     h->launches++;
   }
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[1], s));
-  launch_fast(pyr, g, static_cast<uint32_t*>(h->candArena.p), candCount, overflow, count, s);
+  int fe = launch_fast(pyr, g, static_cast<uint32_t*>(h->candArena.p), candCount, overflow, count, s);
+  if (fe) { set_error("FAST kernel configuration failed: %s", cudaGetErrorString((cudaError_t)fe)); return ORBX_ERR_CUDA; }
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[2], s));
   int oe = launch_octree(dG, g, static_cast<const uint32_t*>(h->candArena.p), candCount,
@@ -245,6 +246,16 @@ int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_imgs, int32_t 
   int rc = ensure_shape(h, width, height, count);
   if (rc) return rc;
   cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : h->stream;
+  if (row_stride < (size_t)width) { set_error("row_stride %zu < width %d", row_stride, width); return ORBX_ERR_ARG; }
+  if ((reinterpret_cast<uintptr_t>(d_imgs) | row_stride | frame_stride) & 3) {
+    // the kernels read rows as aligned 32-bit words: stage unaligned frames in the arena's level-0 slot
+    const FrameSetGeom& g = h->geom;
+    uint8_t* l0 = static_cast<uint8_t*>(h->pyrArena.p);
+    for (int f = 0; f < count; f++)
+      ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, d_imgs + (size_t)f * frame_stride,
+                                      row_stride, width, height, cudaMemcpyDeviceToDevice, s));
+    return run_pipeline(h, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, d_kps, d_desc, cap, d_n, s);
+  }
   return run_pipeline(h, d_imgs, (int)row_stride, (long long)frame_stride, count, d_kps, d_desc, cap, d_n, s);
 }
 

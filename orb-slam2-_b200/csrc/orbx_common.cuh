@@ -91,8 +91,9 @@ struct PyramidPtrs {
   int pitch[kMaxLevels];
 };
 
-void launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
-                 int nframes, cudaStream_t s);
+// returns 0 or a cudaError_t
+int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
+                int nframes, cudaStream_t s);
 
 // returns 0 or a cudaError_t
 int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const uint32_t* cand,

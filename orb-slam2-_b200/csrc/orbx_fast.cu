@@ -16,20 +16,19 @@
 //    the FIRST max-response point of a node); it is a function of (cell row, cell col, y, x), which
 //    the octree kernel recomputes from the coordinates, so candidates are appended unordered.
 //
-// Kernel shape (v2): one CTA of 128 threads per cell. The cell patch is staged word-aligned in shared
-// memory; every thread scores 4 horizontally adjacent pixels per task with branch-free packed
-// 16x2 min/max (VIMNMX3.U16x2): 16 byte->16x2 unpacks and 80 three-input min/max per PAIR of
-// pixels, no divergence, no per-pixel early-outs -- the cost per pixel is content independent
-// (the v1 kernel was bound by the ALU pipe at 18/32 active lanes; see profiles/).
+// Kernel shape (v3): one WARP per cell, 8 cells per CTA, shared memory sized on the host for the
+// largest cell of the shape. The cell patch is staged word-aligned in shared memory; every lane scores
+// 4 horizontally adjacent pixels per task with branch-free packed 16x2 min/max (VIMNMX3.U16x2):
+// 16 byte->16x2 unpacks and 80 three-input min/max per PAIR of pixels, no divergence, no per-pixel
+// early-outs -- the cost per pixel is content independent. (v1 was one thread per pixel with
+// early-outs: ALU-pipe bound at 18/32 active lanes. v2 was one 128-thread CTA per cell: 80 % lane use
+// because sh*nG tasks rarely fill whole rounds of 128; with 32-lane rounds the tail is ~5 %.)
 #include "orbx_common.cuh"
 
 namespace orbx {
 
-constexpr int kFastThreads = 128;
-constexpr int kTileW = 19;                  // 32-bit words per staged row (cell <= 66 px + 7 px alignment slack)
-constexpr int kTileRows = kMaxCellDim + 2;  // cell height <= 60 + 6
-constexpr int kMapRows = kMaxCellDim;       // scan height <= 60, + one zero row above and below
-constexpr int kOutCap = 1024;               // >= (60/2)^2 survivors of a 3x3 strict NMS
+constexpr int kFastWarps = 8;                 // cells per CTA
+constexpr int kFastThreads = kFastWarps * 32;
 
 // bytes I, I+1 of the 12-byte window (w0,w1,w2) as two 16-bit lanes
 template <int I>
@@ -84,17 +83,22 @@ __device__ __forceinline__ uint32_t fast_margin2(const uint32_t (&W)[7][3], uint
   return __viaddmax_s16x2_relu(m, negThBias, 0u);           // max(m - th, 0)
 }
 
-__global__ void __launch_bounds__(kFastThreads)
-fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
-                  uint32_t* __restrict__ cand, int* __restrict__ candCount, int* __restrict__ overflow) {
-  __shared__ uint32_t tile[kTileRows * kTileW];
-  __shared__ uint32_t smap[(kMapRows + 2) * kTileW];
-  __shared__ uint32_t outList[kOutCap];
-  __shared__ int outCount, passCount, passCursor, outBase;
+// words of shared memory one cell needs: staged patch (ch x nW) + score map ((sh+2) x nW)
+__host__ __device__ inline int fast_cell_words(int wCell, int hCell) {
+  const int nW = ((7 + wCell - 1) >> 2) + 2;  // worst alignment: a = 7
+  return (hCell + 6) * nW + (hCell + 2) * nW;
+}
 
+__global__ void __launch_bounds__(kFastThreads, 4)
+fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
+                  uint32_t* __restrict__ cand, int* __restrict__ candCount, int* __restrict__ overflow,
+                  int wordsPerWarp) {
+  extern __shared__ uint32_t smemFast[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * kFastWarps + warp;
+  if (cell >= g.totalCells) return;  // warps are independent: no block-wide barrier below
   const int nl = g.nlevels;
   int level = 0;
-  const int cell = blockIdx.x;
   while (level + 1 < nl && cell >= g.lv[level + 1].cellBase) level++;
   const LevelGeom& L = g.lv[level];
   const int cidx = cell - L.cellBase;
@@ -118,15 +122,17 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   const int a = iniX + 3 - gx0;
   const int b = a + sw;
   const int nG = (b - 1) >> 2;  // groups q = 0..nG-1 cover tile words 1..nG
-  const int nW = nG + 2;        // staged words per row (<= kTileW)
+  const int nW = nG + 2;        // staged words per row
 
-  const int tid = threadIdx.x;
+  uint32_t* tile = smemFast + warp * wordsPerWarp;  // ch rows x nW words
+  uint32_t* smap = tile + ch * nW;                  // (sh+2) rows x nW words, rows 0 and sh+1 stay zero
+
   const int pitch = pyr.pitch[level];
   const uint8_t* src = pyr.lvl[level] + (long long)f * pyr.frameStride[level] + (long long)iniY * pitch + gx0;
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)pitch) & 3) == 0;
   {
-    int r = tid / nW, c = tid - r * nW;
-    const int dr = kFastThreads / nW, dc = kFastThreads - dr * nW;
+    int r = lane / nW, c = lane - r * nW;
+    const int dr = 32 / nW, dc = 32 - dr * nW;
     while (r < ch) {
       const uint8_t* p = src + (long long)r * pitch + 4 * c;
       uint32_t w;
@@ -135,33 +141,33 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
       } else {
         w = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
       }
-      tile[r * kTileW + c] = w;
+      tile[r * nW + c] = w;
       r += dr; c += dc;
       if (c >= nW) { c -= nW; r++; }
     }
   }
-  for (int i = tid; i < (sh + 2) * kTileW; i += kFastThreads) smap[i] = 0u;
-  if (tid == 0) { outCount = 0; passCount = 0; passCursor = 0; }
-  __syncthreads();
+  for (int i = lane; i < (sh + 2) * nW; i += 32) smap[i] = 0u;
+  __syncwarp();
 
   const int minTh = g.minTh, iniTh = g.iniTh;
   // per 16-bit lane: -(256 + minTh)
   const uint32_t negTh = (uint32_t)(-(256 + minTh)) & 0xffffu;
   const uint32_t negThBias = negTh | (negTh << 16);
   const int nTasks = sh * nG;
-  const int dy = kFastThreads / nG, dq = kFastThreads - dy * nG;
+  const int dy = 32 / nG, dq = 32 - dy * nG;
+  const int y0 = lane / nG, q0 = lane - y0 * nG;
 
   // ---- score map: max(m - minTh, 0) for every scanned pixel (0 = not a corner at minTh) ----
   {
-    int y = tid / nG, q = tid - y * nG;
-    for (int t = tid; t < nTasks; t += kFastThreads) {
-      const uint32_t* tp = &tile[y * kTileW + q];
+    int y = y0, q = q0;
+    for (int t = lane; t < nTasks; t += 32) {
+      const uint32_t* tp = &tile[y * nW + q];
       uint32_t W[7][3];
 #pragma unroll
       for (int j = 0; j < 7; j++) {
-        W[j][0] = tp[j * kTileW];
-        W[j][1] = tp[j * kTileW + 1];
-        W[j][2] = tp[j * kTileW + 2];
+        W[j][0] = tp[j * nW];
+        W[j][1] = tp[j * nW + 1];
+        W[j][2] = tp[j * nW + 2];
       }
       const uint32_t u01 = fast_margin2<4>(W, negThBias);
       const uint32_t u23 = fast_margin2<6>(W, negThBias);
@@ -170,37 +176,98 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
       const int skipLo = a - col0, skipHi = col0 + 4 - b;
       if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
       if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
-      smap[(y + 1) * kTileW + q + 1] = word;
+      smap[(y + 1) * nW + q + 1] = word;
       y += dy; q += dq;
       if (q >= nG) { q -= nG; y++; }
     }
   }
-  __syncthreads();
+  __syncwarp();
 
-  // ---- cell-local 3x3 strict non-max suppression; survivors go to a shared list ----
-  int anyIni = 0;
+  // ---- cell-local 3x3 strict non-max suppression, packed: the 8-neighbour maximum of two adjacent
+  //      pixels is 4 VIMNMX on 16x2 lanes; survivors' scores go to a second map that reuses the
+  //      patch rows (same indexing as smap) ----
+  uint32_t* kmap = tile;
+  const int iniByte = max(iniTh - minTh + 1, 1);  // stored value of a pixel whose score is iniTh
+  uint32_t iniFlag = 0;
   {
-    const uint8_t* sb = reinterpret_cast<const uint8_t*>(smap);
-    constexpr int S = kTileW * 4;
-    int y = tid / nG, q = tid - y * nG;
-    for (int t = tid; t < nTasks; t += kFastThreads) {
-      const uint32_t word = smap[(y + 1) * kTileW + q + 1];
+    const uint32_t negIni = ((uint32_t)(-(iniByte - 1)) & 0xffffu) * 0x00010001u;
+    int y = y0, q = q0;
+    for (int t = lane; t < nTasks; t += 32) {
+      const uint32_t* mp = &smap[y * nW + q];  // map rows y, y+1, y+2 = image rows y-1, y, y+1
+      uint32_t E[3][5];                        // column pairs (3,4) (4,5) (5,6) (6,7) (7,8) of the 12-byte window
+#pragma unroll
+      for (int r = 0; r < 3; r++) {
+        const uint32_t w0 = mp[r * nW], w1 = mp[r * nW + 1], w2 = mp[r * nW + 2];
+        E[r][0] = ex2<3>(w0, w1, w2);
+        E[r][1] = ex2<4>(w0, w1, w2);
+        E[r][2] = ex2<5>(w0, w1, w2);
+        E[r][3] = ex2<6>(w0, w1, w2);
+        E[r][4] = ex2<7>(w0, w1, w2);
+      }
+      uint32_t kept[2];
+#pragma unroll
+      for (int p = 0; p < 2; p++) {  // pixel pairs (0,1) and (2,3): left/centre/right pairs E[.][2p .. 2p+2]
+        const uint32_t up = __vimax3_u16x2(E[0][2 * p], E[0][2 * p + 1], E[0][2 * p + 2]);
+        const uint32_t dn = __vimax3_u16x2(E[2][2 * p], E[2][2 * p + 1], E[2][2 * p + 2]);
+        const uint32_t M = __vimax3_u16x2(up, dn, __vmaxu2(E[1][2 * p], E[1][2 * p + 2]));
+        const uint32_t sc = E[1][2 * p + 1];
+        const uint32_t d = __viaddmax_s16x2_relu(sc + 0x01000100u - M, 0xff00ff00u, 0u);  // max(s - M, 0)
+        kept[p] = __vminu2(sc, d << 8);                                                   // s if s > M else 0
+        iniFlag |= __viaddmax_s16x2_relu(kept[p], negIni, 0u);
+      }
+      kmap[(y + 1) * nW + q + 1] = __byte_perm(kept[0], kept[1], 0x6420);
+      y += dy; q += dq;
+      if (q >= nG) { q -= nG; y++; }
+    }
+  }
+  // "cell empty after NMS at iniThFAST?" (:875-883) is a warp-wide vote
+  const bool useIni = __any_sync(0xffffffffu, iniFlag != 0);
+  const int thByte = useIni ? iniByte : 1;
+  int mine = 0;
+  {
+    int y = y0, q = q0;
+    for (int t = lane; t < nTasks; t += 32) {
+      const uint32_t word = kmap[(y + 1) * nW + q + 1];
+      if (word) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) mine += (int)((word >> (8 * j)) & 0xff) >= thByte;
+      }
+      y += dy; q += dq;
+      if (q >= nG) { q -= nG; y++; }
+    }
+  }
+  // exclusive prefix of `mine` over the warp + total
+  int incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  const int total = __shfl_sync(0xffffffffu, incl, 31);
+  if (total == 0) return;
+  int base = 0;
+  if (lane == 0) {
+    base = atomicAdd(&candCount[f * nl + level], total);
+    if (base + total > L.candCap) atomicExch(overflow, 1);
+  }
+  base = __shfl_sync(0xffffffffu, base, 0);
+  __syncwarp();
+  int slot = base + incl - mine;
+  const long long slotBase = L.candOff + (long long)f * L.candCap;
+  {
+    int y = y0, q = q0;
+    for (int t = lane; t < nTasks; t += 32) {
+      const uint32_t word = kmap[(y + 1) * nW + q + 1];
       if (word) {
 #pragma unroll
         for (int j = 0; j < 4; j++) {
           const int s = (word >> (8 * j)) & 0xff;
-          if (s) {
-            const int col = 4 * (q + 1) + j;
-            const uint8_t* c = sb + (y + 1) * S + col;
-            const bool keep = s > c[-S - 1] && s > c[-S] && s > c[-S + 1] && s > c[-1] && s > c[1] &&
-                              s > c[S - 1] && s > c[S] && s > c[S + 1];
-            if (keep) {
-              const int score = s + minTh - 1;  // cv::FAST's cornerScore
-              const int slot = atomicAdd(&outCount, 1);
-              // coordinates relative to minBorder: cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
-              if (slot < kOutCap) outList[slot] = pack_cand(col - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, score);
-              anyIni |= score >= iniTh;
-            }
+          if (s >= thByte) {
+            // cv::FAST's cornerScore = s + minTh - 1; coordinates relative to minBorder:
+            // cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
+            if (slot < L.candCap)
+              cand[slotBase + slot] = pack_cand(4 * (q + 1) + j - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, s + minTh - 1);
+            slot++;
           }
         }
       }
@@ -208,37 +275,20 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
       if (q >= nG) { q -= nG; y++; }
     }
   }
-  // "cell empty after NMS at iniThFAST?" (:875-883) is a block-wide vote
-  const int useIni = __syncthreads_or(anyIni);
-  const int th = useIni ? iniTh : minTh;
-  const int n = min(outCount, kOutCap);
-  if (n == 0) return;
-
-  int mine = 0;
-  for (int i = tid; i < n; i += kFastThreads) mine += cand_score(outList[i]) >= th;
-  if (mine) atomicAdd(&passCount, mine);
-  __syncthreads();
-  const int total = passCount;
-  const long long slotBase = L.candOff + (long long)f * L.candCap;
-  if (tid == 0) outBase = atomicAdd(&candCount[f * nl + level], total);
-  __syncthreads();
-  const int base = outBase;
-  if (base + total > L.candCap) {
-    if (tid == 0) atomicExch(overflow, 1);
-  }
-  for (int i = tid; i < n; i += kFastThreads) {
-    const uint32_t c = outList[i];
-    if (cand_score(c) >= th) {
-      const int slot = base + atomicAdd(&passCursor, 1);
-      if (slot < L.candCap) cand[slotBase + slot] = c;
-    }
-  }
 }
 
-void launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
-                 int nframes, cudaStream_t s) {
-  dim3 grid(hGeom.totalCells, nframes);
-  fast_cells_kernel<<<grid, kFastThreads, 0, s>>>(pyr, hGeom, cand, candCount, overflow);
+int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
+                int nframes, cudaStream_t s) {
+  int words = 0;
+  for (int l = 0; l < hGeom.nlevels; l++) words = max(words, fast_cell_words(hGeom.lv[l].wCell, hGeom.lv[l].hCell));
+  const size_t smem = (size_t)words * 4 * kFastWarps;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+  }
+  dim3 grid((hGeom.totalCells + kFastWarps - 1) / kFastWarps, nframes);
+  fast_cells_kernel<<<grid, kFastThreads, smem, s>>>(pyr, hGeom, cand, candCount, overflow, words);
+  return 0;
 }
 
 }  // namespace orbx

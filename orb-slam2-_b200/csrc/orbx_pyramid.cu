@@ -4,7 +4,8 @@
 //           (R/src/ORBextractor.cpp:1212). The 11-bit fixed-point coefficient tables are computed
 //           once per shape on the host (orbx_geom.cu) exactly as OpenCV does; the kernels are pure
 //           integer arithmetic.
-//           resize4_kernel: one thread per 4 destination pixels. Per source row it loads the three
+//           resize4_kernel: one thread per 4 destination pixels x 8 destination rows (horizontally
+//           interpolated source rows are reused between them). Per source row it loads the three
 //           aligned words that hold the <= 8 source bytes of the group, realigns them with a funnel
 //           shift, gathers (left,right) byte pairs with two PRMTs whose selectors come from the
 //           table, and does the horizontal interpolation with IDP.2A (16-bit weights x 8-bit
@@ -14,10 +15,11 @@
 //  blur   : cv::GaussianBlur 7x7 sigma 2 BORDER_REFLECT_101 on a border-less copy of each level
 //           (R/src/ORBextractor.cpp:1166-1167): 8.8 fixed-point kernel {18,34,48,56,48,34,18},
 //           exact 16-bit horizontal pass, 16.16 vertical pass, one rounding.
-//           One warp per 128x32 pixel strip: each lane owns 4 adjacent columns, the horizontal pass
-//           is 10 IDP.4A per row on the lane's word and its neighbours' words (two shuffles), the
-//           vertical pass runs over a 7-row register window. No shared memory, every source row is
-//           read once per strip (+6 halo rows), one 32-bit store per lane and row.
+//           Eight lanes per 32x32 pixel strip (four strips per warp): each lane owns 4 adjacent
+//           columns, the horizontal pass is 10 IDP.4A per row on the lane's word and its neighbours'
+//           words (two width-8 shuffles), the vertical pass runs over a 7-row register window, loads
+//           run 4 rows ahead. No shared memory, every source row is read once per strip (+6 halo
+//           rows), one 32-bit store per lane and row; image borders are rebuilt with PRMT.
 //
 // Both are HBM-streaming stencils: each source byte is fetched from DRAM once and each destination
 // byte written once.
@@ -61,44 +63,70 @@ __device__ __forceinline__ void resize_row4(const uint32_t* __restrict__ row, co
   h[3] = __dp2a_hi(G.c[3], b23, 0u);
 }
 
-__global__ void __launch_bounds__(256)
+constexpr int kResizeRows = 8;   // destination rows per thread (source rows are reused between them)
+constexpr int kResizeBands = 4;  // threadIdx.y
+
+__global__ void __launch_bounds__(32 * kResizeBands)
 resize4_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int srcPitch,
                uint8_t* __restrict__ dst, long long dstFrameStride, int dstPitch, int dw, int dh,
                const ResizeGroup* __restrict__ xg, const ResizeTap* __restrict__ yt) {
   const int gx = blockIdx.x * 32 + threadIdx.x;  // group of 4 destination pixels
-  const int dy = blockIdx.y * 8 + threadIdx.y;
-  if (4 * gx >= dw || dy >= dh) return;
+  const int dy0 = (blockIdx.y * kResizeBands + threadIdx.y) * kResizeRows;
+  if (4 * gx >= dw || dy0 >= dh) return;
   const uint8_t* S = src + (long long)blockIdx.z * srcFrameStride;
+  uint8_t* D = dst + (long long)blockIdx.z * dstFrameStride + 4 * gx;
   const ResizeGroup G = xg[gx];
-  const ResizeTap ty = yt[dy];
   const int maxWord = (srcPitch >> 2) - 1;
-  uint32_t h0[4], h1[4];
-  resize_row4(reinterpret_cast<const uint32_t*>(S + (long long)ty.p0 * srcPitch), G, maxWord, h0);
-  resize_row4(reinterpret_cast<const uint32_t*>(S + (long long)ty.p1 * srcPitch), G, maxWord, h1);
-  uint32_t out = 0;
+  // horizontally interpolated source rows ia / ib are kept between destination rows (dy is uniform
+  // across the warp, so the reuse branches do not diverge)
+  int ia = -1, ib = -1;
+  uint32_t ha[4] = {0, 0, 0, 0}, hb[4] = {0, 0, 0, 0};
+  const int dyEnd = min(dy0 + kResizeRows, dh);
+  for (int dy = dy0; dy < dyEnd; dy++) {
+    const ResizeTap ty = yt[dy];
+    if (ty.p0 != ia) {
+      if (ty.p0 == ib) {
 #pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const int v = ((((int)ty.c0 * (int)(h0[j] >> 4)) >> 16) + (((int)ty.c1 * (int)(h1[j] >> 4)) >> 16) + 2) >> 2;
-    out |= (uint32_t)min(max(v, 0), 255) << (8 * j);
+        for (int j = 0; j < 4; j++) ha[j] = hb[j];
+      } else {
+        resize_row4(reinterpret_cast<const uint32_t*>(S + (long long)ty.p0 * srcPitch), G, maxWord, ha);
+      }
+      ia = ty.p0;
+    }
+    if (ty.p1 != ib) {
+      if (ty.p1 == ia) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) hb[j] = ha[j];
+      } else {
+        resize_row4(reinterpret_cast<const uint32_t*>(S + (long long)ty.p1 * srcPitch), G, maxWord, hb);
+      }
+      ib = ty.p1;
+    }
+    uint32_t out = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int v = ((((int)ty.c0 * (int)(ha[j] >> 4)) >> 16) + (((int)ty.c1 * (int)(hb[j] >> 4)) >> 16) + 2) >> 2;
+      out |= (uint32_t)min(max(v, 0), 255) << (8 * j);
+    }
+    // destination planes are ours: pitch is a multiple of 16, so the whole word is inside the row
+    *reinterpret_cast<uint32_t*>(D + (long long)dy * dstPitch) = out;
   }
-  // destination planes are ours: pitch is a multiple of 16, so the whole word is inside the row
-  *reinterpret_cast<uint32_t*>(dst + (long long)blockIdx.z * dstFrameStride + (long long)dy * dstPitch + 4 * gx) = out;
 }
 
 void launch_resize(const uint8_t* src, long long srcFrameStride, int srcPitch, int sw, int sh,
                    uint8_t* dst, long long dstFrameStride, int dstPitch, int dw, int dh,
                    const ResizeTables& t, int nframes, cudaStream_t s) {
   (void)sw; (void)sh;
-  dim3 block(32, 8);
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)srcPitch | (uintptr_t)srcFrameStride |
                          reinterpret_cast<uintptr_t>(dst) | (uintptr_t)dstPitch | (uintptr_t)dstFrameStride) & 3) == 0;
   if (t.xg && aligned) {
-    dim3 grid(((dw + 3) / 4 + 31) / 32, (dh + 7) / 8, nframes);
-    resize4_kernel<<<grid, block, 0, s>>>(src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,
+    const int rowsPerCta = kResizeRows * kResizeBands;
+    dim3 grid(((dw + 3) / 4 + 31) / 32, (dh + rowsPerCta - 1) / rowsPerCta, nframes);
+    resize4_kernel<<<grid, dim3(32, kResizeBands), 0, s>>>(src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,
                                           t.xg, t.yt);
   } else {
     dim3 grid((dw + 31) / 32, (dh + 7) / 8, nframes);
-    resize_kernel<<<grid, block, 0, s>>>(src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,
+    resize_kernel<<<grid, dim3(32, 8), 0, s>>>(src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,
                                          t.xt, t.yt);
   }
 }
@@ -106,8 +134,9 @@ void launch_resize(const uint8_t* src, long long srcFrameStride, int srcPitch, i
 // ------------------------------------------------------------------------------------------------
 // blur
 // ------------------------------------------------------------------------------------------------
-constexpr int kBlurStripW = 128, kBlurStripH = 32;
-constexpr int kBlurWarps = 4;
+constexpr int kBlurStripW = 32, kBlurStripH = 32;  // one strip = 8 lanes x 4 px, 32 output rows
+constexpr int kBlurWarps = 4;                      // 4 strips per warp, 16 per CTA
+constexpr int kBlurPrefetch = 4;                   // rows in flight per lane
 
 __device__ __forceinline__ int reflect101(int p, int len) {
   // len >= 4 on every level we accept, so one reflection per side is enough for a 3-pixel halo
@@ -116,64 +145,89 @@ __device__ __forceinline__ int reflect101(int p, int len) {
   return p;
 }
 
-// pixels x..x+3 of a row as one word, BORDER_REFLECT_101 outside [0,w)
-__device__ __forceinline__ uint32_t blur_load4(const uint8_t* __restrict__ row, int x, int w, bool aligned) {
-  if (aligned && x >= 0 && x + 3 < w) return *reinterpret_cast<const uint32_t*>(row + x);
-  uint32_t v = 0;
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const int c = reflect101(min(x + i, w + 2), w);
-    v |= (uint32_t)row[c] << (8 * i);
-  }
-  return v;
-}
-
-__device__ __forceinline__ uint32_t dp4a_u(uint32_t a, uint32_t b, uint32_t c) { return __dp4a(a, b, c); }
-
-// One warp: output columns x0 + 4*lane .. +3, rows y0 .. y0+kBlurStripH-1.
-__device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int srcPitch, uint8_t* __restrict__ dst,
-                                           int dstPitch, int w, int h, int x0, int y0) {
-  const int lane = threadIdx.x & 31;
-  const int x = x0 + 4 * lane;
-  const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)srcPitch) & 3) == 0;
-  // horizontal taps of pixel j over the 12-byte window (left word, own word, right word), byte i of
-  // the window = column x-4+i; kernel k = {18,34,48,56,48,34,18} centred on column x+j
+// horizontal taps of pixel j over the 12-byte window (left word, own word, right word), byte i of the
+// window = column x-4+i; kernel k = {18,34,48,56,48,34,18} centred on column x+j
+__device__ __forceinline__ void blur_hrow(uint32_t l, uint32_t c, uint32_t r, int (&H)[4]) {
   constexpr uint32_t L0 = 0x30221200u, C0 = 0x12223038u;                    // j=0: bytes 1..7
   constexpr uint32_t L1 = 0x22120000u, C1 = 0x22303830u, R1 = 0x00000012u;  // j=1: bytes 2..8
   constexpr uint32_t L2 = 0x12000000u, C2 = 0x30383022u, R2 = 0x00001222u;  // j=2: bytes 3..9
   constexpr uint32_t C3 = 0x38302212u, R3 = 0x00122230u;                    // j=3: bytes 4..10
-  int H[7][4];
-  const bool active = x < w;  // lanes past the right edge still feed their left neighbour
-  const bool feeds = x < w + 4;
+  H[0] = (int)__dp4a(l, L0, __dp4a(c, C0, 0u));
+  H[1] = (int)__dp4a(l, L1, __dp4a(c, C1, __dp4a(r, R1, 0u)));
+  H[2] = (int)__dp4a(l, L2, __dp4a(c, C2, __dp4a(r, R2, 0u)));
+  H[3] = (int)__dp4a(c, C3, __dp4a(r, R3, 0u));
+}
+
+__device__ __forceinline__ uint32_t blur_vcol(const int (&H)[7][4], int r) {
+  // rows r-6..r of the rotating window are taps 0..6
+  uint32_t out = 0;
 #pragma unroll
-  for (int r = 0; r < kBlurStripH + 6; r++) {
+  for (int j = 0; j < 4; j++) {
+    const uint32_t v = 18u * (uint32_t)(H[(r - 6) % 7][j] + H[r % 7][j]) +
+                       34u * (uint32_t)(H[(r - 5) % 7][j] + H[(r - 1) % 7][j]) +
+                       48u * (uint32_t)(H[(r - 4) % 7][j] + H[(r - 2) % 7][j]) + 56u * (uint32_t)H[(r - 3) % 7][j];
+    out |= ((v + 32768u) >> 16) << (8 * j);
+  }
+  return out;
+}
+
+// Fast path: source rows 4-byte aligned, w >= 12. Eight lanes own a 32-px wide strip; every lane does
+// one aligned 32-bit load per row (plus one halo load on the strip's first and last lane); image
+// borders (BORDER_REFLECT_101) are rebuilt from the loaded words with PRMT selectors that are fixed
+// per strip. `valid` is false for the lanes of a quarter-warp without a strip: they run the
+// shuffles with everybody else and store nothing.
+__device__ __forceinline__ void blur_strip8(const uint8_t* __restrict__ src, int srcPitch, uint8_t* __restrict__ dst,
+                                            int dstPitch, int w, int h, int x0, int y0, bool valid) {
+  const int sub = threadIdx.x & 7;
+  const int x = x0 + 4 * sub;
+  const int lastX = (w - 1) & ~3;           // column of the last (possibly partial) word of a row
+  const int xl = min(x, lastX);
+  const bool first = sub == 0, last = sub == 7;
+  const bool isLastWord = x == lastX;
+  const int e = w - 1 - lastX;              // index of the last valid byte in the last word, 0..3
+  // selC: (left, raw) -> the last word with columns >= w reflected; selR: (left, raw) -> the word after it
+  uint32_t selC = 0, selR = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    selC |= (uint32_t)(i <= e ? 4 + i : 4 + 2 * e - i) << (4 * i);
+    selR |= (uint32_t)max(2 * e - i, 0) << (4 * i);
+  }
+  const uint32_t selOwn = isLastWord ? selC : 0x7654u;                       // applied to (l, raw)
+  const uint32_t selHalo = (x + 4 == lastX) ? selC : 0x7654u;                // applied to (own, rawRight)
+  const bool haloL = valid && first && x > 0;
+  const bool haloR = valid && last && x + 4 <= lastX;
+  const int xr = min(x + 4, lastX);
+
+  uint32_t qc[kBlurPrefetch], ql[kBlurPrefetch], qr[kBlurPrefetch];
+  auto fetch = [&](int r, int slot) {
     const int yy = reflect101(min(y0 + r - 3, h + 2), h);
     const uint8_t* row = src + (long long)yy * srcPitch;
-    uint32_t c = 0;
-    if (feeds) c = blur_load4(row, x, w, aligned);
-    uint32_t l = __shfl_up_sync(0xffffffffu, c, 1);
-    uint32_t rr = __shfl_down_sync(0xffffffffu, c, 1);
-    if (lane == 0) l = blur_load4(row, x - 4, w, aligned);
-    if (lane == 31 && active) rr = blur_load4(row, x + 4, w, aligned);
-    int* Hr = H[r % 7];
-    Hr[0] = (int)dp4a_u(l, L0, dp4a_u(c, C0, 0u));
-    Hr[1] = (int)dp4a_u(l, L1, dp4a_u(c, C1, dp4a_u(rr, R1, 0u)));
-    Hr[2] = (int)dp4a_u(l, L2, dp4a_u(c, C2, dp4a_u(rr, R2, 0u)));
-    Hr[3] = (int)dp4a_u(c, C3, dp4a_u(rr, R3, 0u));
+    qc[slot] = valid ? *reinterpret_cast<const uint32_t*>(row + xl) : 0u;
+    ql[slot] = haloL ? *reinterpret_cast<const uint32_t*>(row + x - 4) : 0u;
+    qr[slot] = haloR ? *reinterpret_cast<const uint32_t*>(row + xr) : 0u;
+  };
+#pragma unroll
+  for (int r = 0; r < kBlurPrefetch; r++) fetch(r, r);
+
+  int H[7][4];
+#pragma unroll
+  for (int r = 0; r < kBlurStripH + 6; r++) {
+    const uint32_t raw = qc[r % kBlurPrefetch];
+    const uint32_t hl = ql[r % kBlurPrefetch], hr = qr[r % kBlurPrefetch];
+    if (r + kBlurPrefetch < kBlurStripH + 6) fetch(r + kBlurPrefetch, r % kBlurPrefetch);
+    uint32_t l = __shfl_up_sync(0xffffffffu, raw, 1, 8);
+    if (first) l = hl;                                    // x == 0 is fixed below, once r is known
+    const uint32_t c = __byte_perm(l, raw, selOwn);
+    uint32_t rr = __shfl_down_sync(0xffffffffu, c, 1, 8);
+    if (last) rr = __byte_perm(c, hr, selHalo);
+    if (isLastWord) rr = __byte_perm(l, raw, selR);
+    if (x == 0) l = __byte_perm(c, rr, 0x1234);           // columns -4..-1 = columns 4,3,2,1
+    blur_hrow(l, c, rr, H[r % 7]);
     if (r >= 6) {
       const int y = y0 + r - 6;
-      // rows r-6..r of the window are taps 0..6
-      uint32_t out = 0;
-#pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const uint32_t v = 18u * (uint32_t)(H[(r - 6) % 7][j] + H[r % 7][j]) +
-                           34u * (uint32_t)(H[(r - 5) % 7][j] + H[(r - 1) % 7][j]) +
-                           48u * (uint32_t)(H[(r - 4) % 7][j] + H[(r - 2) % 7][j]) +
-                           56u * (uint32_t)H[(r - 3) % 7][j];
-        out |= ((v + 32768u) >> 16) << (8 * j);
-      }
+      const uint32_t out = blur_vcol(H, r);
       // destination planes are ours (pitch multiple of 16): the word never leaves the row
-      if (active && y < h) *reinterpret_cast<uint32_t*>(dst + (long long)y * dstPitch + x) = out;
+      if (valid && x <= lastX && y < h) *reinterpret_cast<uint32_t*>(dst + (long long)y * dstPitch + x) = out;
     }
   }
 }
@@ -181,27 +235,46 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, int 
 __global__ void __launch_bounds__(kBlurWarps * 32)
 blur_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
             uint8_t* __restrict__ blurArena) {
-  const int task = blockIdx.x * kBlurWarps + (threadIdx.x >> 5);
-  if (task >= g.totalTiles) return;
+  const int task = (blockIdx.x * kBlurWarps + (threadIdx.x >> 5)) * 4 + ((threadIdx.x & 31) >> 3);
+  const bool valid = task < g.totalTiles;
   int level = 0;
   const int nl = g.nlevels;
   while (level + 1 < nl && task >= g.lv[level + 1].tileBase) level++;
   const LevelGeom& L = g.lv[level];
-  const int t = task - L.tileBase;
+  const int t = valid ? task - L.tileBase : 0;
   const int ty = t / L.tilesX, tx = t - ty * L.tilesX;
   const int f = blockIdx.y;
   const uint8_t* src = pyr.lvl[level] + (long long)f * pyr.frameStride[level];
   uint8_t* dst = blurArena + L.planeOff + (long long)f * L.planeBytes;
-  blur_strip(src, pyr.pitch[level], dst, L.pitch, L.w, L.h, tx * kBlurStripW, ty * kBlurStripH);
+  blur_strip8(src, pyr.pitch[level], dst, L.pitch, L.w, L.h, tx * kBlurStripW, ty * kBlurStripH, valid);
 }
 
 __global__ void __launch_bounds__(kBlurWarps * 32)
 blur_single_kernel(const uint8_t* __restrict__ src, int srcPitch, uint8_t* __restrict__ dst, int dstPitch, int w,
                    int h, int tilesX, int tiles) {
-  const int task = blockIdx.x * kBlurWarps + (threadIdx.x >> 5);
-  if (task >= tiles) return;
-  const int ty = task / tilesX, tx = task - ty * tilesX;
-  blur_strip(src, srcPitch, dst, dstPitch, w, h, tx * kBlurStripW, ty * kBlurStripH);
+  const int task = (blockIdx.x * kBlurWarps + (threadIdx.x >> 5)) * 4 + ((threadIdx.x & 31) >> 3);
+  const bool valid = task < tiles;
+  const int t = valid ? task : 0;
+  const int ty = t / tilesX, tx = t - ty * tilesX;
+  blur_strip8(src, srcPitch, dst, dstPitch, w, h, tx * kBlurStripW, ty * kBlurStripH, valid);
+}
+
+// General form (any alignment, any size >= 4x4): one thread per pixel, used by orbx_blur7_u8 for images
+// narrower than 12 px; the pipeline never needs it (levels are >= 62 px wide and staged aligned).
+__global__ void __launch_bounds__(256)
+blur_generic_kernel(const uint8_t* __restrict__ src, int srcPitch, uint8_t* __restrict__ dst, int dstPitch, int w,
+                    int h) {
+  const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (x >= w || y >= h) return;
+  const int k[7] = {18, 34, 48, 56, 48, 34, 18};
+  uint32_t v = 0;
+  for (int j = 0; j < 7; j++) {
+    const uint8_t* row = src + (long long)reflect101(y + j - 3, h) * srcPitch;
+    uint32_t hsum = 0;
+    for (int i = 0; i < 7; i++) hsum += (uint32_t)k[i] * row[reflect101(x + i - 3, w)];
+    v += (uint32_t)k[j] * hsum;
+  }
+  dst[(long long)y * dstPitch + x] = (uint8_t)((v + 32768u) >> 16);
 }
 
 void blur_tiles_for(int w, int h, int* tilesX, int* tilesY) {
@@ -210,15 +283,23 @@ void blur_tiles_for(int w, int h, int* tilesX, int* tilesY) {
 }
 
 void launch_blur(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint8_t* blurArena, int nframes, cudaStream_t s) {
-  dim3 grid((hGeom.totalTiles + kBlurWarps - 1) / kBlurWarps, nframes);
+  const int perCta = kBlurWarps * 4;
+  dim3 grid((hGeom.totalTiles + perCta - 1) / perCta, nframes);
   blur_kernel<<<grid, kBlurWarps * 32, 0, s>>>(pyr, hGeom, blurArena);
 }
 
 void launch_blur_single(const uint8_t* src, int srcPitch, uint8_t* dst, int dstPitch, int w, int h, cudaStream_t s) {
-  int tx, ty;
-  blur_tiles_for(w, h, &tx, &ty);
-  blur_single_kernel<<<(tx * ty + kBlurWarps - 1) / kBlurWarps, kBlurWarps * 32, 0, s>>>(src, srcPitch, dst, dstPitch,
-                                                                                         w, h, tx, tx * ty);
+  const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)srcPitch) & 3) == 0;
+  if (aligned && w >= 12) {
+    int tx, ty;
+    blur_tiles_for(w, h, &tx, &ty);
+    const int perCta = kBlurWarps * 4;
+    blur_single_kernel<<<(tx * ty + perCta - 1) / perCta, kBlurWarps * 32, 0, s>>>(src, srcPitch, dst, dstPitch, w, h,
+                                                                                   tx, tx * ty);
+  } else {
+    dim3 grid((w + 31) / 32, (h + 7) / 8);
+    blur_generic_kernel<<<grid, 256, 0, s>>>(src, srcPitch, dst, dstPitch, w, h);
+  }
 }
 
 }  // namespace orbx

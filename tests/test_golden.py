@@ -36,3 +36,27 @@ def test_extractor_regression_hashes(oracle, pkg):
         k, d = oracle.Extractor(int(nf), 1.2, 8, 20, 7)(img)
         assert len(k) == int(e[key + "_n"])
         assert hashlib.sha256(k.tobytes() + d.tobytes()).hexdigest() == str(e[key + "_sha"])
+
+
+def _ref_cases():
+    e = np.load(G / "ref_extract.npz")
+    return e, sorted(k[:-4] for k in e.files if k.endswith("_sha"))
+
+
+def test_oracle_matches_reference_golden(oracle, pkg):
+    """ref_extract.npz was produced by the REFERENCE's own ORBextractor.cpp (oracle/_ref with the monotonic
+    allocator, tools/make_golden_ref.py); the oracle must reproduce it bit for bit."""
+    e, keys = _ref_cases()
+    assert len(keys) >= 6
+    for key in keys:
+        wh, nf, seed, kind = key.split("_")
+        w, h = map(int, wh.split("x"))
+        if w * h > 800 * 600:
+            continue  # the 1080p case runs in the GPU suite; keep the CPU suite short
+        img = pkg.synth.frame(w, h, int(seed), kind)
+        assert hashlib.sha256(img.tobytes()).hexdigest() == str(e[key + "_imgsha"]), "synthetic generator drifted"
+        k, d = oracle.Extractor(int(nf), 1.2, 8, 20, 7)(img)
+        assert len(k) == int(e[key + "_n"]), key
+        assert np.array_equal(k[:8].view(np.uint8), e[key + "_k8"].view(np.uint8)), key
+        assert np.array_equal(d[:8], e[key + "_d8"]), key
+        assert hashlib.sha256(k.tobytes() + d.tobytes()).hexdigest() == str(e[key + "_sha"]), key

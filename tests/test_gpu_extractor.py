@@ -15,7 +15,8 @@ def test_resize_bit_exact(pkg, oracle, w, h):
         assert np.array_equal(pkg.resize_u8(img, dw, dh), oracle.resize(img, dw, dh))
 
 
-@pytest.mark.parametrize("w,h", SHAPES + [(37, 29), (64, 32), (65, 33), (4, 4)])
+@pytest.mark.parametrize("w,h", SHAPES + [(37, 29), (64, 32), (65, 33), (4, 4), (38, 30), (39, 31), (12, 12), (13, 9),
+                                          (11, 11), (33, 70), (130, 5)])
 def test_blur_bit_exact(pkg, oracle, w, h):
     for kind in ("shapes", "noise"):
         img = pkg.synth.frame(w, h, 12, kind)
@@ -145,3 +146,23 @@ def test_errors_are_loud(pkg):
         ex(np.zeros((1080, 1920), np.uint8))  # larger than the handle was sized for
     with pytest.raises(TypeError):
         ex(np.zeros((480, 640), np.float32))
+
+
+def test_extract_matches_reference_golden(pkg):
+    """CUDA path vs golden vectors produced by the REFERENCE's own ORBextractor.cpp (tools/make_golden_ref.py;
+    /root/reference does not exist on the GPU box, the vectors do)."""
+    import hashlib
+    from pathlib import Path
+    e = np.load(Path(__file__).resolve().parent / "golden" / "ref_extract.npz")
+    keys = sorted(k[:-4] for k in e.files if k.endswith("_sha"))
+    assert len(keys) >= 6
+    for key in keys:
+        wh, nf, seed, kind = key.split("_")
+        w, h = map(int, wh.split("x"))
+        img = pkg.synth.frame(w, h, int(seed), kind)
+        assert hashlib.sha256(img.tobytes()).hexdigest() == str(e[key + "_imgsha"])
+        ex = pkg.ORBextractor(int(nf), 1.2, 8, 20, 7, max_width=w, max_height=h)
+        k, d = ex(img)
+        assert len(k) == int(e[key + "_n"]), key
+        assert np.array_equal(k[:8].view(np.uint8), e[key + "_k8"].view(np.uint8)), key
+        assert hashlib.sha256(k.tobytes() + d.tobytes()).hexdigest() == str(e[key + "_sha"]), key
