@@ -1,6 +1,11 @@
 // C ABI of liborbx.so, extractor half (include/orbx.h). Host orchestration only: shape-dependent
 // setup, arena management, the launch sequence of the extraction pipeline, and host<->device copies
 // for the host-buffer entry points. No CPU implementation of any stage lives here.
+//
+// Host-buffer batches are cut into chunks of kChunk frames that alternate between two lanes (stream +
+// arenas + pinned staging each): while chunk k runs its kernels, chunk k+1's frames cross PCIe and
+// chunk k-1's keypoints/descriptors are scattered into the caller's arrays by the host thread.
+#include <algorithm>
 #include <cstring>
 #include <new>
 
@@ -9,6 +14,8 @@
 using namespace orbx;
 
 namespace {
+
+constexpr int kChunk = 32;  // frames per lane submission on the host-buffer path
 
 int check_device(int device) {
   int n = 0;
@@ -25,47 +32,24 @@ int check_device(int device) {
   return ORBX_OK;
 }
 
-// (Re)build geometry, coefficient tables and arenas for a frame shape / batch size.
-int ensure_shape(orbx_extractor* h, int w, int hh, int count) {
-  if (w <= 0 || hh <= 0 || count <= 0) { set_error("bad shape %dx%d x%d", w, hh, count); return ORBX_ERR_ARG; }
-  if (w > h->params.max_width || hh > h->params.max_height || count > h->params.max_batch) {
-    set_error("frame %dx%d x%d exceeds the handle's limits %dx%d x%d", w, hh, count, h->params.max_width,
-              h->params.max_height, h->params.max_batch);
-    return ORBX_ERR_ARG;
-  }
-  if (w == h->w && hh == h->h && count <= h->batchCap) return ORBX_OK;
-  const int batchCap = h->params.max_batch;
-  FrameSetGeom g;
-  int rc = build_geometry(h->params, h->tables, w, hh, batchCap, &g);
-  if (rc) return rc;
+int init_lane(Lane& L) {
+  if (L.stream) return ORBX_OK;
+  ORBX_CUDA_TRY(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 8; i++) ORBX_CUDA_TRY(cudaEventCreate(&L.ev[i]));
+  ORBX_CUDA_TRY(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+  return ORBX_OK;
+}
+
+// resize coefficient tables for a frame shape: x/y taps and (when they exist) 4-pixel groups per level
+int ensure_taps(orbx_extractor* h, const FrameSetGeom& g, int w, int hh, cudaStream_t s) {
+  if (h->tapW == w && h->tapH == hh) return ORBX_OK;
+  // both lanes may still be reading the old tables
+  for (Lane& L : h->lane) if (L.stream) ORBX_CUDA_TRY(cudaStreamSynchronize(L.stream));
   const int nl = g.nlevels;
-  long long candTotal = 0, keptTotal = 0;
-  for (int l = 0; l < nl; l++) {
-    candTotal += (long long)g.lv[l].candCap * batchCap;
-    keptTotal += (long long)g.lv[l].keptCap * batchCap;
-  }
-  if ((rc = h->pyrArena.ensure((size_t)g.pyrFrameStride + 64))) return rc;
-  if ((rc = h->blurArena.ensure((size_t)g.pyrFrameStride + 64))) return rc;
-  if ((rc = h->candArena.ensure((size_t)candTotal * 4))) return rc;
-  if ((rc = h->nodeArena.ensure((size_t)candTotal * 2))) return rc;
-  if ((rc = h->keptArena.ensure((size_t)keptTotal * 4))) return rc;
-  if ((rc = h->counts.ensure((size_t)(2 * batchCap * nl + 4) * sizeof(int)))) return rc;
-  if ((rc = h->dGeom.ensure(sizeof(FrameSetGeom)))) return rc;
-  if ((rc = h->outKps.ensure((size_t)batchCap * g.keptPerFrame * sizeof(orbx_keypoint)))) return rc;
-  if ((rc = h->outDesc.ensure((size_t)batchCap * g.keptPerFrame * 32))) return rc;
-  if ((rc = h->outN.ensure((size_t)batchCap * sizeof(int)))) return rc;
-  const size_t stageBytes = (size_t)batchCap * g.keptPerFrame * (sizeof(orbx_keypoint) + 32) + (size_t)batchCap * 4 + 64;
-  if (stageBytes > h->hostStageBytes) {
-    if (h->hostStage) cudaFreeHost(h->hostStage);
-    h->hostStage = nullptr;
-    h->hostStageBytes = 0;
-    ORBX_CUDA_TRY(cudaMallocHost(&h->hostStage, stageBytes));
-    h->hostStageBytes = stageBytes;
-  }
-  // resize coefficient tables per destination level: x/y taps and (when they exist) 4-pixel groups
   size_t tapCount = 0, groupCount = 0;
   for (int l = 1; l < nl; l++) { tapCount += g.lv[l].w + g.lv[l].h; groupCount += (g.lv[l].w + 3) / 4; }
   const size_t groupBytes = groupCount * sizeof(ResizeGroup);
+  int rc;
   if ((rc = h->tapArena.ensure(groupBytes + std::max<size_t>(tapCount, 1) * sizeof(ResizeTap)))) return rc;
   std::vector<ResizeGroup> groups, xg;
   std::vector<ResizeTap> all, tx, ty;
@@ -87,93 +71,216 @@ int ensure_shape(orbx_extractor* h, int w, int hh, int count) {
     }
   }
   if (!groups.empty())
-    ORBX_CUDA_TRY(cudaMemcpyAsync(h->tapArena.p, groups.data(), groups.size() * sizeof(ResizeGroup), cudaMemcpyHostToDevice, h->stream));
-  ORBX_CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(h->tapArena.p) + groupBytes, all.data(), all.size() * sizeof(ResizeTap),
-                                cudaMemcpyHostToDevice, h->stream));
-  ORBX_CUDA_TRY(cudaMemcpyAsync(h->dGeom.p, &g, sizeof(g), cudaMemcpyHostToDevice, h->stream));
-  ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));  // `all`, `groups` and `g` are stack/heap temporaries
-  h->geom = g;
-  h->w = w; h->h = hh; h->batchCap = batchCap;
-  h->haveResult = false;
+    ORBX_CUDA_TRY(cudaMemcpyAsync(h->tapArena.p, groups.data(), groups.size() * sizeof(ResizeGroup), cudaMemcpyHostToDevice, s));
+  if (!all.empty())
+    ORBX_CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(h->tapArena.p) + groupBytes, all.data(), all.size() * sizeof(ResizeTap),
+                                  cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(s));  // `all` and `groups` are temporaries; the other lane may read next
+  h->tapW = w; h->tapH = hh;
   return ORBX_OK;
 }
 
-// The extraction pipeline on `count` frames whose level 0 is already on the device.
-int run_pipeline(orbx_extractor* h, const uint8_t* dL0, int l0Pitch, long long l0FrameStride, int count,
+// (Re)build geometry and arenas of a lane for a frame shape and a capacity of `cap` frames.
+int ensure_lane(orbx_extractor* h, Lane& L, int w, int hh, int cap) {
+  if (w <= 0 || hh <= 0 || cap <= 0) { set_error("bad shape %dx%d x%d", w, hh, cap); return ORBX_ERR_ARG; }
+  if (w > h->params.max_width || hh > h->params.max_height || cap > h->params.max_batch) {
+    set_error("frame %dx%d x%d exceeds the handle's limits %dx%d x%d", w, hh, cap, h->params.max_width,
+              h->params.max_height, h->params.max_batch);
+    return ORBX_ERR_ARG;
+  }
+  int rc;
+  if ((rc = init_lane(L))) return rc;
+  if (w == L.w && hh == L.h && cap <= L.batchCap) return ensure_taps(h, L.geom, w, hh, L.stream);
+  ORBX_CUDA_TRY(cudaStreamSynchronize(L.stream));
+  const int batchCap = (w == L.w && hh == L.h) ? std::max(cap, L.batchCap) : cap;
+  FrameSetGeom g;
+  if ((rc = build_geometry(h->params, h->tables, w, hh, batchCap, &g))) return rc;
+  const int nl = g.nlevels;
+  long long candTotal = 0, keptTotal = 0;
+  for (int l = 0; l < nl; l++) {
+    candTotal += (long long)g.lv[l].candCap * batchCap;
+    keptTotal += (long long)g.lv[l].keptCap * batchCap;
+  }
+  if ((rc = L.pyrArena.ensure((size_t)g.pyrFrameStride + 64))) return rc;
+  if ((rc = L.blurArena.ensure((size_t)g.pyrFrameStride + 64))) return rc;
+  if ((rc = L.candArena.ensure((size_t)candTotal * 4))) return rc;
+  if ((rc = L.nodeArena.ensure((size_t)candTotal * 2))) return rc;
+  if ((rc = L.keptArena.ensure((size_t)keptTotal * 4))) return rc;
+  if ((rc = L.counts.ensure((size_t)(2 * batchCap * nl + 4) * sizeof(int)))) return rc;
+  if ((rc = L.dGeom.ensure(sizeof(FrameSetGeom)))) return rc;
+  ORBX_CUDA_TRY(cudaMemcpyAsync(L.dGeom.p, &g, sizeof(g), cudaMemcpyHostToDevice, L.stream));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(L.stream));  // `g` is a stack temporary
+  L.geom = g;
+  L.w = w; L.h = hh; L.batchCap = batchCap;
+  if (&L == &h->lane[0]) h->haveResult = false;
+  return ensure_taps(h, L.geom, w, hh, L.stream);
+}
+
+// device + pinned staging for the host-buffer entry points
+int ensure_lane_staging(Lane& L) {
+  const FrameSetGeom& g = L.geom;
+  int rc;
+  if ((rc = L.outKps.ensure((size_t)L.batchCap * g.keptPerFrame * sizeof(orbx_keypoint)))) return rc;
+  if ((rc = L.outDesc.ensure((size_t)L.batchCap * g.keptPerFrame * 32))) return rc;
+  if ((rc = L.outN.ensure((size_t)L.batchCap * sizeof(int)))) return rc;
+  const size_t stageBytes = (size_t)L.batchCap * g.keptPerFrame * (sizeof(orbx_keypoint) + 32) + (size_t)L.batchCap * 4 + 64;
+  if (stageBytes > L.hostStageBytes) {
+    if (L.hostStage) cudaFreeHost(L.hostStage);
+    L.hostStage = nullptr;
+    L.hostStageBytes = 0;
+    ORBX_CUDA_TRY(cudaMallocHost(&L.hostStage, stageBytes));
+    L.hostStageBytes = stageBytes;
+  }
+  return ORBX_OK;
+}
+
+// The extraction pipeline on `count` frames whose level 0 is already on the device, on stream `s`.
+int run_pipeline(orbx_extractor* h, Lane& L, const uint8_t* dL0, int l0Pitch, long long l0FrameStride, int count,
                  orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dN, cudaStream_t s) {
-  const FrameSetGeom& g = h->geom;
+  const FrameSetGeom& g = L.geom;
   const int nl = g.nlevels;
   PyramidPtrs pyr;
   for (int l = 0; l < kMaxLevels; l++) { pyr.lvl[l] = nullptr; pyr.frameStride[l] = 0; pyr.pitch[l] = 0; }
   pyr.lvl[0] = dL0; pyr.frameStride[0] = l0FrameStride; pyr.pitch[0] = l0Pitch;
-  uint8_t* arena = static_cast<uint8_t*>(h->pyrArena.p);
+  uint8_t* arena = static_cast<uint8_t*>(L.pyrArena.p);
   for (int l = 1; l < nl; l++) {
     pyr.lvl[l] = arena + g.lv[l].planeOff;
     pyr.frameStride[l] = g.lv[l].planeBytes;
     pyr.pitch[l] = g.lv[l].pitch;
   }
-  int* candCount = static_cast<int*>(h->counts.p);
-  int* keptCount = candCount + h->batchCap * nl;
-  int* overflow = keptCount + h->batchCap * nl;
-  const FrameSetGeom* dG = static_cast<const FrameSetGeom*>(h->dGeom.p);
+  int* candCount = static_cast<int*>(L.counts.p);
+  int* keptCount = candCount + L.batchCap * nl;
+  int* overflow = keptCount + L.batchCap * nl;
+  const FrameSetGeom* dG = static_cast<const FrameSetGeom*>(L.dGeom.p);
   const bool prof = h->profiling;
 
-  if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[0], s));
-  ORBX_CUDA_TRY(cudaMemsetAsync(candCount, 0, (size_t)(2 * h->batchCap * nl + 1) * sizeof(int), s));
+  if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[0], s));
+  ORBX_CUDA_TRY(cudaMemsetAsync(candCount, 0, (size_t)(2 * L.batchCap * nl + 1) * sizeof(int), s));
   for (int l = 1; l < nl; l++) {
     launch_resize(pyr.lvl[l - 1], pyr.frameStride[l - 1], pyr.pitch[l - 1], g.lv[l - 1].w, g.lv[l - 1].h,
                   arena + g.lv[l].planeOff, g.lv[l].planeBytes, g.lv[l].pitch, g.lv[l].w, g.lv[l].h, h->taps[l],
                   count, s);
     h->launches++;
   }
-  if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[1], s));
-  int fe = launch_fast(pyr, g, static_cast<uint32_t*>(h->candArena.p), candCount, overflow, count, s);
+  if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[1], s));
+  int fe = launch_fast(pyr, g, static_cast<uint32_t*>(L.candArena.p), candCount, overflow, count, s);
   if (fe) { set_error("FAST kernel configuration failed: %s", cudaGetErrorString((cudaError_t)fe)); return ORBX_ERR_CUDA; }
   h->launches++;
-  if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[2], s));
-  int oe = launch_octree(dG, g, static_cast<const uint32_t*>(h->candArena.p), candCount,
-                         static_cast<uint16_t*>(h->nodeArena.p), static_cast<uint32_t*>(h->keptArena.p), keptCount,
+  if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[2], s));
+  int oe = launch_octree(dG, g, static_cast<const uint32_t*>(L.candArena.p), candCount,
+                         static_cast<uint16_t*>(L.nodeArena.p), static_cast<uint32_t*>(L.keptArena.p), keptCount,
                          count, s);
   if (oe) { set_error("octree kernel configuration failed: %s", cudaGetErrorString((cudaError_t)oe)); return ORBX_ERR_CUDA; }
   h->launches++;
-  if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[3], s));
-  launch_blur(pyr, g, static_cast<uint8_t*>(h->blurArena.p), count, s);
+  if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[3], s));
+  launch_blur(pyr, g, static_cast<uint8_t*>(L.blurArena.p), count, s);
   h->launches++;
-  if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[4], s));
-  launch_describe(pyr, static_cast<const uint8_t*>(h->blurArena.p), g, static_cast<const uint32_t*>(h->keptArena.p),
+  if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[4], s));
+  launch_describe(pyr, static_cast<const uint8_t*>(L.blurArena.p), g, static_cast<const uint32_t*>(L.keptArena.p),
                   keptCount, dKps, dDesc, cap, dN, count, s);
   h->launches++;
-  if (prof) ORBX_CUDA_TRY(cudaEventRecord(h->ev[5], s));
+  if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[5], s));
   ORBX_CUDA_TRY(cudaGetLastError());
-  h->lastCount = count;
-  h->lastLevel0 = dL0; h->lastL0FrameStride = l0FrameStride; h->lastL0Pitch = l0Pitch;
-  h->haveResult = true;
+  if (&L == &h->lane[0]) {
+    h->lastCount = count;
+    h->lastLevel0 = dL0; h->lastL0FrameStride = l0FrameStride; h->lastL0Pitch = l0Pitch;
+    h->haveResult = true;
+  }
   return ORBX_OK;
 }
 
-int collect_profile(orbx_extractor* h) {
-  if (!h->profiling) return ORBX_OK;
-  ORBX_CUDA_TRY(cudaEventSynchronize(h->ev[5]));
-  for (int i = 0; i < 5; i++) ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[i], h->ev[i], h->ev[i + 1]));
-  ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[5], h->ev[0], h->ev[5]));
+struct HostStage {  // layout of Lane::hostStage
+  orbx_keypoint* kps;
+  uint8_t* desc;
+  int* n;
+  int* overflow;
+};
+HostStage stage_of(const Lane& L) {
+  uint8_t* st = static_cast<uint8_t*>(L.hostStage);
+  const size_t rows = (size_t)L.batchCap * L.geom.keptPerFrame;
+  HostStage s;
+  s.kps = reinterpret_cast<orbx_keypoint*>(st);
+  s.desc = st + rows * sizeof(orbx_keypoint);
+  s.n = reinterpret_cast<int*>(s.desc + rows * 32);
+  s.overflow = s.n + L.batchCap;
+  return s;
+}
+
+// H2D + pipeline + D2H of one chunk, all asynchronous on the lane's stream
+int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int count, int width, int height, size_t stride) {
+  const FrameSetGeom& g = L.geom;
+  cudaStream_t s = L.stream;
+  uint8_t* l0 = static_cast<uint8_t*>(L.pyrArena.p);  // level-0 slot of the arena (planeOff 0)
+  bool contiguous = true;
+  for (int f = 0; f < count; f++) {
+    if (!imgs[f]) { set_error("imgs[%d] is null", f); return ORBX_ERR_ARG; }
+    contiguous = contiguous && imgs[f] == imgs[0] + (size_t)f * stride * height;
+  }
+  if (contiguous && g.lv[0].planeBytes == (long long)g.lv[0].pitch * height) {
+    // frames back to back on the host: one 2-D copy of count*height rows
+    ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0, g.lv[0].pitch, imgs[0], stride, width, (size_t)height * count, cudaMemcpyHostToDevice, s));
+  } else {
+    for (int f = 0; f < count; f++)
+      ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, imgs[f], stride, width, height,
+                                      cudaMemcpyHostToDevice, s));
+  }
+  const int rows = g.keptPerFrame;
+  orbx_keypoint* dK = static_cast<orbx_keypoint*>(L.outKps.p);
+  uint8_t* dD = static_cast<uint8_t*>(L.outDesc.p);
+  int* dN = static_cast<int*>(L.outN.p);
+  int rc = run_pipeline(h, L, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, dK, dD, rows, dN, s);
+  if (rc) return rc;
+  HostStage st = stage_of(L);
+  const int* dOverflow = static_cast<const int*>(L.counts.p) + 2 * L.batchCap * g.nlevels;
+  ORBX_CUDA_TRY(cudaMemcpyAsync(st.n, dN, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(st.overflow, dOverflow, sizeof(int), cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(st.kps, dK, (size_t)count * rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(st.desc, dD, (size_t)count * rows * 32, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaEventRecord(L.done, s));
   return ORBX_OK;
 }
 
-int check_overflow(orbx_extractor* h, cudaStream_t s) {
-  int* overflow = static_cast<int*>(h->counts.p) + 2 * h->batchCap * h->geom.nlevels;
-  int v = 0;
-  ORBX_CUDA_TRY(cudaMemcpyAsync(&v, overflow, sizeof(int), cudaMemcpyDeviceToHost, s));
-  ORBX_CUDA_TRY(cudaStreamSynchronize(s));
-  if (v) { set_error("FAST candidate list overflowed its capacity (corner density above 1 per 8 pixels)"); return ORBX_ERR_CAPACITY; }
+// wait for a submitted chunk and scatter its rows into the caller's arrays
+int collect_chunk(orbx_extractor* h, Lane& L, int count, orbx_keypoint* kps, uint8_t* desc, int cap, int* n, bool* tooSmall) {
+  ORBX_CUDA_TRY(cudaEventSynchronize(L.done));
+  HostStage st = stage_of(L);
+  if (*st.overflow) {
+    set_error("FAST candidate list overflowed its capacity (corner density above 1 per 8 pixels)");
+    return ORBX_ERR_CAPACITY;
+  }
+  if (h->profiling) {
+    for (int i = 0; i < 5; i++) ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[i], L.ev[i], L.ev[i + 1]));
+    ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[5], L.ev[0], L.ev[5]));
+  }
+  const int rows = L.geom.keptPerFrame;
+  for (int f = 0; f < count; f++) {
+    const int nf = st.n[f];
+    n[f] = nf;
+    if (nf > cap) { *tooSmall = true; continue; }
+    std::memcpy(kps + (size_t)f * cap, st.kps + (size_t)f * rows, (size_t)nf * sizeof(orbx_keypoint));
+    std::memcpy(desc + (size_t)f * cap * 32, st.desc + (size_t)f * rows * 32, (size_t)nf * 32);
+  }
   return ORBX_OK;
 }
 
 }  // namespace
 
+void orbx::Lane::release() {
+  if (stream) cudaStreamSynchronize(stream);
+  dGeom.release(); pyrArena.release(); blurArena.release(); candArena.release(); nodeArena.release();
+  keptArena.release(); counts.release(); outKps.release(); outDesc.release(); outN.release();
+  if (hostStage) cudaFreeHost(hostStage);
+  hostStage = nullptr; hostStageBytes = 0;
+  for (int i = 0; i < 8; i++) if (ev[i]) { cudaEventDestroy(ev[i]); ev[i] = nullptr; }
+  if (done) { cudaEventDestroy(done); done = nullptr; }
+  if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
+  w = h = batchCap = 0;
+}
+
 extern "C" {
 
 const char* orbx_last_error(void) { return last_error(); }
-const char* orbx_version(void) { return "orbx 0.1 sm_100a"; }
+const char* orbx_version(void) { return "orbx 0.2 sm_100a"; }
 int orbx_device_count(void) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -195,13 +302,7 @@ int orbx_extractor_create(const orbx_params* p, orbx_extractor** out) {
   if (!h) { set_error("out of host memory"); return ORBX_ERR_ARG; }
   h->params = *p;
   build_ctor_tables(p->nfeatures, p->scale_factor, p->nlevels, &h->tables);
-  cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
-  for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreate(&h->ev[i]);
-  if (e != cudaSuccess) {
-    set_error("stream/event creation failed: %s", cudaGetErrorString(e));
-    orbx_extractor_destroy(h);
-    return ORBX_ERR_CUDA;
-  }
+  if ((rc = init_lane(h->lane[0]))) { orbx_extractor_destroy(h); return rc; }
   // validate the largest shape now so that unsupported parameters fail at construction
   FrameSetGeom g;
   rc = build_geometry(h->params, h->tables, p->max_width, p->max_height, 1, &g);
@@ -213,13 +314,8 @@ int orbx_extractor_create(const orbx_params* p, orbx_extractor** out) {
 void orbx_extractor_destroy(orbx_extractor* h) {
   if (!h) return;
   cudaSetDevice(h->params.device);
-  if (h->stream) cudaStreamSynchronize(h->stream);
-  h->dGeom.release(); h->pyrArena.release(); h->blurArena.release(); h->candArena.release();
-  h->nodeArena.release(); h->keptArena.release(); h->counts.release(); h->tapArena.release();
-  h->outKps.release(); h->outDesc.release(); h->outN.release();
-  if (h->hostStage) cudaFreeHost(h->hostStage);
-  for (int i = 0; i < 8; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
-  if (h->stream) cudaStreamDestroy(h->stream);
+  for (Lane& L : h->lane) L.release();
+  h->tapArena.release();
   delete h;
 }
 
@@ -242,65 +338,62 @@ int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_imgs, int32_t 
                               size_t row_stride, size_t frame_stride, orbx_keypoint* d_kps, uint8_t* d_desc,
                               int32_t cap, int32_t* d_n, void* stream) {
   if (!h || !d_imgs || !d_kps || !d_desc || !d_n || cap <= 0) { set_error("null/invalid argument"); return ORBX_ERR_ARG; }
-  ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
-  int rc = ensure_shape(h, width, height, count);
-  if (rc) return rc;
-  cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : h->stream;
   if (row_stride < (size_t)width) { set_error("row_stride %zu < width %d", row_stride, width); return ORBX_ERR_ARG; }
+  ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
+  Lane& L = h->lane[0];
+  int rc = ensure_lane(h, L, width, height, count);
+  if (rc) return rc;
+  cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : L.stream;
   if ((reinterpret_cast<uintptr_t>(d_imgs) | row_stride | frame_stride) & 3) {
     // the kernels read rows as aligned 32-bit words: stage unaligned frames in the arena's level-0 slot
-    const FrameSetGeom& g = h->geom;
-    uint8_t* l0 = static_cast<uint8_t*>(h->pyrArena.p);
+    const FrameSetGeom& g = L.geom;
+    uint8_t* l0 = static_cast<uint8_t*>(L.pyrArena.p);
     for (int f = 0; f < count; f++)
       ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, d_imgs + (size_t)f * frame_stride,
                                       row_stride, width, height, cudaMemcpyDeviceToDevice, s));
-    return run_pipeline(h, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, d_kps, d_desc, cap, d_n, s);
+    return run_pipeline(h, L, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, d_kps, d_desc, cap, d_n, s);
   }
-  return run_pipeline(h, d_imgs, (int)row_stride, (long long)frame_stride, count, d_kps, d_desc, cap, d_n, s);
+  return run_pipeline(h, L, d_imgs, (int)row_stride, (long long)frame_stride, count, d_kps, d_desc, cap, d_n, s);
 }
 
 int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width, int32_t height,
                        size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n) {
-  if (!h || !imgs || !kps || !desc || !n || cap <= 0) { set_error("null/invalid argument"); return ORBX_ERR_ARG; }
+  if (!h || !imgs || !kps || !desc || !n || cap <= 0 || count <= 0) { set_error("null/invalid argument"); return ORBX_ERR_ARG; }
   if (stride < (size_t)width) { set_error("stride %zu < width %d", stride, width); return ORBX_ERR_ARG; }
+  if (count > h->params.max_batch) {
+    set_error("batch of %d frames exceeds the handle's max_batch %d", count, h->params.max_batch);
+    return ORBX_ERR_ARG;
+  }
   ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
-  int rc = ensure_shape(h, width, height, count);
-  if (rc) return rc;
-  const FrameSetGeom& g = h->geom;
-  cudaStream_t s = h->stream;
-  uint8_t* l0 = static_cast<uint8_t*>(h->pyrArena.p);  // level-0 slot of the arena (planeOff 0)
-  for (int f = 0; f < count; f++) {
-    if (!imgs[f]) { set_error("imgs[%d] is null", f); return ORBX_ERR_ARG; }
-    ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, imgs[f], stride, width, height,
-                                    cudaMemcpyHostToDevice, s));
+  const int chunk = std::min(kChunk, count);
+  const int nchunks = (count + chunk - 1) / chunk;
+  const int nlanes = nchunks > 1 ? 2 : 1;
+  int rc;
+  for (int i = 0; i < nlanes; i++) {
+    if ((rc = ensure_lane(h, h->lane[i], width, height, chunk))) return rc;
+    if ((rc = ensure_lane_staging(h->lane[i]))) return rc;
   }
-  const int rows = g.keptPerFrame;
-  orbx_keypoint* dK = static_cast<orbx_keypoint*>(h->outKps.p);
-  uint8_t* dD = static_cast<uint8_t*>(h->outDesc.p);
-  int* dN = static_cast<int*>(h->outN.p);
-  rc = run_pipeline(h, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, dK, dD, rows, dN, s);
-  if (rc) return rc;
-  // one D2H per output array into pinned staging, then row copies into the caller's buffers
-  uint8_t* st = static_cast<uint8_t*>(h->hostStage);
-  orbx_keypoint* hK = reinterpret_cast<orbx_keypoint*>(st);
-  uint8_t* hD = st + (size_t)h->batchCap * rows * sizeof(orbx_keypoint);
-  int* hN = reinterpret_cast<int*>(hD + (size_t)h->batchCap * rows * 32);
-  ORBX_CUDA_TRY(cudaMemcpyAsync(hN, dN, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
-  ORBX_CUDA_TRY(cudaMemcpyAsync(hK, dK, (size_t)count * rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
-  ORBX_CUDA_TRY(cudaMemcpyAsync(hD, dD, (size_t)count * rows * 32, cudaMemcpyDeviceToHost, s));
-  rc = check_overflow(h, s);  // synchronises the stream
-  if (rc) return rc;
-  if ((rc = collect_profile(h))) return rc;
   bool tooSmall = false;
-  for (int f = 0; f < count; f++) {
-    n[f] = hN[f];
-    if (hN[f] > cap) tooSmall = true;
+  for (int c = 0; c <= nchunks; c++) {
+    if (c < nchunks) {
+      const int f0 = c * chunk, cnt = std::min(chunk, count - f0);
+      if (c >= 2) {  // the lane's staging still holds chunk c-2: scatter it before reusing the lane
+        const int g0 = (c - 2) * chunk, gc = std::min(chunk, count - g0);
+        if ((rc = collect_chunk(h, h->lane[c & 1], gc, kps + (size_t)g0 * cap, desc + (size_t)g0 * cap * 32, cap, n + g0,
+                                &tooSmall)))
+          return rc;
+      }
+      if ((rc = submit_chunk(h, h->lane[c & 1], imgs + f0, cnt, width, height, stride))) return rc;
+    }
   }
+  for (int c = std::max(nchunks - 2, 0); c < nchunks; c++) {
+    const int f0 = c * chunk, cnt = std::min(chunk, count - f0);
+    if ((rc = collect_chunk(h, h->lane[c & 1], cnt, kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, n + f0,
+                            &tooSmall)))
+      return rc;
+  }
+  if (nchunks > 1) h->haveResult = false;  // introspection only covers single-chunk batches
   if (tooSmall) { set_error("keypoint capacity %d too small (see n[])", cap); return ORBX_ERR_CAPACITY; }
-  for (int f = 0; f < count; f++) {
-    std::memcpy(kps + (size_t)f * cap, hK + (size_t)f * rows, (size_t)hN[f] * sizeof(orbx_keypoint));
-    std::memcpy(desc + (size_t)f * cap * 32, hD + (size_t)f * rows * 32, (size_t)hN[f] * 32);
-  }
   return ORBX_OK;
 }
 

@@ -31,16 +31,16 @@ int use_device(int device) {
 }
 
 int copy_plane_out(orbx_extractor* h, const uint8_t* dsrc, int pitch, int w, int hh, uint8_t* dst, size_t dstStride) {
-  ORBX_CUDA_TRY(cudaMemcpy2DAsync(dst, dstStride, dsrc, pitch, w, hh, cudaMemcpyDeviceToHost, h->stream));
-  ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+  ORBX_CUDA_TRY(cudaMemcpy2DAsync(dst, dstStride, dsrc, pitch, w, hh, cudaMemcpyDeviceToHost, h->lane[0].stream));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(h->lane[0].stream));
   return ORBX_OK;
 }
 
 int check_result(const orbx_extractor* h, int frame, int level) {
   if (!h) { set_error("null handle"); return ORBX_ERR_ARG; }
   if (!h->haveResult) { set_error("no extraction has run on this handle yet"); return ORBX_ERR_STATE; }
-  if (level < 0 || level >= h->geom.nlevels || frame < 0 || frame >= h->lastCount) {
-    set_error("frame %d / level %d out of range (%d frames, %d levels)", frame, level, h->lastCount, h->geom.nlevels);
+  if (level < 0 || level >= h->lane[0].geom.nlevels || frame < 0 || frame >= h->lastCount) {
+    set_error("frame %d / level %d out of range (%d frames, %d levels)", frame, level, h->lastCount, h->lane[0].geom.nlevels);
     return ORBX_ERR_ARG;
   }
   return ORBX_OK;
@@ -52,10 +52,10 @@ extern "C" {
 
 int orbx_level_size(const orbx_extractor* h, int32_t level, int32_t* width, int32_t* height) {
   if (!h || !width || !height) { set_error("null argument"); return ORBX_ERR_ARG; }
-  if (h->w == 0) { set_error("no extraction has run on this handle yet"); return ORBX_ERR_STATE; }
-  if (level < 0 || level >= h->geom.nlevels) { set_error("level %d out of range", level); return ORBX_ERR_ARG; }
-  *width = h->geom.lv[level].w;
-  *height = h->geom.lv[level].h;
+  if (h->lane[0].w == 0) { set_error("no extraction has run on this handle yet"); return ORBX_ERR_STATE; }
+  if (level < 0 || level >= h->lane[0].geom.nlevels) { set_error("level %d out of range", level); return ORBX_ERR_ARG; }
+  *width = h->lane[0].geom.lv[level].w;
+  *height = h->lane[0].geom.lv[level].h;
   return ORBX_OK;
 }
 
@@ -64,10 +64,10 @@ int orbx_get_level(orbx_extractor* h, int32_t frame, int32_t level, uint8_t* dst
   if (rc) return rc;
   if (!dst) { set_error("null dst"); return ORBX_ERR_ARG; }
   ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
-  const LevelGeom& L = h->geom.lv[level];
+  const LevelGeom& L = h->lane[0].geom.lv[level];
   if (level == 0)
     return copy_plane_out(h, h->lastLevel0 + (long long)frame * h->lastL0FrameStride, h->lastL0Pitch, L.w, L.h, dst, dst_stride);
-  const uint8_t* src = static_cast<const uint8_t*>(h->pyrArena.p) + L.planeOff + (long long)frame * L.planeBytes;
+  const uint8_t* src = static_cast<const uint8_t*>(h->lane[0].pyrArena.p) + L.planeOff + (long long)frame * L.planeBytes;
   return copy_plane_out(h, src, L.pitch, L.w, L.h, dst, dst_stride);
 }
 
@@ -76,8 +76,8 @@ int orbx_get_blurred_level(orbx_extractor* h, int32_t frame, int32_t level, uint
   if (rc) return rc;
   if (!dst) { set_error("null dst"); return ORBX_ERR_ARG; }
   ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
-  const LevelGeom& L = h->geom.lv[level];
-  const uint8_t* src = static_cast<const uint8_t*>(h->blurArena.p) + L.planeOff + (long long)frame * L.planeBytes;
+  const LevelGeom& L = h->lane[0].geom.lv[level];
+  const uint8_t* src = static_cast<const uint8_t*>(h->lane[0].blurArena.p) + L.planeOff + (long long)frame * L.planeBytes;
   return copy_plane_out(h, src, L.pitch, L.w, L.h, dst, dst_stride);
 }
 
@@ -86,20 +86,20 @@ int orbx_get_level_candidates(orbx_extractor* h, int32_t frame, int32_t level, i
   if (rc) return rc;
   if (!n) { set_error("null n"); return ORBX_ERR_ARG; }
   ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
-  const LevelGeom& L = h->geom.lv[level];
-  const int nl = h->geom.nlevels;
+  const LevelGeom& L = h->lane[0].geom.lv[level];
+  const int nl = h->lane[0].geom.nlevels;
   int cnt = 0;
-  ORBX_CUDA_TRY(cudaMemcpyAsync(&cnt, static_cast<const int*>(h->counts.p) + frame * nl + level, sizeof(int),
-                                cudaMemcpyDeviceToHost, h->stream));
-  ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(&cnt, static_cast<const int*>(h->lane[0].counts.p) + frame * nl + level, sizeof(int),
+                                cudaMemcpyDeviceToHost, h->lane[0].stream));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(h->lane[0].stream));
   cnt = std::min(cnt, L.candCap);
   *n = cnt;
   const int m = std::min(cnt, cap);
   if (m > 0 && xys) {
     std::vector<uint32_t> tmp(m);
-    ORBX_CUDA_TRY(cudaMemcpyAsync(tmp.data(), static_cast<const uint32_t*>(h->candArena.p) + L.candOff + (long long)frame * L.candCap,
-                                  (size_t)m * 4, cudaMemcpyDeviceToHost, h->stream));
-    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(tmp.data(), static_cast<const uint32_t*>(h->lane[0].candArena.p) + L.candOff + (long long)frame * L.candCap,
+                                  (size_t)m * 4, cudaMemcpyDeviceToHost, h->lane[0].stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->lane[0].stream));
     for (int i = 0; i < m; i++) {
       xys[3 * i] = cand_x(tmp[i]); xys[3 * i + 1] = cand_y(tmp[i]); xys[3 * i + 2] = cand_score(tmp[i]);
     }
@@ -118,9 +118,10 @@ int orbx_set_profiling(orbx_extractor* h, int32_t enable) {
 int orbx_last_stage_ms(orbx_extractor* h, float* ms6) {
   if (!h || !ms6) { set_error("null argument"); return ORBX_ERR_ARG; }
   if (!h->profiling || !h->haveResult) { set_error("profiling not enabled or nothing extracted"); return ORBX_ERR_STATE; }
-  ORBX_CUDA_TRY(cudaEventSynchronize(h->ev[5]));
-  for (int i = 0; i < 5; i++) ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[i], h->ev[i], h->ev[i + 1]));
-  ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[5], h->ev[0], h->ev[5]));
+  const Lane& L = h->lane[0];
+  ORBX_CUDA_TRY(cudaEventSynchronize(L.ev[5]));
+  for (int i = 0; i < 5; i++) ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[i], L.ev[i], L.ev[i + 1]));
+  ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[5], L.ev[0], L.ev[5]));
   for (int i = 0; i < 6; i++) ms6[i] = h->stageMs[i];
   return ORBX_OK;
 }

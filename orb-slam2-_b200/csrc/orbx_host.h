@@ -35,24 +35,41 @@ struct DeviceBuf {
 
 }  // namespace orbx
 
+namespace orbx {
+
+// One in-flight batch: a stream, its device arenas and pinned staging. The host-buffer entry points
+// alternate between two lanes so that the H2D copy of chunk k+1, the kernels of chunk k and the D2H +
+// host scatter of chunk k-1 overlap; the device-resident entry point uses lane 0 only.
+struct Lane {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[8] = {};             // stage timing (profiling)
+  cudaEvent_t done = nullptr;         // results of the chunk are in hostStage
+  int w = 0, h = 0, batchCap = 0;     // shape the arenas are laid out for
+  FrameSetGeom geom;                  // host copy (plane/candidate offsets depend on batchCap)
+  DeviceBuf dGeom;                    // FrameSetGeom on device (octree kernel)
+  DeviceBuf pyrArena, blurArena, candArena, nodeArena, keptArena, counts;
+  DeviceBuf outKps, outDesc, outN;    // device staging for the host-buffer entry points
+  void* hostStage = nullptr;          // pinned: kps | desc | n | overflow flag
+  size_t hostStageBytes = 0;
+  void release();
+};
+
+}  // namespace orbx
+
 struct orbx_extractor {
   orbx_params params;
   orbx::CtorTables tables;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev[8] = {};
+  orbx::Lane lane[2];
   bool profiling = false;
   float stageMs[6] = {};
   long long launches = 0;
 
-  // current shape
-  int w = 0, h = 0, batchCap = 0;
-  orbx::FrameSetGeom geom;            // host copy
-  orbx::DeviceBuf dGeom;              // FrameSetGeom on device
-  orbx::DeviceBuf pyrArena, blurArena, candArena, nodeArena, keptArena, counts, tapArena;
-  orbx::DeviceBuf outKps, outDesc, outN;         // staging for the host-buffer entry points
-  void* hostStage = nullptr;                     // pinned: kps | desc | n | counts
-  size_t hostStageBytes = 0;
+  // resize tables of the current shape (shared by the lanes)
+  int tapW = 0, tapH = 0;
+  orbx::DeviceBuf tapArena;
   orbx::ResizeTables taps[orbx::kMaxLevels];
+
+  // last batch run on lane 0 (introspection / mvImagePyramid read-back)
   int lastCount = 0;                  // frames in the last batch
   const uint8_t* lastLevel0 = nullptr;  // device pointer of level 0 of the last batch
   long long lastL0FrameStride = 0;

@@ -95,6 +95,20 @@ class ORBextractor:
         check(lib().orbx_extract_batch(self._h, arr, cnt, w, h, stride, ptr(kps), ptr(desc), cap, ptr(n)))
         return [(kps[f, :n[f]].copy(), desc[f, :n[f]].copy()) for f in range(cnt)]
 
+    def extract_batch_into(self, frames, kps, desc, n):
+        """orbx_extract_batch on a (B, H, W) uint8 host array (ideally pinned) into caller-owned outputs:
+        kps (B, cap) KP_DTYPE, desc (B, cap, 32) uint8, n (B,) int32. No per-frame Python work: this is the
+        call bench.py times end to end."""
+        if frames.dtype != np.uint8 or frames.ndim != 3 or frames.strides[2] != 1:
+            raise TypeError("frames must be a (B, H, W) uint8 array with contiguous rows")
+        cnt, h, w = frames.shape
+        cap = kps.shape[1]
+        if kps.dtype != KP_DTYPE or kps.shape[0] < cnt or desc.shape[:2] != kps.shape[:2] or n.shape[0] < cnt:
+            raise TypeError("output arrays do not match the batch")
+        base, fs = frames.ctypes.data, frames.strides[0]
+        arr = (C.c_void_p * cnt)(*[base + f * fs for f in range(cnt)])
+        check(lib().orbx_extract_batch(self._h, arr, cnt, w, h, frames.strides[1], ptr(kps), ptr(desc), cap, ptr(n)))
+
     def extract_batch_device(self, d_imgs_ptr, count, width, height, row_stride, frame_stride, d_kps_ptr,
                              d_desc_ptr, cap, d_n_ptr, stream=0):
         """Device-resident batch (raw device pointers, e.g. torch tensors' data_ptr()); asynchronous."""

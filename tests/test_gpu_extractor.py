@@ -166,3 +166,30 @@ def test_extract_matches_reference_golden(pkg):
         assert len(k) == int(e[key + "_n"]), key
         assert np.array_equal(k[:8].view(np.uint8), e[key + "_k8"].view(np.uint8)), key
         assert hashlib.sha256(k.tobytes() + d.tobytes()).hexdigest() == str(e[key + "_sha"]), key
+
+
+def test_chunked_host_batch_equals_single(pkg, oracle):
+    """More frames than one chunk: the two-lane pipeline of orbx_extract_batch must give every frame the
+    result of a single-frame call (and of the oracle for a sample)."""
+    B = 70
+    frames = np.stack([pkg.synth.frame(320, 240, 200 + i) for i in range(B)])
+    ex = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240, max_batch=128)
+    cap = 700
+    kps = np.empty((B, cap), pkg.KP_DTYPE)
+    desc = np.empty((B, cap, 32), np.uint8)
+    n = np.zeros(B, np.int32)
+    ex.extract_batch_into(frames, kps, desc, n)
+    ox = oracle.Extractor(500, 1.2, 8, 20, 7)
+    single = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240)
+    for f in range(B):
+        sk, sd = single(frames[f])
+        assert n[f] == len(sk)
+        assert np.array_equal(kps[f, :n[f]].view(np.uint8), sk.view(np.uint8)), f
+        assert np.array_equal(desc[f, :n[f]], sd), f
+        if f % 16 == 0:
+            ok, od = ox(frames[f])
+            assert np.array_equal(sk.view(np.uint8), ok.view(np.uint8)) and np.array_equal(sd, od)
+    # a second call on the same handle (lanes are reused) and a non-contiguous list of frames
+    res = ex.extract_batch([frames[i] for i in (5, 3, 69)])
+    for (gk, gd), i in zip(res, (5, 3, 69)):
+        assert np.array_equal(gk.view(np.uint8), kps[i, :n[i]].view(np.uint8)) and np.array_equal(gd, desc[i, :n[i]])
