@@ -58,7 +58,28 @@ def build(force=False, verbose=False):
                            [str(o) for o in objs], capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    build_host_mirror(force)
     return LIB
+
+
+def build_host_mirror(force=False):
+    """host/libmirror_test.so: the C++ drop-in ORBextractor (host/ORBextractor.{h,cc}) compiled against the
+    cv shim (OpenCV C++ is not installed here) plus C test entry points; linked to liborbx.so. Used by
+    tests/test_gpu_host_mirror.py only -- a deployment compiles host/ORBextractor.cc against real OpenCV."""
+    host = HERE / "host"
+    out = host / "libmirror_test.so"
+    srcs = [host / "ORBextractor.cc", host / "mirror_capi.cc"]
+    shim = HERE.parent / "oracle" / "ref_shim"
+    deps = srcs + [host / "ORBextractor.h", HERE.parent / "include" / "orbx.h", shim / "opencv2" / "core" / "core.hpp", LIB]
+    if not (force or _stale(out, deps)):
+        return out
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++11", "-fPIC", "-shared", "-Wall", "-Wno-stringop-overflow", "-Wno-array-bounds",
+           f"-I{host}", f"-I{HERE.parent / 'include'}", f"-I{shim}"] + [str(s) for s in srcs] + \
+          ["-o", str(out), f"-L{HERE}", "-lorbx", "-Wl,-rpath,$ORIGIN/.."]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"host mirror build failed:\n{r.stdout}\n{r.stderr}")
+    return out
 
 
 if __name__ == "__main__":

@@ -1,0 +1,151 @@
+// ORB_SLAM2::ORBextractor over liborbx.so -- see ORBextractor.h. Mirrors the observable behaviour of
+// R/src/ORBextractor.cpp:418-502 (ctor tables) and :1120-1188 (operator()).
+#include "ORBextractor.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "orbx.h"
+
+namespace ORB_SLAM2
+{
+
+static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint),
+              "cv::KeyPoint {Point2f pt; float size, angle, response; int octave, class_id} must be 28 bytes");
+
+static void Fail(const char* what)
+{
+    // no CPU fallback and no error channel in the reference's interface: fail loudly
+    std::fprintf(stderr, "ORBextractor (orbx): %s: %s\n", what, orbx_last_error());
+    std::abort();
+}
+
+ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels,
+                           int _iniThFAST, int _minThFAST):
+    nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels),
+    iniThFAST(_iniThFAST), minThFAST(_minThFAST), mpHandle(NULL), mnDevice(0), mnMaxWidth(0), mnMaxHeight(0),
+    mbPyramidReadback(true)
+{
+    if(const char* dev = std::getenv("ORBX_DEVICE"))
+        mnDevice = std::atoi(dev);
+
+    // The tables only depend on the ctor arguments; a 64x64 probe handle computes them with the library's
+    // arithmetic (the reference's own types and operation order, R/src/ORBextractor.cpp:435-500).
+    mvScaleFactor.resize(nlevels);
+    mvInvScaleFactor.resize(nlevels);
+    mvLevelSigma2.resize(nlevels);
+    mvInvLevelSigma2.resize(nlevels);
+    mnFeaturesPerLevel.resize(nlevels);
+    umax.resize(16);
+    mvImagePyramid.resize(nlevels);
+
+    orbx_params p;
+    p.nfeatures = nfeatures; p.scale_factor = _scaleFactor; p.nlevels = nlevels;
+    p.ini_th_fast = iniThFAST; p.min_th_fast = minThFAST; p.device = mnDevice;
+    p.max_width = 4095; p.max_height = 4095; p.max_batch = 1;
+    orbx_extractor* probe = NULL;
+    if(orbx_extractor_create(&p, &probe) != ORBX_OK)
+        Fail("orbx_extractor_create");
+    if(orbx_extractor_tables(probe, &mvScaleFactor[0], &mvInvScaleFactor[0], &mvLevelSigma2[0],
+                             &mvInvLevelSigma2[0], &mnFeaturesPerLevel[0], &umax[0]) != ORBX_OK)
+        Fail("orbx_extractor_tables");
+    mpHandle = probe;   // arenas are allocated on first use, for the size of the first image
+    mnMaxWidth = p.max_width;
+    mnMaxHeight = p.max_height;
+}
+
+ORBextractor::~ORBextractor()
+{
+    orbx_extractor_destroy(mpHandle);
+}
+
+void ORBextractor::SetDevice(int device)
+{
+    if(device == mnDevice)
+        return;
+    mnDevice = device;
+    orbx_extractor_destroy(mpHandle);
+    mpHandle = NULL;
+}
+
+void ORBextractor::EnsureHandle(int width, int height)
+{
+    if(mpHandle && width <= mnMaxWidth && height <= mnMaxHeight)
+        return;
+    orbx_extractor_destroy(mpHandle);
+    mpHandle = NULL;
+    orbx_params p;
+    p.nfeatures = nfeatures; p.scale_factor = (float)scaleFactor; p.nlevels = nlevels;
+    p.ini_th_fast = iniThFAST; p.min_th_fast = minThFAST; p.device = mnDevice;
+    p.max_width = width > 4095 ? width : 4095; p.max_height = height > 4095 ? height : 4095; p.max_batch = 1;
+    if(orbx_extractor_create(&p, &mpHandle) != ORBX_OK)
+        Fail("orbx_extractor_create");
+    mnMaxWidth = p.max_width;
+    mnMaxHeight = p.max_height;
+}
+
+void ORBextractor::operator()( cv::InputArray _image, cv::InputArray _mask, std::vector<cv::KeyPoint>& _keypoints,
+                      cv::OutputArray _descriptors)
+{
+    (void)_mask;                       // ignored by the reference as well
+    if(_image.empty())
+        return;                        // outputs untouched (R/src/ORBextractor.cpp:1123-1124)
+
+    cv::Mat image = _image.getMat();
+    if(image.type() != CV_8UC1)        // the reference only asserts (:1127), compiled out in Release
+    {
+        std::fprintf(stderr, "ORBextractor (orbx): image must be CV_8UC1\n");
+        std::abort();
+    }
+
+    EnsureHandle(image.cols, image.rows);
+
+    // Upper bound on the keypoints of one image: every level's quota plus the octree's overshoot
+    int cap = nfeatures + 64 * nlevels + 512;
+    int n = 0;
+    std::vector<cv::KeyPoint> keys(cap);
+    std::vector<unsigned char> desc((size_t)cap * 32);
+    int rc = orbx_extract(mpHandle, image.data, image.cols, image.rows, (size_t)image.step,
+                          reinterpret_cast<orbx_keypoint*>(&keys[0]), &desc[0], cap, &n);
+    if(rc == ORBX_ERR_CAPACITY && n > cap)
+    {
+        cap = n;
+        keys.resize(cap);
+        desc.resize((size_t)cap * 32);
+        rc = orbx_extract(mpHandle, image.data, image.cols, image.rows, (size_t)image.step,
+                          reinterpret_cast<orbx_keypoint*>(&keys[0]), &desc[0], cap, &n);
+    }
+    if(rc != ORBX_OK)
+        Fail("orbx_extract");
+
+    if(n == 0)
+        _descriptors.release();        // :1145
+    else
+    {
+        _descriptors.create(n, 32, CV_8U);
+        cv::Mat descriptors = _descriptors.getMat();
+        for(int i=0; i<n; i++)
+            std::memcpy(descriptors.ptr(i), &desc[(size_t)i*32], 32);
+    }
+
+    keys.resize(n);
+    _keypoints.swap(keys);             // clear + fill (:1153-1186)
+
+    // mvImagePyramid: level 0 aliases the caller's image (:1223); the others are copied back on demand
+    mvImagePyramid[0] = image;
+    if(mbPyramidReadback)
+    {
+        for(int level=1; level<nlevels; ++level)
+        {
+            int w = 0, h = 0;
+            if(orbx_level_size(mpHandle, level, &w, &h) != ORBX_OK)
+                Fail("orbx_level_size");
+            mvImagePyramid[level].create(h, w, CV_8UC1);
+            if(orbx_get_level(mpHandle, 0, level, mvImagePyramid[level].data, (size_t)mvImagePyramid[level].step) != ORBX_OK)
+                Fail("orbx_get_level");
+        }
+    }
+}
+
+} //namespace ORB_SLAM

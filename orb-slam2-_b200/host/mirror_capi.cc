@@ -1,0 +1,53 @@
+// C entry points around the C++ mirror class, used by tests/test_gpu_host_mirror.py to drive
+// ORB_SLAM2::ORBextractor (host/ORBextractor.h) exactly as Frame.cpp does, without OpenCV installed
+// (the test build compiles the mirror against the cv shim; a real deployment compiles it against OpenCV).
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "ORBextractor.h"
+
+struct mirror_keypoint { float x, y, size, angle, response; int32_t octave, class_id; };
+
+extern "C" {
+
+void* mirror_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh) {
+  return new ORB_SLAM2::ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+}
+void mirror_destroy(void* h) { delete static_cast<ORB_SLAM2::ORBextractor*>(h); }
+
+int mirror_extract(void* h, const uint8_t* img, int w, int hgt, int stride, mirror_keypoint* kps, uint8_t* desc, int cap) {
+  ORB_SLAM2::ORBextractor& ex = *static_cast<ORB_SLAM2::ORBextractor*>(h);
+  cv::Mat image(hgt, w, CV_8UC1, const_cast<uint8_t*>(img), (size_t)stride);
+  std::vector<cv::KeyPoint> keys(3);   // must be cleared by the call
+  cv::Mat descriptors;
+  ex(image, cv::Mat(), keys, descriptors);
+  const int n = (int)keys.size();
+  if (n > cap) return -n;
+  if (n > 0 && (descriptors.rows != n || descriptors.cols != 32)) return -1000000;
+  if (n == 0 && !descriptors.empty()) return -1000001;
+  std::memcpy(kps, keys.data(), (size_t)n * sizeof(mirror_keypoint));
+  for (int i = 0; i < n; i++) std::memcpy(desc + (size_t)i * 32, descriptors.ptr(i), 32);
+  return n;
+}
+
+void mirror_tables(void* h, float* scale, float* invScale, float* sigma2, float* invSigma2) {
+  ORB_SLAM2::ORBextractor& ex = *static_cast<ORB_SLAM2::ORBextractor*>(h);
+  const int n = ex.GetLevels();
+  const std::vector<float> a = ex.GetScaleFactors(), b = ex.GetInverseScaleFactors(), c = ex.GetScaleSigmaSquares(),
+                           d = ex.GetInverseScaleSigmaSquares();
+  for (int i = 0; i < n; i++) { scale[i] = a[i]; invScale[i] = b[i]; sigma2[i] = c[i]; invSigma2[i] = d[i]; }
+}
+
+void mirror_level_size(void* h, int level, int* w, int* hgt) {
+  ORB_SLAM2::ORBextractor& ex = *static_cast<ORB_SLAM2::ORBextractor*>(h);
+  *w = ex.mvImagePyramid[level].cols;
+  *hgt = ex.mvImagePyramid[level].rows;
+}
+void mirror_get_level(void* h, int level, uint8_t* dst, int dstride) {
+  ORB_SLAM2::ORBextractor& ex = *static_cast<ORB_SLAM2::ORBextractor*>(h);
+  const cv::Mat& m = ex.mvImagePyramid[level];
+  for (int r = 0; r < m.rows; r++) std::memcpy(dst + (size_t)r * dstride, m.ptr(r), (size_t)m.cols);
+}
+
+}  // extern "C"
