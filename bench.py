@@ -202,6 +202,64 @@ def run_reference(args):
     return 0
 
 
+HAM_NQ, HAM_NDB = 10_000, 10_000_000   # BASELINE.json config 5
+
+
+def run_hamming(torch, dist, pkg, world, rank, local, args, barrier, max_over_ranks):
+    """Second metric of BASELINE.json ("Hamming match Gpairs/s"), config 5: 10k queries against a 10M-row
+    descriptor database split into `world` contiguous row ranges (strong scaling: the database is fixed),
+    queries replicated, per-rank top-2, all-gather of (idx, d1, d2) over NCCL, merge + ratio test on every
+    rank. Timed on the device, max over ranks; database and queries are resident in HBM."""
+    dev = torch.device("cuda", local)
+    g = torch.Generator(device=dev)
+    g.manual_seed(99)
+    q = torch.randint(0, 256, (HAM_NQ, 32), generator=g, device=dev, dtype=torch.uint8)   # same on every rank
+    lo, hi = pkg.sharding.block_range(HAM_NDB, rank, world)
+    g.manual_seed(1000 + rank)
+    db = torch.randint(0, 256, (hi - lo, 32), generator=g, device=dev, dtype=torch.uint8)
+    plant = torch.arange(0, min(HAM_NQ // 2, hi - lo), device=dev)
+    db[plant * ((hi - lo) // max(len(plant), 1))] = q[plant]   # half of the queries have an exact row in shard `rank`
+    m = pkg.ORBmatcher(0.6, device=local)
+    part = torch.empty((3, HAM_NQ), dtype=torch.int32, device=dev)
+    gathered = torch.empty((world, 3, HAM_NQ), dtype=torch.int32, device=dev)
+    out = torch.empty((3, HAM_NQ), dtype=torch.int32, device=dev)
+    acc = torch.empty(HAM_NQ, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        m.match_bf2_device(q.data_ptr(), HAM_NQ, db.data_ptr(), hi - lo, lo, part[0].data_ptr(), part[1].data_ptr(),
+                           part[2].data_ptr(), stream)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, part)
+            idx, d1, d2 = (gathered[:, k, :].contiguous() for k in range(3))
+        else:
+            idx, d1, d2 = part[0], part[1], part[2]
+        m.merge_device(idx.data_ptr(), d1.data_ptr(), d2.data_ptr(), world, HAM_NQ, 50, out[0].data_ptr(),
+                       out[1].data_ptr(), out[2].data_ptr(), acc.data_ptr(), stream)
+
+    for _ in range(3):
+        step()
+    steps = max(1, min(args.steps, 5))
+    l0 = m.launch_count()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / steps
+    pairs = float(HAM_NQ) * float(HAM_NDB)
+    gp = pairs / (ms * 1e-3) / 1e9
+    return {"metric": "Hamming match Gpairs/s", "value": gp, "unit": "Gpairs/s", "ms_per_step": ms, "steps": steps,
+            "config": {"workload": f"C5: brute-force top-2 + ratio, {HAM_NQ} queries x {HAM_NDB} database rows (32 B), "
+                                   f"database sharded x{world}, all-gather + merge", "scaling": "strong"},
+            "accepted": int(acc.sum().item()), "gpu_launches_per_step": (m.launch_count() - l0) // steps,
+            "compulsory_bytes_per_step": HAM_NDB * 32 + HAM_NQ * 32 * world + HAM_NQ * 13,
+            "hbm_gbs": (HAM_NDB * 32 / world) / (ms * 1e-3) / 1e9,
+            "note": "bound by the integer/popc pipe (8 POPC + 8 XOR per pair, ~2500 popc per database byte), not by HBM"}
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -294,6 +352,8 @@ def run_gpu(args):
                "d2h_bytes_per_step": Be * rows_per_frame * 60 + Be * 4, "frames_per_step": Be,
                "api": "orbx_extract_batch (pinned host frames in, host keypoints+descriptors out; 32-frame chunks on 2 streams)"}
 
+    hamming = None if args.skip_hamming else run_hamming(torch, dist, pkg, world, rank, local, args, barrier, max_over_ranks)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -337,7 +397,7 @@ def run_gpu(args):
                        "l2_policy": "inputs larger than L2 (157 MB of distinct frames per step)",
                        "keypoints_per_frame": nkp / B, "parallelism": f"frame sharding x{world}, no collective"},
             "clocks": clocks, "e2e": e2e_obj, "gpu_launches": launches, "roofline": roof, "stages": stages,
-            "cpu_baseline": cpu}
+            "cpu_baseline": cpu, "hamming": hamming}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -352,6 +412,7 @@ def main():
     ap.add_argument("--impl", default="orbx", choices=["orbx", "reference"])
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs only: skip the CPU baseline leg")
+    ap.add_argument("--skip-hamming", action="store_true", help="profiling runs only: skip the Hamming (config 5) leg")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -8,7 +8,7 @@ from ._capi import KP_DTYPE, LIB_PATH, OrbxError, SIGNATURES, lib  # noqa: F401
 from .extractor import (ORBextractor, blur7_u8, distribute, fast_atan2, resize_u8, sincosf,  # noqa: F401
                         sincosf_sweep)
 from .matcher import ORBmatcher  # noqa: F401
-from . import synth  # noqa: F401
+from . import sharding, synth  # noqa: F401
 
 
 def device_count():
