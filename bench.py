@@ -225,6 +225,7 @@ def run_hamming(torch, dist, pkg, world, rank, local, args, barrier, max_over_ra
     out = torch.empty((3, HAM_NQ), dtype=torch.int32, device=dev)
     acc = torch.empty(HAM_NQ, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
+    assert stream != 0
 
     def step():
         m.match_bf2_device(q.data_ptr(), HAM_NQ, db.data_ptr(), hi - lo, lo, part[0].data_ptr(), part[1].data_ptr(),
@@ -262,6 +263,20 @@ def run_hamming(torch, dist, pkg, world, rank, local, args, barrier, max_over_ra
 
 def run_gpu(args):
     import torch
+    # The C ABI treats a NULL stream as "the handle's own stream"; torch's default stream has handle 0, so all
+    # device work of this process runs on one explicit side stream: the kernels, NCCL and the timing events
+    # are then ordered on the same stream.
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device; liborbx has no CPU fallback")
+    torch.cuda.set_device(local)
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        return _run_gpu(args, torch)
+
+
+def _run_gpu(args, torch):
     import torch.distributed as dist
     import orbslam2_b200 as pkg
 
@@ -296,6 +311,7 @@ def run_gpu(args):
     d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device="cuda")
     d_n = torch.zeros(B, dtype=torch.int32, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
+    assert stream != 0
 
     def step():
         ex.extract_batch_device(frames.data_ptr(), B, W, H, W, W * H, d_kps.data_ptr(), d_desc.data_ptr(), cap,

@@ -28,6 +28,78 @@ static inline int descriptor_distance(const uint8_t* a, const uint8_t* b) {
   return dist;
 }
 
+
+// ---- Frame grid: R/include/Frame.h:37-38,181; R/src/Frame.cpp AssignFeaturesToGrid :244-260,
+//      PosInGrid :442-452, GetFeaturesInArea :387-440 -------------------------------------------
+constexpr int kGridCols = 64, kGridRows = 48;
+
+struct Grid {
+  std::vector<orb_oracle_keypoint> kps;  // mvKeysUn
+  float minX, minY, invW, invH;          // mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv
+  std::vector<int> cells[kGridCols][kGridRows];
+
+  void build(const orb_oracle_keypoint* k, int n, float minX_, float maxX_, float minY_, float maxY_) {
+    kps.assign(k, k + n);
+    minX = minX_; minY = minY_;
+    invW = static_cast<float>(kGridCols) / (maxX_ - minX_);   // Frame.cpp:168-169
+    invH = static_cast<float>(kGridRows) / (maxY_ - minY_);
+    for (int i = 0; i < n; i++) {
+      const int px = (int)std::round((kps[i].x - minX) * invW);  // :444-445 (round half away from zero)
+      const int py = (int)std::round((kps[i].y - minY) * invH);
+      if (px < 0 || px >= kGridCols || py < 0 || py >= kGridRows) continue;
+      cells[px][py].push_back(i);
+    }
+  }
+
+  void query(float x, float y, float r, int minLevel, int maxLevel, std::vector<int>& out) const {
+    out.clear();
+    const int nMinCellX = std::max(0, (int)std::floor((x - minX - r) * invW));
+    if (nMinCellX >= kGridCols) return;
+    const int nMaxCellX = std::min(kGridCols - 1, (int)std::ceil((x - minX + r) * invW));
+    if (nMaxCellX < 0) return;
+    const int nMinCellY = std::max(0, (int)std::floor((y - minY - r) * invH));
+    if (nMinCellY >= kGridRows) return;
+    const int nMaxCellY = std::min(kGridRows - 1, (int)std::ceil((y - minY + r) * invH));
+    if (nMaxCellY < 0) return;
+    const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+      for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+        for (int idx : cells[ix][iy]) {
+          const orb_oracle_keypoint& kp = kps[idx];
+          if (bCheckLevels) {
+            if (kp.octave < minLevel) continue;
+            if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+          }
+          const float distx = kp.x - x, disty = kp.y - y;
+          if (std::fabs(distx) < r && std::fabs(disty) < r) out.push_back(idx);
+        }
+  }
+};
+
+// R/src/ORBmatcher.cpp:1854-1895
+static void compute_three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  for (int i = 0; i < L; i++) {
+    const int s = (int)histo[i].size();
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
+  }
+  if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+  else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+constexpr int kHistoLength = 30, kThLow = 50, kThHigh = 100;  // R/src/ORBmatcher.cpp:37-39
+
+static inline int rot_bin(float a1, float a2) {  // :569-575, :1684-1690
+  const float factor = kHistoLength / 360.0f;
+  float rot = a1 - a2;
+  if (rot < 0.0) rot += 360.0f;
+  int bin = (int)std::round(rot * factor);
+  if (bin == kHistoLength) bin = 0;
+  return bin;
+}
+
 }  // namespace orb_oracle
 
 using namespace orb_oracle;
@@ -60,3 +132,271 @@ void orb_oracle_match_bf2(const uint8_t* q, int nq, const uint8_t* db, int64_t n
 }
 
 }  // extern "C"
+
+// ---- windowed searches ----------------------------------------------------------------------------
+struct orb_oracle_grid { Grid g; };
+
+extern "C" {
+
+orb_oracle_grid* orb_oracle_grid_create(const orb_oracle_keypoint* kps_un, int n, float min_x, float max_x,
+                                        float min_y, float max_y) {
+  orb_oracle_grid* h = new orb_oracle_grid();
+  h->g.build(kps_un, n, min_x, max_x, min_y, max_y);
+  return h;
+}
+void orb_oracle_grid_destroy(orb_oracle_grid* h) { delete h; }
+int orb_oracle_grid_query(orb_oracle_grid* h, float x, float y, float r, int min_level, int max_level,
+                          int32_t* out_idx, int cap) {
+  std::vector<int> v;
+  h->g.query(x, y, r, min_level, max_level, v);
+  for (int i = 0; i < (int)v.size() && i < cap; i++) out_idx[i] = v[i];
+  return (int)v.size();
+}
+
+// R/src/ORBmatcher.cpp:499-617
+int orb_oracle_search_for_initialization(const orb_oracle_keypoint* kps1, const uint8_t* desc1, int n1,
+                                         const orb_oracle_keypoint* kps2, const uint8_t* desc2, int n2,
+                                         float min_x, float max_x, float min_y, float max_y,
+                                         float* prev_matched_xy, int32_t* matches12, int window, float nnratio,
+                                         int check_orientation) {
+  Grid g2;
+  g2.build(kps2, n2, min_x, max_x, min_y, max_y);
+  int nmatches = 0;
+  for (int i = 0; i < n1; i++) matches12[i] = -1;
+  std::vector<int> rotHist[kHistoLength];
+  std::vector<int> vMatchedDistance(n2, INT_MAX), vnMatches21(n2, -1), vIndices2;
+  for (int i1 = 0; i1 < n1; i1++) {
+    const int level1 = kps1[i1].octave;
+    if (level1 > 0) continue;
+    g2.query(prev_matched_xy[2 * i1], prev_matched_xy[2 * i1 + 1], (float)window, level1, level1, vIndices2);
+    if (vIndices2.empty()) continue;
+    const uint8_t* d1 = desc1 + (size_t)i1 * 32;
+    int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+    for (int i2 : vIndices2) {
+      const int dist = descriptor_distance(d1, desc2 + (size_t)i2 * 32);
+      if (vMatchedDistance[i2] <= dist) continue;
+      if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+      else if (dist < bestDist2) { bestDist2 = dist; }
+    }
+    if (bestDist <= kThLow) {
+      if (bestDist < (float)bestDist2 * nnratio) {
+        if (vnMatches21[bestIdx2] >= 0) { matches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+        matches12[i1] = bestIdx2;
+        vnMatches21[bestIdx2] = i1;
+        vMatchedDistance[bestIdx2] = bestDist;
+        nmatches++;
+        if (check_orientation) rotHist[rot_bin(kps1[i1].angle, kps2[bestIdx2].angle)].push_back(i1);
+      }
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    compute_three_maxima(rotHist, kHistoLength, ind1, ind2, ind3);
+    for (int i = 0; i < kHistoLength; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx1 : rotHist[i])
+        if (matches12[idx1] >= 0) { matches12[idx1] = -1; nmatches--; }
+    }
+  }
+  for (int i1 = 0; i1 < n1; i1++)
+    if (matches12[i1] >= 0) {
+      prev_matched_xy[2 * i1] = kps2[matches12[i1]].x;
+      prev_matched_xy[2 * i1 + 1] = kps2[matches12[i1]].y;
+    }
+  return nmatches;
+}
+
+// R/src/ORBmatcher.cpp:63-163. The map-point side is given as arrays: projection (u,v), search radius
+// r = RadiusByViewingCos(viewCos)*th (:85-89), predicted level, projected right coordinate, descriptor.
+// has_mp[idx] != 0 <=> F.mvpMapPoints[idx] && Observations()>0 (:118-121); mp_match[iMP] = keypoint or -1.
+int orb_oracle_search_by_projection_mp(const orb_oracle_keypoint* kps_un, const uint8_t* desc, int n,
+                                       const float* uright, const uint8_t* has_mp, float min_x, float max_x,
+                                       float min_y, float max_y, const float* mp_uv, const float* mp_r,
+                                       const int32_t* mp_level, const float* mp_ur, const uint8_t* mp_desc, int nmp,
+                                       const float* scale_factors, float nnratio, int32_t* mp_match) {
+  Grid g;
+  g.build(kps_un, n, min_x, max_x, min_y, max_y);
+  std::vector<uint8_t> owned(has_mp, has_mp + n);
+  std::vector<int> vIndices;
+  int nmatches = 0;
+  for (int iMP = 0; iMP < nmp; iMP++) {
+    mp_match[iMP] = -1;
+    const int nPredictedLevel = mp_level[iMP];
+    const float r = mp_r[iMP];
+    g.query(mp_uv[2 * iMP], mp_uv[2 * iMP + 1], r * scale_factors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel,
+            vIndices);
+    if (vIndices.empty()) continue;
+    const uint8_t* dMP = mp_desc + (size_t)iMP * 32;
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+    for (int idx : vIndices) {
+      if (owned[idx]) continue;
+      if (uright && uright[idx] > 0) {
+        const float er = std::fabs(mp_ur[iMP] - uright[idx]);
+        if (er > r * scale_factors[nPredictedLevel]) continue;
+      }
+      const int dist = descriptor_distance(dMP, desc + (size_t)idx * 32);
+      if (dist < bestDist) {
+        bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = kps_un[idx].octave; bestIdx = idx;
+      } else if (dist < bestDist2) {
+        bestLevel2 = kps_un[idx].octave; bestDist2 = dist;
+      }
+    }
+    if (bestDist <= kThHigh) {
+      if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+      mp_match[iMP] = bestIdx;
+      owned[bestIdx] = 1;  // F.mvpMapPoints[bestIdx]=pMP: later map points skip it (a tracked point has observations)
+      nmatches++;
+    }
+  }
+  return nmatches;
+}
+
+// R/src/ORBmatcher.cpp:1564-1718 after the projection prologue (:1600-1634): per last-frame map point the
+// projection (u,v), radius th*scale[octave], level window, projected right coordinate ur = u - mbf*invzc
+// (:1655), the last frame's keypoint angle and descriptor. cur_match[i2] = query index or -1.
+int orb_oracle_search_by_projection_frame(const orb_oracle_keypoint* kps_un, const uint8_t* desc, int n,
+                                          const float* uright, const uint8_t* has_mp, float min_x, float max_x,
+                                          float min_y, float max_y, const float* q_uv, const float* q_r,
+                                          const int32_t* q_min_level, const int32_t* q_max_level, const float* q_ur,
+                                          const float* q_angle, const uint8_t* q_desc, int nq, int th_dist,
+                                          int check_orientation, int32_t* cur_match) {
+  Grid g;
+  g.build(kps_un, n, min_x, max_x, min_y, max_y);
+  std::vector<uint8_t> owned(has_mp, has_mp + n);
+  for (int i = 0; i < n; i++) cur_match[i] = -1;
+  std::vector<int> rotHist[kHistoLength], vIndices2;
+  int nmatches = 0;
+  for (int i = 0; i < nq; i++) {
+    const float radius = q_r[i];
+    g.query(q_uv[2 * i], q_uv[2 * i + 1], radius, q_min_level[i], q_max_level[i], vIndices2);
+    if (vIndices2.empty()) continue;
+    const uint8_t* dMP = q_desc + (size_t)i * 32;
+    int bestDist = 256, bestIdx2 = -1;
+    for (int i2 : vIndices2) {
+      if (owned[i2]) continue;
+      if (uright && uright[i2] > 0) {
+        const float er = std::fabs(q_ur[i] - uright[i2]);
+        if (er > radius) continue;
+      }
+      const int dist = descriptor_distance(dMP, desc + (size_t)i2 * 32);
+      if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+    }
+    if (bestDist <= th_dist) {
+      cur_match[bestIdx2] = i;
+      owned[bestIdx2] = 1;
+      nmatches++;
+      if (check_orientation) rotHist[rot_bin(q_angle[i], kps_un[bestIdx2].angle)].push_back(bestIdx2);
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    compute_three_maxima(rotHist, kHistoLength, ind1, ind2, ind3);
+    for (int i = 0; i < kHistoLength; i++)
+      if (i != ind1 && i != ind2 && i != ind3)
+        for (int idx : rotHist[i]) { cur_match[idx] = -1; nmatches--; }
+  }
+  return nmatches;
+}
+
+}  // extern "C"
+
+// ---- Frame::ComputeStereoMatches (R/src/Frame.cpp:551-770) ----------------------------------------
+extern "C" int orb_oracle_stereo_matches(const orb_oracle_keypoint* kps_l, const uint8_t* desc_l, int nl,
+                                         const orb_oracle_keypoint* kps_r, const uint8_t* desc_r, int nr,
+                                         const uint8_t* const* pyr_l, const uint8_t* const* pyr_r,
+                                         const int32_t* lvl_w, const int32_t* lvl_h, const int32_t* lvl_stride,
+                                         int nlevels, const float* scale_factors, const float* inv_scale_factors,
+                                         float mbf, float mb, float* u_right, float* depth) {
+  (void)nlevels;
+  for (int i = 0; i < nl; i++) { u_right[i] = -1.0f; depth[i] = -1.0f; }
+  const int thOrbDist = (kThHigh + kThLow) / 2;
+  const int nRows = lvl_h[0];
+  std::vector<std::vector<int>> vRowIndices(nRows);
+  for (int iR = 0; iR < nr; iR++) {
+    const float kpY = kps_r[iR].y;
+    const float r = 2.0f * scale_factors[kps_r[iR].octave];
+    const int maxr = (int)std::ceil(kpY + r);
+    const int minr = (int)std::floor(kpY - r);
+    for (int yi = minr; yi <= maxr; yi++)
+      if (yi >= 0 && yi < nRows) vRowIndices[yi].push_back(iR);  // (the reference indexes unchecked)
+  }
+  const float minZ = mb, minD = 0, maxD = mbf / minZ;
+  std::vector<std::pair<int, int>> vDistIdx;
+  for (int iL = 0; iL < nl; iL++) {
+    const orb_oracle_keypoint& kpL = kps_l[iL];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const std::vector<int>& vCandidates = vRowIndices[(size_t)vL];
+    if (vCandidates.empty()) continue;
+    const float minU = uL - maxD, maxU = uL - minD;
+    if (maxU < 0) continue;
+    int bestDist = kThHigh;
+    int bestIdxR = 0;
+    const uint8_t* dL = desc_l + (size_t)iL * 32;
+    for (int iR : vCandidates) {
+      const orb_oracle_keypoint& kpR = kps_r[iR];
+      if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+      const float uR = kpR.x;
+      if (uR >= minU && uR <= maxU) {
+        const int dist = descriptor_distance(dL, desc_r + (size_t)iR * 32);
+        if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+      }
+    }
+    if (bestDist < thOrbDist) {
+      const float uR0 = kps_r[bestIdxR].x;
+      const float scaleFactor = inv_scale_factors[kpL.octave];
+      const float scaleduL = std::round(kpL.x * scaleFactor);
+      const float scaledvL = std::round(kpL.y * scaleFactor);
+      const float scaleduR0 = std::round(uR0 * scaleFactor);
+      const int w = 5, L = 5;
+      const int lv = kpL.octave;
+      const uint8_t* IL = pyr_l[lv];
+      const uint8_t* IR = pyr_r[lv];
+      const int sL = lvl_stride[lv];
+      const int y0 = (int)(scaledvL - w), xL0 = (int)(scaleduL - w);
+      const float iniu = scaleduR0 + L - w, endu = scaleduR0 + L + w + 1;
+      if (iniu < 0 || endu >= lvl_w[lv]) continue;
+      int bestSad = INT_MAX, bestincR = 0;
+      float vDists[2 * 5 + 1];
+      const float cL = (float)IL[(size_t)(y0 + w) * sL + xL0 + w];
+      for (int incR = -L; incR <= +L; incR++) {
+        const int xR0 = (int)(scaleduR0 + incR - w);
+        const float cR = (float)IR[(size_t)(y0 + w) * sL + xR0 + w];
+        double acc = 0;  // cv::norm(NORM_L1) of exact small integers: exact in any accumulation order
+        for (int yy = 0; yy < 2 * w + 1; yy++)
+          for (int xx = 0; xx < 2 * w + 1; xx++) {
+            const float a = (float)IL[(size_t)(y0 + yy) * sL + xL0 + xx] - cL;
+            const float b = (float)IR[(size_t)(y0 + yy) * sL + xR0 + xx] - cR;
+            acc += std::fabs(a - b);
+          }
+        const float dist = (float)acc;
+        if (dist < bestSad) { bestSad = (int)dist; bestincR = incR; }
+        vDists[L + incR] = dist;
+      }
+      if (bestincR == -L || bestincR == L) continue;
+      const float dist1 = vDists[L + bestincR - 1], dist2 = vDists[L + bestincR], dist3 = vDists[L + bestincR + 1];
+      const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+      if (deltaR < -1 || deltaR > 1) continue;
+      float bestuR = scale_factors[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+      float disparity = (uL - bestuR);
+      if (disparity >= minD && disparity < maxD) {
+        if (disparity <= 0) { disparity = 0.01f; bestuR = uL - 0.01f; }
+        depth[iL] = mbf / disparity;
+        u_right[iL] = bestuR;
+        vDistIdx.push_back(std::make_pair(bestSad, iL));
+      }
+    }
+  }
+  if (vDistIdx.empty()) return 0;  // (the reference reads vDistIdx[0] unconditionally)
+  std::sort(vDistIdx.begin(), vDistIdx.end());
+  const float median = (float)vDistIdx[vDistIdx.size() / 2].first;
+  const float thDist = 1.5f * 1.4f * median;
+  int kept = (int)vDistIdx.size();
+  for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+    if (vDistIdx[i].first < thDist) break;
+    u_right[vDistIdx[i].second] = -1;
+    depth[vDistIdx[i].second] = -1;
+    kept--;
+  }
+  return kept;
+}
