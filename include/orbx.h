@@ -154,6 +154,28 @@ int orbx_match_merge_device(orbx_matcher* h, const int32_t* d_idx, const int32_t
                             int32_t nshards, int32_t nq, float ratio, int32_t th, int32_t* d_out_idx,
                             int32_t* d_out_d1, int32_t* d_out_d2, uint8_t* d_accepted, void* stream);
 
+/* Windowed search on the Frame grid: the data-parallel half of SearchForInitialization / SearchByProjection
+ * (R/src/ORBmatcher.cpp:499-617, :63-163, :1564-1718). The target frame is (kps_un, desc, n) with the image
+ * bounds mnMinX..mnMaxY that define its 64x48 grid (R/src/Frame.cpp:168-169, :244-260). For query i the
+ * candidates are exactly Frame::GetFeaturesInArea(q_xy[2i], q_xy[2i+1], q_r[i], q_min_level[i],
+ * q_max_level[i]) (R/src/Frame.cpp:387-440) in the reference's order: cand_idx[cand_off[i] .. cand_off[i+1])
+ * with cand_dist = DescriptorDistance(q_desc[i], desc[cand_idx]). Host buffers, synchronous.
+ * ORBX_ERR_CAPACITY when cand_cap is too small (*n_cand = needed, cand_off is valid). The order-dependent
+ * resolve runs on the host (orb-slam2-_b200/host/orbx_search.h). */
+int orbx_match_window(orbx_matcher* h, const orbx_keypoint* kps_un, const uint8_t* desc, int32_t n, float min_x,
+                      float max_x, float min_y, float max_y, const float* q_xy, const float* q_r,
+                      const int32_t* q_min_level, const int32_t* q_max_level, const uint8_t* q_desc, int32_t nq,
+                      int32_t* cand_off, int32_t* cand_idx, int32_t* cand_dist, int32_t cand_cap, int32_t* n_cand);
+
+/* Frame::ComputeStereoMatches (R/src/Frame.cpp:551-770) for the last frames extracted by `left` and `right`
+ * (single-chunk calls; their pyramids are still on the device): row-band Hamming match, 11x11 SAD refinement
+ * over 11 offsets, sub-pixel parabola, depth = mbf/disparity, median-SAD filter. kps/desc are the two
+ * extractors' outputs (host). u_right/depth: nl floats, -1 where unmatched; *n_matched = surviving matches. */
+int orbx_stereo_match(orbx_matcher* h, orbx_extractor* left, orbx_extractor* right, int32_t frame_left,
+                      int32_t frame_right, const orbx_keypoint* kps_l, const uint8_t* desc_l, int32_t nl,
+                      const orbx_keypoint* kps_r, const uint8_t* desc_r, int32_t nr, float mbf, float mb,
+                      float* u_right, float* depth, int32_t* n_matched);
+
 #ifdef __cplusplus
 }
 #endif

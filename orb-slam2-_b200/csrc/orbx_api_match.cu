@@ -1,5 +1,6 @@
 // C ABI of liborbx.so, matcher half (include/orbx.h): DescriptorDistance and brute-force top-2.
 #include <algorithm>
+#include <initializer_list>
 #include <new>
 
 #include "orbx_host.h"
@@ -11,6 +12,25 @@ void launch_bf2(const uint8_t* q, int nq, const uint8_t* db, long long ndb, int 
 void launch_merge(const int* pIdx, const int* pD1, const int* pD2, int nshards, int nq, float ratio, int th,
                   int* oIdx, int* oD1, int* oD2, uint8_t* accepted, cudaStream_t s);
 void launch_distance(const uint8_t* a, const uint8_t* b, int* d, long long n, cudaStream_t s);
+void launch_grid_build(const orbx_keypoint* kps, int n, float minX, float maxX, float minY, float maxY, int* cellStart,
+                       int* items, cudaStream_t s);
+void launch_window(bool fill, const orbx_keypoint* kps, const uint8_t* desc, float minX, float maxX, float minY, float maxY,
+                   const int* cellStart, const int* items, const float* qxy, const float* qr, const int* qMinLevel,
+                   const int* qMaxLevel, const uint8_t* qdesc, int nq, int* count, const int* off, int* candIdx,
+                   int* candDist, cudaStream_t s);
+void launch_scan(const int* count, int n, int* off, cudaStream_t s);
+int grid_cells();
+struct StereoLevels {
+  const uint8_t* left[kMaxLevels];
+  const uint8_t* right[kMaxLevels];
+  int pitchL[kMaxLevels], pitchR[kMaxLevels];
+  int width[kMaxLevels];
+  float scale[kMaxLevels], invScale[kMaxLevels];
+  int rows0;
+};
+void launch_stereo(const StereoLevels& lv, const orbx_keypoint* kpL, const uint8_t* descL, int nl,
+                   const orbx_keypoint* kpR, const uint8_t* descR, int nr, float mbf, float mb, float* uRight,
+                   float* depth, int* sad, int* nKept, cudaStream_t s);
 }  // namespace orbx
 
 using namespace orbx;
@@ -22,6 +42,7 @@ struct orbx_matcher {
   long long launches = 0;
   DeviceBuf partial;           // [3][chunks][nq] ints
   DeviceBuf dQ, dDb, dOut;     // staging for the host-buffer entry points
+  DeviceBuf dWin;              // windowed search / stereo: one arena carved per call
 };
 
 namespace {
@@ -59,7 +80,7 @@ void orbx_matcher_destroy(orbx_matcher* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
-  h->partial.release(); h->dQ.release(); h->dDb.release(); h->dOut.release();
+  h->partial.release(); h->dQ.release(); h->dDb.release(); h->dOut.release(); h->dWin.release();
   delete h;
 }
 
@@ -145,6 +166,176 @@ int orbx_match_bf2(orbx_matcher* h, const uint8_t* q, int32_t nq, const uint8_t*
   ORBX_CUDA_TRY(cudaMemcpyAsync(d1, tD1, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
   ORBX_CUDA_TRY(cudaMemcpyAsync(d2, tD2, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
   if (accepted) ORBX_CUDA_TRY(cudaMemcpyAsync(accepted, dAcc, (size_t)nq, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  return ORBX_OK;
+}
+
+}  // extern "C"
+
+namespace {
+// bump allocation inside h->dWin (256-byte aligned pieces)
+struct Carver {
+  uint8_t* base; size_t off = 0;
+  template <class T> T* take(size_t count) {
+    T* p = reinterpret_cast<T*>(base + off);
+    off += (count * sizeof(T) + 255) & ~size_t(255);
+    return p;
+  }
+};
+size_t carve_size(std::initializer_list<size_t> bytes) {
+  size_t t = 0;
+  for (size_t b : bytes) t += (b + 255) & ~size_t(255);
+  return t + 256;
+}
+}  // namespace
+
+extern "C" {
+
+int orbx_match_window(orbx_matcher* h, const orbx_keypoint* kps_un, const uint8_t* desc, int32_t n, float min_x,
+                      float max_x, float min_y, float max_y, const float* q_xy, const float* q_r,
+                      const int32_t* q_min_level, const int32_t* q_max_level, const uint8_t* q_desc, int32_t nq,
+                      int32_t* cand_off, int32_t* cand_idx, int32_t* cand_dist, int32_t cand_cap, int32_t* n_cand) {
+  int rc = set_dev(h);
+  if (rc) return rc;
+  if (!kps_un || !desc || !q_xy || !q_r || !q_min_level || !q_max_level || !q_desc || !cand_off || !n_cand || n < 0 ||
+      nq < 0 || cand_cap < 0 || !(max_x > min_x) || !(max_y > min_y)) {
+    set_error("bad arguments");
+    return ORBX_ERR_ARG;
+  }
+  *n_cand = 0;
+  if (nq == 0) { cand_off[0] = 0; return ORBX_OK; }
+  const int cells = grid_cells();
+  const size_t N = (size_t)std::max(n, 1), Q = (size_t)nq;
+  if ((rc = h->dWin.ensure(carve_size({N * sizeof(orbx_keypoint), N * 32, (size_t)(cells + 1) * 4, N * 4, Q * 8, Q * 4, Q * 4,
+                                       Q * 4, Q * 32, Q * 4, (Q + 1) * 4, (size_t)cand_cap * 4, (size_t)cand_cap * 4}))))
+    return rc;
+  Carver c{static_cast<uint8_t*>(h->dWin.p)};
+  orbx_keypoint* dK = c.take<orbx_keypoint>(N);
+  uint8_t* dD = c.take<uint8_t>(N * 32);
+  int* dCell = c.take<int>(cells + 1);
+  int* dItems = c.take<int>(N);
+  float* dQxy = c.take<float>(Q * 2);
+  float* dQr = c.take<float>(Q);
+  int* dQmin = c.take<int>(Q);
+  int* dQmax = c.take<int>(Q);
+  uint8_t* dQd = c.take<uint8_t>(Q * 32);
+  int* dCount = c.take<int>(Q);
+  int* dOff = c.take<int>(Q + 1);
+  int* dCi = c.take<int>(std::max(cand_cap, 1));
+  int* dCd = c.take<int>(std::max(cand_cap, 1));
+  cudaStream_t s = h->stream;
+  if (n > 0) {
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dK, kps_un, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dD, desc, (size_t)n * 32, cudaMemcpyHostToDevice, s));
+  }
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dQxy, q_xy, Q * 8, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dQr, q_r, Q * 4, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dQmin, q_min_level, Q * 4, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dQmax, q_max_level, Q * 4, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dQd, q_desc, Q * 32, cudaMemcpyHostToDevice, s));
+  launch_grid_build(dK, n, min_x, max_x, min_y, max_y, dCell, dItems, s);
+  launch_window(false, dK, dD, min_x, max_x, min_y, max_y, dCell, dItems, dQxy, dQr, dQmin, dQmax, dQd, nq, dCount, dOff,
+                dCi, dCd, s);
+  launch_scan(dCount, nq, dOff, s);
+  h->launches += 3;
+  ORBX_CUDA_TRY(cudaGetLastError());
+  ORBX_CUDA_TRY(cudaMemcpyAsync(cand_off, dOff, (Q + 1) * 4, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  const int total = cand_off[nq];
+  *n_cand = total;
+  if (total > cand_cap || (total > 0 && (!cand_idx || !cand_dist))) {
+    set_error("candidate capacity %d < %d", cand_cap, total);
+    return ORBX_ERR_CAPACITY;
+  }
+  if (total > 0) {
+    launch_window(true, dK, dD, min_x, max_x, min_y, max_y, dCell, dItems, dQxy, dQr, dQmin, dQmax, dQd, nq, dCount, dOff,
+                  dCi, dCd, s);
+    h->launches++;
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(cand_idx, dCi, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(cand_dist, dCd, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  }
+  return ORBX_OK;
+}
+
+int orbx_stereo_match(orbx_matcher* h, orbx_extractor* left, orbx_extractor* right, int32_t frame_left,
+                      int32_t frame_right, const orbx_keypoint* kps_l, const uint8_t* desc_l, int32_t nl,
+                      const orbx_keypoint* kps_r, const uint8_t* desc_r, int32_t nr, float mbf, float mb,
+                      float* u_right, float* depth, int32_t* n_matched) {
+  int rc = set_dev(h);
+  if (rc) return rc;
+  if (!left || !right || !u_right || !depth || !n_matched || nl < 0 || nr < 0 || (nl > 0 && (!kps_l || !desc_l)) ||
+      (nr > 0 && (!kps_r || !desc_r))) {
+    set_error("bad arguments");
+    return ORBX_ERR_ARG;
+  }
+  if (nr > 65535) { set_error("more than 65535 right keypoints"); return ORBX_ERR_ARG; }
+  if (left->params.device != h->device || right->params.device != h->device) {
+    set_error("extractors and matcher live on different devices");
+    return ORBX_ERR_ARG;
+  }
+  const orbx::Lane& LL = left->lane[0];
+  const orbx::Lane& LR = right->lane[0];
+  if (!left->haveResult || !right->haveResult || frame_left < 0 || frame_left >= left->lastCount || frame_right < 0 ||
+      frame_right >= right->lastCount) {
+    set_error("the extractors hold no (single-chunk) result for frames %d / %d", frame_left, frame_right);
+    return ORBX_ERR_STATE;
+  }
+  const int nlv = LL.geom.nlevels;
+  if (LR.geom.nlevels != nlv || LL.w != LR.w || LL.h != LR.h) { set_error("left/right shapes differ"); return ORBX_ERR_ARG; }
+  StereoLevels lv;
+  for (int l = 0; l < kMaxLevels; l++) { lv.left[l] = lv.right[l] = nullptr; lv.pitchL[l] = lv.pitchR[l] = lv.width[l] = 0; lv.scale[l] = lv.invScale[l] = 1.f; }
+  for (int l = 0; l < nlv; l++) {
+    const LevelGeom& G = LL.geom.lv[l];
+    if (l == 0) {
+      lv.left[0] = left->lastLevel0 + (long long)frame_left * left->lastL0FrameStride;
+      lv.right[0] = right->lastLevel0 + (long long)frame_right * right->lastL0FrameStride;
+      lv.pitchL[0] = left->lastL0Pitch; lv.pitchR[0] = right->lastL0Pitch;
+    } else {
+      lv.left[l] = static_cast<const uint8_t*>(LL.pyrArena.p) + G.planeOff + (long long)frame_left * G.planeBytes;
+      lv.right[l] = static_cast<const uint8_t*>(LR.pyrArena.p) + LR.geom.lv[l].planeOff + (long long)frame_right * LR.geom.lv[l].planeBytes;
+      lv.pitchL[l] = G.pitch; lv.pitchR[l] = LR.geom.lv[l].pitch;
+    }
+    lv.width[l] = G.w;
+    lv.scale[l] = left->tables.scale[l];
+    lv.invScale[l] = left->tables.invScale[l];
+  }
+  lv.rows0 = LL.geom.lv[0].h;
+  const size_t NL = (size_t)std::max(nl, 1), NR = (size_t)std::max(nr, 1);
+  if ((rc = h->dWin.ensure(carve_size({NL * sizeof(orbx_keypoint), NL * 32, NR * sizeof(orbx_keypoint), NR * 32, NL * 4, NL * 4,
+                                       NL * 4, 4}))))
+    return rc;
+  Carver c{static_cast<uint8_t*>(h->dWin.p)};
+  orbx_keypoint* dKL = c.take<orbx_keypoint>(NL);
+  uint8_t* dDL = c.take<uint8_t>(NL * 32);
+  orbx_keypoint* dKR = c.take<orbx_keypoint>(NR);
+  uint8_t* dDR = c.take<uint8_t>(NR * 32);
+  float* dU = c.take<float>(NL);
+  float* dZ = c.take<float>(NL);
+  int* dSad = c.take<int>(NL);
+  int* dKept = c.take<int>(1);
+  // the extractors' streams produced the pyramids; their host-buffer calls are synchronous, the device-resident
+  // entry point is not: wait for both before reading
+  ORBX_CUDA_TRY(cudaStreamSynchronize(LL.stream));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(LR.stream));
+  cudaStream_t s = h->stream;
+  if (nl > 0) {
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dKL, kps_l, (size_t)nl * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dDL, desc_l, (size_t)nl * 32, cudaMemcpyHostToDevice, s));
+  }
+  if (nr > 0) {
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dKR, kps_r, (size_t)nr * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dDR, desc_r, (size_t)nr * 32, cudaMemcpyHostToDevice, s));
+  }
+  launch_stereo(lv, dKL, dDL, nl, dKR, dDR, nr, mbf, mb, dU, dZ, dSad, dKept, s);
+  h->launches += 2;
+  ORBX_CUDA_TRY(cudaGetLastError());
+  if (nl > 0) {
+    ORBX_CUDA_TRY(cudaMemcpyAsync(u_right, dU, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(depth, dZ, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+  }
+  ORBX_CUDA_TRY(cudaMemcpyAsync(n_matched, dKept, 4, cudaMemcpyDeviceToHost, s));
   ORBX_CUDA_TRY(cudaStreamSynchronize(s));
   return ORBX_OK;
 }

@@ -51,3 +51,40 @@ void mirror_get_level(void* h, int level, uint8_t* dst, int dstride) {
 }
 
 }  // extern "C"
+
+// ---- windowed searches (host/orbx_search.h) ---------------------------------------------------
+#include "orbx_search.h"
+
+extern "C" {
+
+static orbx_host::FrameView view(const orbx_keypoint* k, const unsigned char* d, int n, const float* b, const float* ur) {
+  orbx_host::FrameView v;
+  v.keysUn = k; v.descriptors = d; v.N = n; v.minX = b[0]; v.maxX = b[1]; v.minY = b[2]; v.maxY = b[3]; v.uRight = ur;
+  return v;
+}
+
+int mirror_search_for_initialization(orbx_matcher* m, const orbx_keypoint* k1, const unsigned char* d1, int n1,
+                                     const orbx_keypoint* k2, const unsigned char* d2, int n2, const float* bounds,
+                                     float* prevMatched, int* matches12, int window, float nnratio, int checkOri) {
+  return orbx_host::SearchForInitialization(m, view(k1, d1, n1, bounds, 0), view(k2, d2, n2, bounds, 0), prevMatched,
+                                            matches12, window, nnratio, checkOri != 0);
+}
+
+int mirror_search_by_projection_mp(orbx_matcher* m, const orbx_keypoint* k, const unsigned char* d, int n,
+                                   const float* uright, unsigned char* hasMP, const float* bounds, const float* mpUV,
+                                   const float* mpR, const int* mpLevel, const float* mpUR, const unsigned char* mpDesc,
+                                   int nMP, const float* scaleFactors, float nnratio, int* mpMatch) {
+  return orbx_host::SearchByProjection(m, view(k, d, n, bounds, uright), hasMP, mpUV, mpR, mpLevel, mpUR, mpDesc, nMP,
+                                       scaleFactors, nnratio, mpMatch);
+}
+
+int mirror_search_by_projection_frame(orbx_matcher* m, const orbx_keypoint* k, const unsigned char* d, int n,
+                                      const float* uright, unsigned char* hasMP, const float* bounds, const float* qUV,
+                                      const float* qR, const int* qMin, const int* qMax, const float* qUR,
+                                      const float* qAngle, const unsigned char* qDesc, int nQ, int thDist, int checkOri,
+                                      int* curMatch) {
+  return orbx_host::SearchByProjection(m, view(k, d, n, bounds, uright), hasMP, qUV, qR, qMin, qMax, qUR, qAngle, qDesc, nQ,
+                                       thDist, checkOri != 0, curMatch);
+}
+
+}  // extern "C"

@@ -1,0 +1,216 @@
+// See orbx_search.h. Control flow follows R/src/ORBmatcher.cpp line by line; the candidate lists and the
+// Hamming distances come from the device.
+#include "orbx_search.h"
+
+#include <climits>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+
+namespace orbx_host {
+
+namespace {
+
+struct Candidates {
+  std::vector<int> off, idx, dist;
+};
+
+void Fail(const char* what) {
+  std::fprintf(stderr, "orbx_host: %s: %s\n", what, orbx_last_error());
+  std::abort();  // no CPU fallback
+}
+
+void WindowSearch(orbx_matcher* m, const FrameView& F, const std::vector<float>& qxy, const std::vector<float>& qr,
+                  const std::vector<int>& qmin, const std::vector<int>& qmax, const unsigned char* qdesc, int nq,
+                  Candidates* c) {
+  c->off.assign(nq + 1, 0);
+  if (nq == 0) return;
+  int cap = 64 * nq, need = 0;
+  for (;;) {
+    c->idx.resize(cap);
+    c->dist.resize(cap);
+    const int rc = orbx_match_window(m, F.keysUn, F.descriptors, F.N, F.minX, F.maxX, F.minY, F.maxY, &qxy[0], &qr[0],
+                                     &qmin[0], &qmax[0], qdesc, nq, &c->off[0], &c->idx[0], &c->dist[0], cap, &need);
+    if (rc == ORBX_ERR_CAPACITY && need > cap) { cap = need; continue; }
+    if (rc != ORBX_OK) Fail("orbx_match_window");
+    return;
+  }
+}
+
+int RotBin(float a1, float a2) {  // :569-575
+  const float factor = HISTO_LENGTH / 360.0f;
+  float rot = a1 - a2;
+  if (rot < 0.0) rot += 360.0f;
+  int bin = (int)roundf(rot * factor);
+  if (bin == HISTO_LENGTH) bin = 0;
+  return bin;
+}
+
+}  // namespace
+
+void ComputeThreeMaxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  for (int i = 0; i < L; i++) {
+    const int s = (int)histo[i].size();
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
+  }
+  if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+  else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+int SearchForInitialization(orbx_matcher* m, const FrameView& F1, const FrameView& F2, float* vbPrevMatched,
+                            int* vnMatches12, int windowSize, float nnratio, bool checkOrientation) {
+  int nmatches = 0;
+  for (int i = 0; i < F1.N; i++) vnMatches12[i] = -1;
+  // queries: the level-0 keypoints of F1 (:515-517), window around vbPrevMatched (:519)
+  std::vector<int> qOf;  // query -> i1
+  std::vector<float> qxy, qr;
+  std::vector<int> qmin, qmax;
+  std::vector<unsigned char> qdesc;
+  for (int i1 = 0; i1 < F1.N; i1++) {
+    if (F1.keysUn[i1].octave > 0) continue;
+    qOf.push_back(i1);
+    qxy.push_back(vbPrevMatched[2 * i1]);
+    qxy.push_back(vbPrevMatched[2 * i1 + 1]);
+    qr.push_back((float)windowSize);
+    qmin.push_back(F1.keysUn[i1].octave);
+    qmax.push_back(F1.keysUn[i1].octave);
+    qdesc.insert(qdesc.end(), F1.descriptors + (size_t)i1 * 32, F1.descriptors + (size_t)i1 * 32 + 32);
+  }
+  Candidates c;
+  WindowSearch(m, F2, qxy, qr, qmin, qmax, qdesc.empty() ? NULL : &qdesc[0], (int)qOf.size(), &c);
+
+  std::vector<int> rotHist[HISTO_LENGTH];
+  std::vector<int> vMatchedDistance(F2.N, INT_MAX), vnMatches21(F2.N, -1);
+  for (size_t q = 0; q < qOf.size(); q++) {
+    const int i1 = qOf[q];
+    if (c.off[q] == c.off[q + 1]) continue;
+    int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+    for (int k = c.off[q]; k < c.off[q + 1]; k++) {
+      const int i2 = c.idx[k], dist = c.dist[k];
+      if (vMatchedDistance[i2] <= dist) continue;
+      if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+      else if (dist < bestDist2) { bestDist2 = dist; }
+    }
+    if (bestDist <= TH_LOW) {
+      if (bestDist < (float)bestDist2 * nnratio) {
+        if (vnMatches21[bestIdx2] >= 0) { vnMatches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+        vnMatches12[i1] = bestIdx2;
+        vnMatches21[bestIdx2] = i1;
+        vMatchedDistance[bestIdx2] = bestDist;
+        nmatches++;
+        if (checkOrientation) rotHist[RotBin(F1.keysUn[i1].angle, F2.keysUn[bestIdx2].angle)].push_back(i1);
+      }
+    }
+  }
+  if (checkOrientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (size_t j = 0; j < rotHist[i].size(); j++) {
+        const int idx1 = rotHist[i][j];
+        if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; nmatches--; }
+      }
+    }
+  }
+  for (int i1 = 0; i1 < F1.N; i1++)
+    if (vnMatches12[i1] >= 0) {
+      vbPrevMatched[2 * i1] = F2.keysUn[vnMatches12[i1]].x;
+      vbPrevMatched[2 * i1 + 1] = F2.keysUn[vnMatches12[i1]].y;
+    }
+  return nmatches;
+}
+
+int SearchByProjection(orbx_matcher* m, const FrameView& F, unsigned char* hasMapPoint, const float* mpUV,
+                       const float* mpRadius, const int* mpLevel, const float* mpUR, const unsigned char* mpDesc,
+                       int nMP, const float* scaleFactors, float nnratio, int* mpMatch) {
+  std::vector<float> qxy(mpUV, mpUV + 2 * (size_t)nMP), qr(nMP);
+  std::vector<int> qmin(nMP), qmax(nMP);
+  for (int i = 0; i < nMP; i++) {
+    qr[i] = mpRadius[i] * scaleFactors[mpLevel[i]];  // :93
+    qmin[i] = mpLevel[i] - 1;
+    qmax[i] = mpLevel[i];
+  }
+  Candidates c;
+  WindowSearch(m, F, qxy, qr, qmin, qmax, mpDesc, nMP, &c);
+  int nmatches = 0;
+  for (int iMP = 0; iMP < nMP; iMP++) {
+    mpMatch[iMP] = -1;
+    if (c.off[iMP] == c.off[iMP + 1]) continue;
+    const int nPredictedLevel = mpLevel[iMP];
+    const float r = mpRadius[iMP];
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+    for (int k = c.off[iMP]; k < c.off[iMP + 1]; k++) {
+      const int idx = c.idx[k];
+      if (hasMapPoint[idx]) continue;  // :118-121
+      if (F.uRight && F.uRight[idx] > 0) {
+        const float er = fabsf(mpUR[iMP] - F.uRight[idx]);
+        if (er > r * scaleFactors[nPredictedLevel]) continue;
+      }
+      const int dist = c.dist[k];
+      if (dist < bestDist) {
+        bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = F.keysUn[idx].octave; bestIdx = idx;
+      } else if (dist < bestDist2) {
+        bestLevel2 = F.keysUn[idx].octave; bestDist2 = dist;
+      }
+    }
+    if (bestDist <= TH_HIGH) {
+      if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+      mpMatch[iMP] = bestIdx;
+      hasMapPoint[bestIdx] = 1;  // F.mvpMapPoints[bestIdx]=pMP (:157)
+      nmatches++;
+    }
+  }
+  return nmatches;
+}
+
+int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* hasMapPoint, const float* qUV,
+                       const float* qRadius, const int* qMinLevel, const int* qMaxLevel, const float* qUR,
+                       const float* qAngle, const unsigned char* qDesc, int nQ, int thDist, bool checkOrientation,
+                       int* curMatch) {
+  std::vector<float> qxy(qUV, qUV + 2 * (size_t)nQ), qr(qRadius, qRadius + nQ);
+  std::vector<int> qmin(qMinLevel, qMinLevel + nQ), qmax(qMaxLevel, qMaxLevel + nQ);
+  Candidates c;
+  WindowSearch(m, Cur, qxy, qr, qmin, qmax, qDesc, nQ, &c);
+  for (int i = 0; i < Cur.N; i++) curMatch[i] = -1;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  int nmatches = 0;
+  for (int i = 0; i < nQ; i++) {
+    if (c.off[i] == c.off[i + 1]) continue;
+    const float radius = qRadius[i];
+    int bestDist = 256, bestIdx2 = -1;
+    for (int k = c.off[i]; k < c.off[i + 1]; k++) {
+      const int i2 = c.idx[k];
+      if (hasMapPoint[i2]) continue;  // :1648-1650
+      if (Cur.uRight && Cur.uRight[i2] > 0) {
+        const float er = fabsf(qUR[i] - Cur.uRight[i2]);
+        if (er > radius) continue;
+      }
+      const int dist = c.dist[k];
+      if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+    }
+    if (bestDist <= thDist) {
+      curMatch[bestIdx2] = i;
+      hasMapPoint[bestIdx2] = 1;  // CurrentFrame.mvpMapPoints[bestIdx2]=pMP (:1675)
+      nmatches++;
+      if (checkOrientation) rotHist[RotBin(qAngle[i], Cur.keysUn[bestIdx2].angle)].push_back(bestIdx2);
+    }
+  }
+  if (checkOrientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++)
+      if (i != ind1 && i != ind2 && i != ind3)
+        for (size_t j = 0; j < rotHist[i].size(); j++) {
+          curMatch[rotHist[i][j]] = -1;
+          hasMapPoint[rotHist[i][j]] = 0;  // mvpMapPoints[...] = NULL (:1711)
+          nmatches--;
+        }
+  }
+  return nmatches;
+}
+
+}  // namespace orbx_host

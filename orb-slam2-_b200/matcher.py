@@ -55,5 +55,44 @@ class ORBmatcher:
         check(lib().orbx_match_merge_device(self._h, d_idx, d_d1, d_d2, nshards, nq, self.mfNNratio, th,
                                             o_idx, o_d1, o_d2, o_acc, stream))
 
+    def match_window(self, kps_un, desc, bounds, q_xy, q_r, q_min_level, q_max_level, q_desc):
+        """Candidates of Frame::GetFeaturesInArea for every query, in the reference's order, with their Hamming
+        distances: (cand_off[nq+1], cand_idx, cand_dist). bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+        kps_un = np.ascontiguousarray(kps_un)
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        q_xy = np.ascontiguousarray(q_xy, np.float32).reshape(-1, 2)
+        nq = q_xy.shape[0]
+        q_r = np.ascontiguousarray(q_r, np.float32)
+        q_min_level = np.ascontiguousarray(q_min_level, np.int32)
+        q_max_level = np.ascontiguousarray(q_max_level, np.int32)
+        q_desc = np.ascontiguousarray(q_desc, np.uint8).reshape(-1, 32)
+        if not (len(q_r) == len(q_min_level) == len(q_max_level) == len(q_desc) == nq) or len(desc) != len(kps_un):
+            raise ValueError("query / frame arrays disagree in length")
+        off = np.zeros(nq + 1, np.int32)
+        cap = max(64, 32 * nq)
+        while True:
+            idx, dist = np.empty(cap, np.int32), np.empty(cap, np.int32)
+            n = C.c_int32(0)
+            rc = lib().orbx_match_window(self._h, ptr(kps_un), ptr(desc), len(kps_un), bounds[0], bounds[1], bounds[2],
+                                         bounds[3], ptr(q_xy), ptr(q_r), ptr(q_min_level), ptr(q_max_level), ptr(q_desc),
+                                         nq, ptr(off), ptr(idx), ptr(dist), cap, C.byref(n))
+            if rc == -3 and n.value > cap:
+                cap = n.value
+                continue
+            check(rc)
+            return off, idx[:n.value].copy(), dist[:n.value].copy()
+
+    def stereo_match(self, ex_left, ex_right, kps_l, desc_l, kps_r, desc_r, mbf, mb, frame_left=0, frame_right=0):
+        """Frame::ComputeStereoMatches on the pyramids the two extractors still hold: (mvuRight, mvDepth, n)."""
+        kps_l, kps_r = np.ascontiguousarray(kps_l), np.ascontiguousarray(kps_r)
+        desc_l = np.ascontiguousarray(desc_l, np.uint8).reshape(-1, 32)
+        desc_r = np.ascontiguousarray(desc_r, np.uint8).reshape(-1, 32)
+        nl = len(kps_l)
+        u, z = np.empty(max(nl, 1), np.float32), np.empty(max(nl, 1), np.float32)
+        n = C.c_int32(0)
+        check(lib().orbx_stereo_match(self._h, ex_left._h, ex_right._h, frame_left, frame_right, ptr(kps_l), ptr(desc_l), nl,
+                                      ptr(kps_r), ptr(desc_r), len(kps_r), mbf, mb, ptr(u), ptr(z), C.byref(n)))
+        return u[:nl], z[:nl], n.value
+
     def launch_count(self):
         return int(lib().orbx_matcher_launch_count(self._h))

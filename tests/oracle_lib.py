@@ -68,6 +68,18 @@ def lib():
         L.orb_oracle_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p]
         L.orb_oracle_match_bf2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_float, C.c_int,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orb_oracle_grid_create.restype = C.c_void_p
+        L.orb_oracle_grid_create.argtypes = [C.c_void_p, C.c_int] + [C.c_float] * 4
+        L.orb_oracle_grid_destroy.argtypes = [C.c_void_p]
+        L.orb_oracle_grid_query.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orb_oracle_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int] + \
+            [C.c_float] * 4 + [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int]
+        L.orb_oracle_search_by_projection_mp.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] + \
+            [C.c_float] * 4 + [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_float, C.c_void_p]
+        L.orb_oracle_search_by_projection_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] + \
+            [C.c_float] * 4 + [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.orb_oracle_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int] + \
+            [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
     return _lib
 
 
@@ -211,3 +223,92 @@ class Extractor:
 
     def tie_sensitive(self, l):
         return lib().orb_oracle_level_tie_sensitive(self._h, l)
+
+
+# ---- windowed matchers / stereo ------------------------------------------------------------------
+def _opt(a):
+    return None if a is None else _ptr(a)
+
+
+class Grid:
+    """Frame grid + GetFeaturesInArea (R/src/Frame.cpp:244-260, 387-452)."""
+
+    def __init__(self, kps_un, bounds):
+        self._k = np.ascontiguousarray(kps_un)
+        self._h = lib().orb_oracle_grid_create(_ptr(self._k), len(self._k), *[float(b) for b in bounds])
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orb_oracle_grid_destroy(self._h)
+            self._h = None
+
+    def query(self, x, y, r, min_level, max_level):
+        out = np.empty(max(len(self._k), 1), np.int32)
+        n = lib().orb_oracle_grid_query(self._h, x, y, r, min_level, max_level, _ptr(out), len(out))
+        return out[:n].copy()
+
+
+def search_for_initialization(kps1, desc1, kps2, desc2, bounds, prev_matched, window, nnratio, check_ori=True):
+    kps1, kps2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    desc1, desc2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.empty(len(kps1), np.int32)
+    n = lib().orb_oracle_search_for_initialization(_ptr(kps1), _ptr(desc1), len(kps1), _ptr(kps2), _ptr(desc2), len(kps2),
+                                                   *[float(b) for b in bounds], _ptr(pm), _ptr(m12), window, nnratio,
+                                                   int(check_ori))
+    return n, m12, pm
+
+
+def search_by_projection_mp(kps_un, desc, uright, has_mp, bounds, mp_uv, mp_r, mp_level, mp_ur, mp_desc, scale_factors,
+                            nnratio):
+    kps_un = np.ascontiguousarray(kps_un)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    args = [np.ascontiguousarray(mp_uv, np.float32), np.ascontiguousarray(mp_r, np.float32),
+            np.ascontiguousarray(mp_level, np.int32), np.ascontiguousarray(mp_ur, np.float32),
+            np.ascontiguousarray(mp_desc, np.uint8)]
+    has_mp = np.ascontiguousarray(has_mp, np.uint8)
+    ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    match = np.empty(len(args[1]), np.int32)
+    n = lib().orb_oracle_search_by_projection_mp(_ptr(kps_un), _ptr(desc), len(kps_un), _opt(ur), _ptr(has_mp),
+                                                 *[float(b) for b in bounds], *[_ptr(a) for a in args], len(args[1]),
+                                                 _ptr(sf), nnratio, _ptr(match))
+    return n, match
+
+
+def search_by_projection_frame(kps_un, desc, uright, has_mp, bounds, q_uv, q_r, q_min_level, q_max_level, q_ur, q_angle,
+                               q_desc, th_dist, check_ori=True):
+    kps_un = np.ascontiguousarray(kps_un)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    args = [np.ascontiguousarray(q_uv, np.float32), np.ascontiguousarray(q_r, np.float32),
+            np.ascontiguousarray(q_min_level, np.int32), np.ascontiguousarray(q_max_level, np.int32),
+            np.ascontiguousarray(q_ur, np.float32), np.ascontiguousarray(q_angle, np.float32),
+            np.ascontiguousarray(q_desc, np.uint8)]
+    has_mp = np.ascontiguousarray(has_mp, np.uint8)
+    ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+    match = np.empty(len(kps_un), np.int32)
+    n = lib().orb_oracle_search_by_projection_frame(_ptr(kps_un), _ptr(desc), len(kps_un), _opt(ur), _ptr(has_mp),
+                                                    *[float(b) for b in bounds], *[_ptr(a) for a in args], len(args[1]),
+                                                    th_dist, int(check_ori), _ptr(match))
+    return n, match
+
+
+def stereo_matches(kps_l, desc_l, kps_r, desc_r, pyr_l, pyr_r, scale_factors, inv_scale_factors, mbf, mb):
+    kps_l, kps_r = np.ascontiguousarray(kps_l), np.ascontiguousarray(kps_r)
+    desc_l, desc_r = np.ascontiguousarray(desc_l, np.uint8), np.ascontiguousarray(desc_r, np.uint8)
+    pl = [np.ascontiguousarray(p, np.uint8) for p in pyr_l]
+    pr = [np.ascontiguousarray(p, np.uint8) for p in pyr_r]
+    nlev = len(pl)
+    PL = (C.c_void_p * nlev)(*[p.ctypes.data for p in pl])
+    PR = (C.c_void_p * nlev)(*[p.ctypes.data for p in pr])
+    w = np.array([p.shape[1] for p in pl], np.int32)
+    h = np.array([p.shape[0] for p in pl], np.int32)
+    st = np.array([p.strides[0] for p in pl], np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    isf = np.ascontiguousarray(inv_scale_factors, np.float32)
+    u = np.empty(max(len(kps_l), 1), np.float32)
+    z = np.empty(max(len(kps_l), 1), np.float32)
+    n = lib().orb_oracle_stereo_matches(_ptr(kps_l), _ptr(desc_l), len(kps_l), _ptr(kps_r), _ptr(desc_r), len(kps_r),
+                                        PL, PR, _ptr(w), _ptr(h), _ptr(st), nlev, _ptr(sf), _ptr(isf), mbf, mb,
+                                        _ptr(u), _ptr(z))
+    return u[:len(kps_l)], z[:len(kps_l)], n
