@@ -137,13 +137,23 @@ def device_frames(torch, base, count, rank):
     return out
 
 
+def cpu_extractor_factory():
+    """(constructor, kind): the reference's own ORBextractor.cpp (oracle/_ref, built in the authoring container from
+    /root/reference against the cv shim; the .so travels) when present -> kind "reference"; else the oracle port."""
+    import ref_lib
+    if ref_lib.available():
+        ref_lib.lib()
+        return (lambda: ref_lib.RefExtractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)), "reference"
+    import oracle_lib
+    oracle_lib.lib()
+    return (lambda: oracle_lib.Extractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)), "port"
+
+
 def time_cpu_oracle(frames, budget_s, nthreads):
     """frames/s of the CPU oracle with `nthreads` threads, each with its own extractor instance
     (the reference's own pattern: one ORBextractor per std::thread, R/src/Frame.cpp:86-89)."""
-    import oracle_lib
-    oracle_lib.lib()
     nfr = len(frames)
-    exs = [oracle_lib.Extractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH) for _ in range(nthreads)]
+    exs = [cpu_extractor_factory()[0]() for _ in range(nthreads)]
     exs[0](frames[0])  # warm caches / page in
     done = [0] * nthreads
     per_call = []
@@ -194,11 +204,12 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "frames_per_step": "time-bounded sample"},
-            "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample,
+            "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": cpu_extractor_factory()[1],
+                             "sample": sample,
                              "single_thread_ms_per_frame": med_ms},
             "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
     return 0
 
 
@@ -217,8 +228,8 @@ def run_hamming(torch, dist, pkg, world, rank, local, args, barrier, max_over_ra
     lo, hi = pkg.sharding.block_range(HAM_NDB, rank, world)
     g.manual_seed(1000 + rank)
     db = torch.randint(0, 256, (hi - lo, 32), generator=g, device=dev, dtype=torch.uint8)
-    plant = torch.arange(0, min(HAM_NQ // 2, hi - lo), device=dev)
-    db[plant * ((hi - lo) // max(len(plant), 1))] = q[plant]   # half of the queries have an exact row in shard `rank`
+    plant = torch.arange(rank, HAM_NQ // 2, world, device=dev)      # query i has ONE exact row, in shard i % world
+    db[(plant // world) * ((hi - lo) // (HAM_NQ // 2 // world + 1))] = q[plant]
     m = pkg.ORBmatcher(0.6, device=local)
     part = torch.empty((3, HAM_NQ), dtype=torch.int32, device=dev)
     gathered = torch.empty((world, 3, HAM_NQ), dtype=torch.int32, device=dev)
@@ -402,7 +413,7 @@ def _run_gpu(args, torch):
         cores = os.cpu_count() or 1
         sample_frames = [f for f in frames[:BASE_FRAMES].cpu().numpy()]
         fps, n, med_ms = time_cpu_oracle(sample_frames, 12.0, cores)
-        cpu = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+        cpu = {"value": fps, "unit": "frames/s", "cores": cores, "kind": cpu_extractor_factory()[1],
                "sample": f"12 s of the same {W}x{H} frames on {cores} threads ({n} frames), one extractor per thread",
                "single_thread_ms_per_frame": med_ms}
 
@@ -414,13 +425,17 @@ def _run_gpu(args, torch):
                        "keypoints_per_frame": nkp / B, "parallelism": f"frame sharding x{world}, no collective"},
             "clocks": clocks, "e2e": e2e_obj, "gpu_launches": launches, "roofline": roof, "stages": stages,
             "cpu_baseline": cpu, "hamming": hamming}
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
 def main():
+    # NCCL / torchrun may write to stdout; the contract is ONE JSON line there. Everything else goes to stderr.
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
