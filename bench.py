@@ -35,7 +35,7 @@ sys.path.insert(0, str(ROOT / "tests"))
 
 W, H, NFEAT, NLEVELS, SCALE, INI_TH, MIN_TH = 640, 480, 1000, 8, 1.2, 20, 7
 FRAMES_PER_STEP = 512          # 512 x 307200 B = 157 MB of input per step (> 126 MB L2)
-E2E_FRAMES_PER_STEP = 256
+E2E_FRAMES_PER_STEP = 512
 BASE_FRAMES = 32               # distinct numpy-generated frames; the rest are shifted/noised copies
 METRIC = "ORB frames/s (640x480, 1000 kp)"
 WORKLOAD = ("C1: ORBextractor::operator() on 640x480 u8 frames, 1000 features, 8 levels, scale 1.2, "
@@ -377,7 +377,7 @@ def _run_gpu(args, torch):
         assert int(h_n.sum()) > 0 and np.array_equal(h_n, d_n[:Be].cpu().numpy()), "e2e leg disagrees with the device leg"
     e2e_obj = {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": Be * W * H,
                "d2h_bytes_per_step": Be * rows_per_frame * 60 + Be * 4, "frames_per_step": Be,
-               "api": "orbx_extract_batch (pinned host frames in, host keypoints+descriptors out; 32-frame chunks on 2 streams)"}
+               "api": "orbx_extract_batch (pinned host frames in, host keypoints+descriptors out; 32-frame chunks rotating over 4 streams)"}
 
     hamming = None if args.skip_hamming else run_hamming(torch, dist, pkg, world, rank, local, args, barrier, max_over_ranks)
 

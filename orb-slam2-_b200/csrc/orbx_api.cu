@@ -2,10 +2,11 @@
 // setup, arena management, the launch sequence of the extraction pipeline, and host<->device copies
 // for the host-buffer entry points. No CPU implementation of any stage lives here.
 //
-// Host-buffer batches are cut into chunks of kChunk frames that alternate between two lanes (stream +
+// Host-buffer batches are cut into chunks of kChunk frames that rotate over up to kMaxLanes lanes (stream +
 // arenas + pinned staging each): while chunk k runs its kernels, chunk k+1's frames cross PCIe and
 // chunk k-1's keypoints/descriptors are scattered into the caller's arrays by the host thread.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -15,7 +16,25 @@ using namespace orbx;
 
 namespace {
 
-constexpr int kChunk = 32;  // frames per lane submission on the host-buffer path
+constexpr int kChunkDefault = 32;  // frames per lane submission on the host-buffer path
+
+int chunk_frames() {  // ORBX_CHUNK overrides (tuning knob; any value gives identical results)
+  static const int v = [] {
+    const char* e = std::getenv("ORBX_CHUNK");
+    const int x = e ? std::atoi(e) : 0;
+    return x > 0 ? x : kChunkDefault;
+  }();
+  return v;
+}
+
+int lane_count() {  // ORBX_LANES overrides (1..kMaxLanes)
+  static const int v = [] {
+    const char* e = std::getenv("ORBX_LANES");
+    const int x = e ? std::atoi(e) : 0;
+    return x > 0 ? std::min(x, kMaxLanes) : kMaxLanes;
+  }();
+  return v;
+}
 
 int check_device(int device) {
   int n = 0;
@@ -365,9 +384,9 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
     return ORBX_ERR_ARG;
   }
   ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
-  const int chunk = std::min(kChunk, count);
+  const int chunk = std::min(chunk_frames(), count);
   const int nchunks = (count + chunk - 1) / chunk;
-  const int nlanes = nchunks > 1 ? 2 : 1;
+  const int nlanes = std::min(nchunks, lane_count());
   int rc;
   for (int i = 0; i < nlanes; i++) {
     if ((rc = ensure_lane(h, h->lane[i], width, height, chunk))) return rc;
@@ -377,18 +396,18 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
   for (int c = 0; c <= nchunks; c++) {
     if (c < nchunks) {
       const int f0 = c * chunk, cnt = std::min(chunk, count - f0);
-      if (c >= 2) {  // the lane's staging still holds chunk c-2: scatter it before reusing the lane
-        const int g0 = (c - 2) * chunk, gc = std::min(chunk, count - g0);
-        if ((rc = collect_chunk(h, h->lane[c & 1], gc, kps + (size_t)g0 * cap, desc + (size_t)g0 * cap * 32, cap, n + g0,
+      if (c >= nlanes) {  // the lane's staging still holds chunk c-nlanes: scatter it before reusing the lane
+        const int g0 = (c - nlanes) * chunk, gc = std::min(chunk, count - g0);
+        if ((rc = collect_chunk(h, h->lane[c % nlanes], gc, kps + (size_t)g0 * cap, desc + (size_t)g0 * cap * 32, cap, n + g0,
                                 &tooSmall)))
           return rc;
       }
-      if ((rc = submit_chunk(h, h->lane[c & 1], imgs + f0, cnt, width, height, stride))) return rc;
+      if ((rc = submit_chunk(h, h->lane[c % nlanes], imgs + f0, cnt, width, height, stride))) return rc;
     }
   }
-  for (int c = std::max(nchunks - 2, 0); c < nchunks; c++) {
+  for (int c = std::max(nchunks - nlanes, 0); c < nchunks; c++) {
     const int f0 = c * chunk, cnt = std::min(chunk, count - f0);
-    if ((rc = collect_chunk(h, h->lane[c & 1], cnt, kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, n + f0,
+    if ((rc = collect_chunk(h, h->lane[c % nlanes], cnt, kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, n + f0,
                             &tooSmall)))
       return rc;
   }

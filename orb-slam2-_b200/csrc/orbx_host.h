@@ -37,8 +37,10 @@ struct DeviceBuf {
 
 namespace orbx {
 
+constexpr int kMaxLanes = 4;
+
 // One in-flight batch: a stream, its device arenas and pinned staging. The host-buffer entry points
-// alternate between two lanes so that the H2D copy of chunk k+1, the kernels of chunk k and the D2H +
+// rotate over the lanes so that the H2D copy of chunk k+1, the kernels of chunk k and the D2H +
 // host scatter of chunk k-1 overlap; the device-resident entry point uses lane 0 only.
 struct Lane {
   cudaStream_t stream = nullptr;
@@ -59,7 +61,7 @@ struct Lane {
 struct orbx_extractor {
   orbx_params params;
   orbx::CtorTables tables;
-  orbx::Lane lane[2];
+  orbx::Lane lane[orbx::kMaxLanes];
   bool profiling = false;
   float stageMs[6] = {};
   long long launches = 0;
