@@ -269,7 +269,7 @@ def run_hamming(torch, dist, pkg, world, rank, local, args, barrier, max_over_ra
             "accepted": int(acc.sum().item()), "gpu_launches_per_step": (m.launch_count() - l0) // steps,
             "compulsory_bytes_per_step": HAM_NDB * 32 + HAM_NQ * 32 * world + HAM_NQ * 13,
             "hbm_gbs": (HAM_NDB * 32 / world) / (ms * 1e-3) / 1e9,
-            "note": "bound by the integer/popc pipe (8 POPC + 8 XOR per pair, ~2500 popc per database byte), not by HBM"}
+            "note": "bound by integer issue, not by HBM: 4 POPC (16 lanes/clk/SM) + 16 LOP3 + 2.5 VIMNMX + 4 IMAD per pair after carry-save compression of the 8 XOR words"}
 
 
 def run_gpu(args):
@@ -359,8 +359,8 @@ def _run_gpu(args, torch):
     host.copy_(frames[:Be].cpu())
     hnp = host.numpy()
     ecap = NFEAT + 64
-    h_kps = np.empty((Be, ecap), pkg.KP_DTYPE)
-    h_desc = np.empty((Be, ecap, 32), np.uint8)
+    h_kps = pkg.pinned_empty((Be, ecap), pkg.KP_DTYPE, device=local)      # results land here without a staging copy
+    h_desc = pkg.pinned_empty((Be, ecap, 32), np.uint8, device=local)
     h_n = np.zeros(Be, np.int32)
     e2e_steps = 0 if args.skip_e2e else args.steps
     for _ in range(0 if args.skip_e2e else 3):
@@ -377,7 +377,7 @@ def _run_gpu(args, torch):
         assert int(h_n.sum()) > 0 and np.array_equal(h_n, d_n[:Be].cpu().numpy()), "e2e leg disagrees with the device leg"
     e2e_obj = {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": Be * W * H,
                "d2h_bytes_per_step": Be * rows_per_frame * 60 + Be * 4, "frames_per_step": Be,
-               "api": "orbx_extract_batch (pinned host frames in, host keypoints+descriptors out; 32-frame chunks rotating over 4 streams)"}
+               "api": "orbx_extract_batch (pinned host frames in, pinned host keypoints+descriptors out; 32-frame chunks rotating over 4 streams)"}
 
     hamming = None if args.skip_hamming else run_hamming(torch, dist, pkg, world, rank, local, args, barrier, max_over_ranks)
 
@@ -401,8 +401,19 @@ def _run_gpu(args, torch):
     dom = max(("pyramid", "fast", "octree", "blur", "describe"), key=lambda k: stages[k]["ms_per_step"])
     kernel_names = {"pyramid": "resize4_kernel (7 launches)", "fast": "fast_cells_kernel", "octree": "octree_kernel",
                     "blur": "blur_kernel", "describe": "describe_kernel"}
+    # DRAM traffic and the limiting pipe of that kernel come from the committed ncu --set full capture (per launch of
+    # 512 frames, like `achieved`); null when the digest does not cover this kernel or this launch size
+    traffic, limiter = None, None
+    digest_path = ROOT / "profiles" / "ncu_digest.json"
+    if digest_path.exists():
+        dg = json.loads(digest_path.read_text())
+        k = dg["kernels"].get(kernel_names[dom])
+        if k and dg["frames_per_launch"] == B:
+            traffic = k["dram_bytes"]
+            limiter = {"pipe": "alu (integer issue)", "pct_of_peak": k.get("alu_pipe_pct"), "issue_pct": k.get("issue_pct"),
+                       "source": dg["source"]}
     roof = {"bound": "hbm", "kernel": kernel_names[dom], "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s",
-            "frac": stages[dom]["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+            "frac": stages[dom]["gbs"] / peak, "traffic": traffic, "limiter": limiter, "peak_source": peak_src,
             "share_of_step": stages[dom]["ms_per_step"] / (stage_acc["total"] / args.steps),
             "pipeline_achieved": ab["total"] * value / world / 1e9,
             "pipeline_frac": ab["total"] * value / world / 1e9 / peak,

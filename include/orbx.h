@@ -80,8 +80,16 @@ int orbx_extractor_tables(const orbx_extractor* h, float* scale_factors, float* 
 int orbx_extract(orbx_extractor* h, const uint8_t* img, int32_t width, int32_t height, size_t stride,
                  orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n);
 
+/* Page-locked host memory for frames and results (cudaHostAlloc on `device`'s context). Optional: every
+ * host-buffer entry point accepts pageable memory too, pinned buffers make its copies asynchronous. */
+int orbx_host_alloc(int32_t device, size_t bytes, void** out);
+int orbx_host_free(void* p);
+
 /* `count` same-sized frames, host buffers (frame f at imgs[f]); outputs are count x cap rows,
- * n[f] per frame. Used for image sequences / stereo pairs (BASELINE.json configs 2-4). */
+ * n[f] per frame. Used for image sequences / stereo pairs (BASELINE.json configs 2-4).
+ * Frames are processed in chunks that rotate over several streams, so H2D, kernels and D2H overlap.
+ * Pinned kps/desc arrays receive the device rows directly (entries past n[f] are then unspecified);
+ * pageable ones are filled from a pinned staging buffer, rows [0, n[f]) only. */
 int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width,
                        int32_t height, size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap,
                        int32_t* n);

@@ -4,7 +4,7 @@ The product is liborbx.so (hand-written CUDA for sm_100a behind the C ABI in inc
 This package is the Python host-side mirror of the reference's two classes, used by the parity
 tests and bench.py. Nothing here computes on the CPU and nothing here imports oracle/.
 """
-from ._capi import KP_DTYPE, LIB_PATH, OrbxError, SIGNATURES, lib  # noqa: F401
+from ._capi import KP_DTYPE, LIB_PATH, OrbxError, SIGNATURES, lib, pinned_empty  # noqa: F401
 from .extractor import (ORBextractor, blur7_u8, distribute, fast_atan2, resize_u8, sincosf,  # noqa: F401
                         sincosf_sweep)
 from .matcher import ORBmatcher  # noqa: F401

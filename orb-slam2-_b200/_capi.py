@@ -32,6 +32,8 @@ SIGNATURES = {
     "orbx_last_error": (C.c_char_p, []),
     "orbx_version": (C.c_char_p, []),
     "orbx_device_count": (C.c_int, []),
+    "orbx_host_alloc": (C.c_int, [_i32, _sz, C.POINTER(_vp)]),
+    "orbx_host_free": (C.c_int, [_vp]),
     "orbx_extractor_create": (C.c_int, [C.POINTER(Params), C.POINTER(_vp)]),
     "orbx_extractor_destroy": (None, [_vp]),
     "orbx_extractor_tables": (C.c_int, [_vp] + [_vp] * 6),
@@ -91,3 +93,24 @@ def check(rc):
 
 def ptr(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+def _host_free(address):
+    lib().orbx_host_free(C.c_void_p(address))
+
+
+def pinned_empty(shape, dtype, device=0):
+    """numpy array in page-locked host memory (orbx_host_alloc): frames and results in such arrays make the
+    copies of orbx_extract_batch asynchronous and let results land in them without a staging copy.
+    The block is freed when the last view of the array is gone."""
+    import weakref
+
+    import numpy as np
+    dt = np.dtype(dtype)
+    shape = (shape,) if isinstance(shape, int) else tuple(shape)
+    n = int(np.prod(shape)) * dt.itemsize
+    p = C.c_void_p()
+    check(lib().orbx_host_alloc(device, max(n, 1), C.byref(p)))
+    owner = np.frombuffer((C.c_uint8 * max(n, 1)).from_address(p.value), dtype=np.uint8)  # every view's .base
+    weakref.finalize(owner, _host_free, p.value)
+    return owner[:n].view(dt).reshape(shape)

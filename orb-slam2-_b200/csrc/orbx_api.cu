@@ -226,7 +226,26 @@ HostStage stage_of(const Lane& L) {
 }
 
 // H2D + pipeline + D2H of one chunk, all asynchronous on the lane's stream
-int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int count, int width, int height, size_t stride) {
+// Where a chunk's rows go on the host. Pinned caller arrays take the D2H copies directly (row pitch cap);
+// pageable ones go through the lane's pinned staging and are scattered by collect_chunk.
+struct HostOut {
+  orbx_keypoint* kps;
+  uint8_t* desc;
+  int cap;
+  bool direct;
+};
+
+bool is_pinned(const void* p, size_t bytes) {
+  cudaPointerAttributes a0, a1;
+  if (cudaPointerGetAttributes(&a0, p) != cudaSuccess || cudaPointerGetAttributes(&a1, static_cast<const char*>(p) + bytes - 1) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a0.type == cudaMemoryTypeHost && a1.type == cudaMemoryTypeHost;
+}
+
+int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int count, int width, int height, size_t stride,
+                 const HostOut& out) {
   const FrameSetGeom& g = L.geom;
   cudaStream_t s = L.stream;
   uint8_t* l0 = static_cast<uint8_t*>(L.pyrArena.p);  // level-0 slot of the arena (planeOff 0)
@@ -236,8 +255,11 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
     contiguous = contiguous && imgs[f] == imgs[0] + (size_t)f * stride * height;
   }
   if (contiguous && g.lv[0].planeBytes == (long long)g.lv[0].pitch * height) {
-    // frames back to back on the host: one 2-D copy of count*height rows
-    ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0, g.lv[0].pitch, imgs[0], stride, width, (size_t)height * count, cudaMemcpyHostToDevice, s));
+    // frames back to back on the host: one copy of count*height rows
+    if (stride == (size_t)width && g.lv[0].pitch == width)
+      ORBX_CUDA_TRY(cudaMemcpyAsync(l0, imgs[0], (size_t)width * height * count, cudaMemcpyHostToDevice, s));
+    else
+      ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0, g.lv[0].pitch, imgs[0], stride, width, (size_t)height * count, cudaMemcpyHostToDevice, s));
   } else {
     for (int f = 0; f < count; f++)
       ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, imgs[f], stride, width, height,
@@ -253,14 +275,26 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
   const int* dOverflow = static_cast<const int*>(L.counts.p) + 2 * L.batchCap * g.nlevels;
   ORBX_CUDA_TRY(cudaMemcpyAsync(st.n, dN, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
   ORBX_CUDA_TRY(cudaMemcpyAsync(st.overflow, dOverflow, sizeof(int), cudaMemcpyDeviceToHost, s));
-  ORBX_CUDA_TRY(cudaMemcpyAsync(st.kps, dK, (size_t)count * rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
-  ORBX_CUDA_TRY(cudaMemcpyAsync(st.desc, dD, (size_t)count * rows * 32, cudaMemcpyDeviceToHost, s));
+  if (out.direct) {
+    // one "row" per frame: the first min(rows, cap) keypoints; entries past n[f] are unspecified
+    const size_t take = (size_t)std::min(rows, out.cap);
+    ORBX_CUDA_TRY(cudaMemcpy2DAsync(out.kps, (size_t)out.cap * sizeof(orbx_keypoint), dK, (size_t)rows * sizeof(orbx_keypoint),
+                                    take * sizeof(orbx_keypoint), count, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaMemcpy2DAsync(out.desc, (size_t)out.cap * 32, dD, (size_t)rows * 32, take * 32, count,
+                                    cudaMemcpyDeviceToHost, s));
+  } else {
+    ORBX_CUDA_TRY(cudaMemcpyAsync(st.kps, dK, (size_t)count * rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(st.desc, dD, (size_t)count * rows * 32, cudaMemcpyDeviceToHost, s));
+  }
   ORBX_CUDA_TRY(cudaEventRecord(L.done, s));
   return ORBX_OK;
 }
 
 // wait for a submitted chunk and scatter its rows into the caller's arrays
-int collect_chunk(orbx_extractor* h, Lane& L, int count, orbx_keypoint* kps, uint8_t* desc, int cap, int* n, bool* tooSmall) {
+int collect_chunk(orbx_extractor* h, Lane& L, int count, const HostOut& out, int* n, bool* tooSmall) {
+  orbx_keypoint* kps = out.kps;
+  uint8_t* desc = out.desc;
+  const int cap = out.cap;
   ORBX_CUDA_TRY(cudaEventSynchronize(L.done));
   HostStage st = stage_of(L);
   if (*st.overflow) {
@@ -276,6 +310,7 @@ int collect_chunk(orbx_extractor* h, Lane& L, int count, orbx_keypoint* kps, uin
     const int nf = st.n[f];
     n[f] = nf;
     if (nf > cap) { *tooSmall = true; continue; }
+    if (out.direct) continue;
     std::memcpy(kps + (size_t)f * cap, st.kps + (size_t)f * rows, (size_t)nf * sizeof(orbx_keypoint));
     std::memcpy(desc + (size_t)f * cap * 32, st.desc + (size_t)f * rows * 32, (size_t)nf * 32);
   }
@@ -299,7 +334,19 @@ void orbx::Lane::release() {
 extern "C" {
 
 const char* orbx_last_error(void) { return last_error(); }
-const char* orbx_version(void) { return "orbx 0.2 sm_100a"; }
+const char* orbx_version(void) { return "orbx 0.3 sm_100a"; }
+
+int orbx_host_alloc(int32_t device, size_t bytes, void** out) {
+  if (!out || bytes == 0) { set_error("null/invalid argument"); return ORBX_ERR_ARG; }
+  ORBX_CUDA_TRY(cudaSetDevice(device));
+  ORBX_CUDA_TRY(cudaHostAlloc(out, bytes, cudaHostAllocPortable));
+  return ORBX_OK;
+}
+
+int orbx_host_free(void* p) {
+  if (p) ORBX_CUDA_TRY(cudaFreeHost(p));
+  return ORBX_OK;
+}
 int orbx_device_count(void) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -393,23 +440,21 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
     if ((rc = ensure_lane_staging(h->lane[i]))) return rc;
   }
   bool tooSmall = false;
+  const bool direct = is_pinned(kps, (size_t)count * cap * sizeof(orbx_keypoint)) && is_pinned(desc, (size_t)count * cap * 32);
+  auto out_at = [&](int f0) { return HostOut{kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, direct}; };
   for (int c = 0; c <= nchunks; c++) {
     if (c < nchunks) {
       const int f0 = c * chunk, cnt = std::min(chunk, count - f0);
       if (c >= nlanes) {  // the lane's staging still holds chunk c-nlanes: scatter it before reusing the lane
         const int g0 = (c - nlanes) * chunk, gc = std::min(chunk, count - g0);
-        if ((rc = collect_chunk(h, h->lane[c % nlanes], gc, kps + (size_t)g0 * cap, desc + (size_t)g0 * cap * 32, cap, n + g0,
-                                &tooSmall)))
-          return rc;
+        if ((rc = collect_chunk(h, h->lane[c % nlanes], gc, out_at(g0), n + g0, &tooSmall))) return rc;
       }
-      if ((rc = submit_chunk(h, h->lane[c % nlanes], imgs + f0, cnt, width, height, stride))) return rc;
+      if ((rc = submit_chunk(h, h->lane[c % nlanes], imgs + f0, cnt, width, height, stride, out_at(f0)))) return rc;
     }
   }
   for (int c = std::max(nchunks - nlanes, 0); c < nchunks; c++) {
     const int f0 = c * chunk, cnt = std::min(chunk, count - f0);
-    if ((rc = collect_chunk(h, h->lane[c % nlanes], cnt, kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, n + f0,
-                            &tooSmall)))
-      return rc;
+    if ((rc = collect_chunk(h, h->lane[c % nlanes], cnt, out_at(f0), n + f0, &tooSmall))) return rc;
   }
   if (nchunks > 1) h->haveResult = false;  // introspection only covers single-chunk batches
   if (tooSmall) { set_error("keypoint capacity %d too small (see n[])", cap); return ORBX_ERR_CAPACITY; }

@@ -55,26 +55,32 @@ __device__ __forceinline__ uint32_t fast_margin2(const uint32_t (&W)[7][3], uint
   P[12] = ORBX_RING(-3, 0);  P[13] = ORBX_RING(-3, 1);  P[14] = ORBX_RING(-2, 2);  P[15] = ORBX_RING(-1, 3);
   const uint32_t v = ORBX_RING(0, 0);
 #undef ORBX_RING
-  uint32_t T[16];
-  // A = min over arcs of the arc maximum
+  // A = min over the 16 arcs of the arc maximum. Arcs i and i+1 (i even) share p[i+1..i+8] =: M, and
+  // min(max(M, p[i]), max(M, p[i+9])) = max(M, min(p[i], p[i+9])): 8 pair terms instead of 16 arcs.
+  // U[j] = p[2j+1..2j+2], V[j] = p[2j+1..2j+4], M of arc pair m = V[m] and V[m+2]: 36 VIMNMX per side.
+  uint32_t U[8], V[8];
 #pragma unroll
-  for (int k = 0; k < 16; k++) T[k] = __vimax3_u16x2(P[k], P[(k + 1) & 15], P[(k + 2) & 15]);
+  for (int j = 0; j < 8; j++) U[j] = __vmaxu2(P[2 * j + 1], P[(2 * j + 2) & 15]);
+#pragma unroll
+  for (int j = 0; j < 8; j++) V[j] = __vmaxu2(U[j], U[(j + 1) & 7]);
   uint32_t A = 0xffffffffu;
 #pragma unroll
-  for (int k = 0; k < 16; k += 2) {
-    const uint32_t a0 = __vimax3_u16x2(T[k], T[(k + 3) & 15], T[(k + 6) & 15]);
-    const uint32_t a1 = __vimax3_u16x2(T[k + 1], T[(k + 4) & 15], T[(k + 7) & 15]);
-    A = __vimin3_u16x2(A, a0, a1);
+  for (int m = 0; m < 8; m += 2) {
+    const uint32_t x0 = __vimax3_u16x2(V[m], V[(m + 2) & 7], __vminu2(P[2 * m], P[(2 * m + 9) & 15]));
+    const uint32_t x1 = __vimax3_u16x2(V[m + 1], V[(m + 3) & 7], __vminu2(P[2 * m + 2], P[(2 * m + 11) & 15]));
+    A = __vimin3_u16x2(A, x0, x1);
   }
-  // B = max over arcs of the arc minimum
+  // B = max over arcs of the arc minimum, the same with min and max exchanged
 #pragma unroll
-  for (int k = 0; k < 16; k++) T[k] = __vimin3_u16x2(P[k], P[(k + 1) & 15], P[(k + 2) & 15]);
+  for (int j = 0; j < 8; j++) U[j] = __vminu2(P[2 * j + 1], P[(2 * j + 2) & 15]);
+#pragma unroll
+  for (int j = 0; j < 8; j++) V[j] = __vminu2(U[j], U[(j + 1) & 7]);
   uint32_t B = 0u;
 #pragma unroll
-  for (int k = 0; k < 16; k += 2) {
-    const uint32_t b0 = __vimin3_u16x2(T[k], T[(k + 3) & 15], T[(k + 6) & 15]);
-    const uint32_t b1 = __vimin3_u16x2(T[k + 1], T[(k + 4) & 15], T[(k + 7) & 15]);
-    B = __vimax3_u16x2(B, b0, b1);
+  for (int m = 0; m < 8; m += 2) {
+    const uint32_t x0 = __vimin3_u16x2(V[m], V[(m + 2) & 7], __vmaxu2(P[2 * m], P[(2 * m + 9) & 15]));
+    const uint32_t x1 = __vimin3_u16x2(V[m + 1], V[(m + 3) & 7], __vmaxu2(P[2 * m + 2], P[(2 * m + 11) & 15]));
+    B = __vimax3_u16x2(B, x0, x1);
   }
   // both lanes biased by +256 so the plain 32-bit subtractions cannot borrow across lanes
   const uint32_t dark = v + 0x01000100u - A;

@@ -28,10 +28,46 @@ __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, cons
          __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+// ---- brute-force inner step -------------------------------------------------------------------------
+// POPC issues at 16 lanes/clk/SM on sm_100a (tools/pipe_probe.cu: 0.124 warp-instr/clk/SMSP), a quarter of
+// the LOP3/VIMNMX rate, so 8 POPC per pair made the first version of this kernel POPC-bound (ncu r1_l: ALU
+// pipe 45 %, 15.2 of 16 POPC lanes/clk). The 8 XOR words are first compressed with carry-save adders
+// (a full adder over three words is two LOP3: parity 0x96 and majority 0xE8):
+//   (x0,x1,x2)->(s1,c1)  (x3,x4,x5)->(s2,c2)  (s1,s2,x6)->(s3,c3)  (c1,c2,c3)->(s4,c4)
+//   distance = popc(s3) + popc(x7) + 2 popc(s4) + 4 popc(c4)
+// 4 POPC + 8 LOP3 + 8 XOR per pair. The weighted sum and the key packing (distance << 23 | row) are one
+// IMAD each on the otherwise idle FMA pipe; the multipliers come in as kernel arguments so that ptxas
+// keeps them as IMADs instead of strength-reducing them to ALU shifts.
+struct KeyMul { unsigned m23, m24, m25; };
+
+__device__ __forceinline__ unsigned lop3_xor(unsigned a, unsigned b, unsigned c) {
+  unsigned r; asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r;
+}
+__device__ __forceinline__ unsigned lop3_maj(unsigned a, unsigned b, unsigned c) {
+  unsigned r; asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r;
+}
+__device__ __forceinline__ unsigned imad(unsigned a, unsigned b, unsigned c) {
+  unsigned r; asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r;
+}
+
+__device__ __forceinline__ unsigned hamming_key(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1,
+                                                unsigned rowKey, const KeyMul& km) {
+  const unsigned x0 = a0.x ^ b0.x, x1 = a0.y ^ b0.y, x2 = a0.z ^ b0.z, x3 = a0.w ^ b0.w;
+  const unsigned x4 = a1.x ^ b1.x, x5 = a1.y ^ b1.y, x6 = a1.z ^ b1.z, x7 = a1.w ^ b1.w;
+  const unsigned s1 = lop3_xor(x0, x1, x2), c1 = lop3_maj(x0, x1, x2);
+  const unsigned s2 = lop3_xor(x3, x4, x5), c2 = lop3_maj(x3, x4, x5);
+  const unsigned s3 = lop3_xor(s1, s2, x6), c3 = lop3_maj(s1, s2, x6);
+  const unsigned s4 = lop3_xor(c1, c2, c3), c4 = lop3_maj(c1, c2, c3);
+  unsigned key = imad(__popc(s3), km.m23, rowKey);
+  key = imad(__popc(x7), km.m23, key);
+  key = imad(__popc(s4), km.m24, key);
+  return imad(__popc(c4), km.m25, key);
+}
+
 // grid: (query groups, chunks). partial arrays are [chunk][nq].
 __global__ void __launch_bounds__(kBfThreads)
 bf2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, long long ndb, int rowsPerChunk,
-           long long idxBase, int* __restrict__ pIdx, int* __restrict__ pD1, int* __restrict__ pD2) {
+           long long idxBase, int* __restrict__ pIdx, int* __restrict__ pD1, int* __restrict__ pD2, const KeyMul km) {
   __shared__ uint4 tile[kBfTileRows * 2];
   const int tid = threadIdx.x;
   const int qBase = blockIdx.x * kBfQueriesPerCta;
@@ -55,12 +91,24 @@ bf2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, lo
     for (int i = tid; i < rows * 2; i += kBfThreads) tile[i] = db[2 * t0 + i];
     __syncthreads();
     unsigned rowKey = (unsigned)(t0 - rowBegin);
-#pragma unroll 2
-    for (int r = 0; r < rows; r++, rowKey++) {
+    int r = 0;
+    // two rows per step: the (k1, k2) update of a sorted pair (lo, hi) is 5 min/max instead of 6
+    for (; r + 1 < rows; r += 2, rowKey += 2) {
+      const uint4 d0 = tile[2 * r], d1 = tile[2 * r + 1], e0 = tile[2 * r + 2], e1 = tile[2 * r + 3];
+#pragma unroll
+      for (int k = 0; k < kBfQPT; k++) {
+        const unsigned ka = hamming_key(qa[k], qb[k], d0, d1, rowKey, km);
+        const unsigned kb = hamming_key(qa[k], qb[k], e0, e1, rowKey + 1, km);
+        const unsigned lo = min(ka, kb), hi = max(ka, kb);
+        k2[k] = min(min(k2[k], hi), max(k1[k], lo));
+        k1[k] = min(k1[k], lo);
+      }
+    }
+    if (r < rows) {
       const uint4 d0 = tile[2 * r], d1 = tile[2 * r + 1];
 #pragma unroll
       for (int k = 0; k < kBfQPT; k++) {
-        const unsigned key = ((unsigned)hamming256(qa[k], qb[k], d0, d1) << 23) | rowKey;
+        const unsigned key = hamming_key(qa[k], qb[k], d0, d1, rowKey, km);
         k2[k] = min(k2[k], max(k1[k], key));
         k1[k] = min(k1[k], key);
       }
@@ -125,8 +173,9 @@ int bf2_plan_chunks(int nq, long long ndb, int smCount, int* rowsPerChunk) {
 void launch_bf2(const uint8_t* q, int nq, const uint8_t* db, long long ndb, int rowsPerChunk, int chunks,
                 long long idxBase, int* pIdx, int* pD1, int* pD2, cudaStream_t s) {
   dim3 grid((nq + kBfQueriesPerCta - 1) / kBfQueriesPerCta, chunks);
+  const KeyMul km = {1u << 23, 1u << 24, 1u << 25};
   bf2_kernel<<<grid, kBfThreads, 0, s>>>(reinterpret_cast<const uint4*>(q), nq, reinterpret_cast<const uint4*>(db), ndb,
-                                         rowsPerChunk, idxBase, pIdx, pD1, pD2);
+                                         rowsPerChunk, idxBase, pIdx, pD1, pD2, km);
 }
 
 void launch_merge(const int* pIdx, const int* pD1, const int* pD2, int nshards, int nq, float ratio, int th,

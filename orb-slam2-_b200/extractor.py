@@ -105,9 +105,9 @@ class ORBextractor:
         cap = kps.shape[1]
         if kps.dtype != KP_DTYPE or kps.shape[0] < cnt or desc.shape[:2] != kps.shape[:2] or n.shape[0] < cnt:
             raise TypeError("output arrays do not match the batch")
-        base, fs = frames.ctypes.data, frames.strides[0]
-        arr = (C.c_void_p * cnt)(*[base + f * fs for f in range(cnt)])
-        check(lib().orbx_extract_batch(self._h, arr, cnt, w, h, frames.strides[1], ptr(kps), ptr(desc), cap, ptr(n)))
+        ptrs = frames.ctypes.data + frames.strides[0] * np.arange(cnt, dtype=np.int64)   # imgs[f], no Python loop
+        check(lib().orbx_extract_batch(self._h, C.cast(ptr(ptrs), C.POINTER(C.c_void_p)), cnt, w, h, frames.strides[1],
+                                       ptr(kps), ptr(desc), cap, ptr(n)))
 
     def extract_batch_device(self, d_imgs_ptr, count, width, height, row_stride, frame_stride, d_kps_ptr,
                              d_desc_ptr, cap, d_n_ptr, stream=0):

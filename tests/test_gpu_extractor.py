@@ -193,3 +193,30 @@ def test_chunked_host_batch_equals_single(pkg, oracle):
     res = ex.extract_batch([frames[i] for i in (5, 3, 69)])
     for (gk, gd), i in zip(res, (5, 3, 69)):
         assert np.array_equal(gk.view(np.uint8), kps[i, :n[i]].view(np.uint8)) and np.array_equal(gd, desc[i, :n[i]])
+
+
+@pytest.mark.parametrize("cap", [700, 400])
+def test_pinned_outputs_take_rows_directly(pkg, cap):
+    """Pinned result arrays receive the device rows with no staging copy (orbx_host_alloc + the direct D2H path of
+    orbx_extract_batch): same rows as the pageable path for every frame; cap below the per-frame row count
+    truncates the copy but never the reported n."""
+    B = 70
+    frames = pkg.pinned_empty((B, 240, 320), np.uint8)
+    for i in range(B):
+        frames[i] = pkg.synth.frame(320, 240, 300 + i)
+    ex = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240, max_batch=128)
+    big = 700
+    rk, rd, rn = np.empty((B, big), pkg.KP_DTYPE), np.empty((B, big, 32), np.uint8), np.zeros(B, np.int32)
+    ex.extract_batch_into(frames, rk, rd, rn)
+    pk, pd, pn = pkg.pinned_empty((B, cap), pkg.KP_DTYPE), pkg.pinned_empty((B, cap, 32), np.uint8), np.zeros(B, np.int32)
+    if cap >= rn.max():
+        ex.extract_batch_into(frames, pk, pd, pn)
+    else:
+        with pytest.raises(pkg.OrbxError):
+            ex.extract_batch_into(frames, pk, pd, pn)
+    assert np.array_equal(pn, rn)
+    for f in range(B):
+        m = min(int(rn[f]), cap)
+        if rn[f] <= cap:
+            assert np.array_equal(pk[f, :m].view(np.uint8), rk[f, :m].view(np.uint8)), f
+            assert np.array_equal(pd[f, :m], rd[f, :m]), f

@@ -22,4 +22,13 @@ timeout 900 ncu --set full --clock-control none --import-source on \
   -o $OUT/pipeline_full -f $CMD > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ncu -i $OUT/pipeline_full.ncu-rep --page raw --csv > $OUT/pipeline_full_raw.csv 2>/dev/null
+# matcher / stereo kernels: one small scripted pass (tools/match_probe.py), launch list + full capture
+MCMD="python tools/match_probe.py"
+timeout 300 $MCMD > $OUT/match_probe.log 2>&1
+echo "match probe exit $?"; tail -5 $OUT/match_probe.log
+timeout 600 ncu --set full --clock-control none --import-source on \
+  -k regex:'bf2_kernel|bf2_reduce|window_kernel|grid_build|stereo_match|stereo_median|merge_kernel' --launch-count 12 \
+  -o $OUT/match_full -f $MCMD > $OUT/ncu_match.log 2>&1
+echo "ncu match exit $?"
+ncu -i $OUT/match_full.ncu-rep --page raw --csv > $OUT/match_full_raw.csv 2>/dev/null
 ls -la $OUT
