@@ -66,6 +66,10 @@ public:
     // takes effect at the next operator() call.
     void SetDevice(int device);
 
+    // The liborbx handle behind this extractor: orbx_stereo_match reads the device pyramids of the
+    // last operator() call through it (the device-side Frame::ComputeStereoMatches).
+    orbx_extractor* handle() const { return mpHandle; }
+
 protected:
 
     void EnsureHandle(int width, int height);
