@@ -89,10 +89,11 @@ __device__ __forceinline__ uint32_t fast_margin2(const uint32_t (&W)[7][3], uint
   return __viaddmax_s16x2_relu(m, negThBias, 0u);           // max(m - th, 0)
 }
 
-// words of shared memory one cell needs: staged patch (ch x nW) + score map ((sh+2) x nW)
+// words of shared memory one cell needs: staged patch (ch x nW) + score map ((sh+2) x nW) + the queue of
+// tasks with a non-zero score word (16 bits per task)
 __host__ __device__ inline int fast_cell_words(int wCell, int hCell) {
   const int nW = ((7 + wCell - 1) >> 2) + 2;  // worst alignment: a = 7
-  return (hCell + 6) * nW + (hCell + 2) * nW;
+  return (hCell + 6) * nW + (hCell + 2) * nW + (hCell * (nW - 2) + 1) / 2 + 1;
 }
 
 __global__ void __launch_bounds__(kFastThreads, 4)
@@ -132,6 +133,7 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
 
   uint32_t* tile = smemFast + warp * wordsPerWarp;  // ch rows x nW words
   uint32_t* smap = tile + ch * nW;                  // (sh+2) rows x nW words, rows 0 and sh+1 stay zero
+  uint16_t* queue = reinterpret_cast<uint16_t*>(smap + (sh + 2) * nW);  // y<<8 | q of the tasks worth a second look
 
   const int pitch = pyr.pitch[level];
   const uint8_t* src = pyr.lvl[level] + (long long)f * pyr.frameStride[level] + (long long)iniY * pitch + gx0;
@@ -164,41 +166,52 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   const int y0 = lane / nG, q0 = lane - y0 * nG;
 
   // ---- score map: max(m - minTh, 0) for every scanned pixel (0 = not a corner at minTh) ----
+  // Rounds are warp-uniform (lanes past the last task idle inside the round) so that the ballot below is
+  // a full-warp one. Only a task whose word holds a corner can keep one after suppression: such tasks are
+  // queued (y<<8 | q) and everything after this loop walks the queue with all 32 lanes busy.
+  int nQ = 0;
   {
     int y = y0, q = q0;
-    for (int t = lane; t < nTasks; t += 32) {
-      const uint32_t* tp = &tile[y * nW + q];
-      uint32_t W[7][3];
+    for (int t0 = 0; t0 < nTasks; t0 += 32) {
+      uint32_t word = 0u;
+      if (t0 + lane < nTasks) {
+        const uint32_t* tp = &tile[y * nW + q];
+        uint32_t W[7][3];
 #pragma unroll
-      for (int j = 0; j < 7; j++) {
-        W[j][0] = tp[j * nW];
-        W[j][1] = tp[j * nW + 1];
-        W[j][2] = tp[j * nW + 2];
+        for (int j = 0; j < 7; j++) {
+          W[j][0] = tp[j * nW];
+          W[j][1] = tp[j * nW + 1];
+          W[j][2] = tp[j * nW + 2];
+        }
+        const uint32_t u01 = fast_margin2<4>(W, negThBias);
+        const uint32_t u23 = fast_margin2<6>(W, negThBias);
+        word = __byte_perm(u01, u23, 0x6420);
+        const int col0 = 4 * (q + 1);
+        const int skipLo = a - col0, skipHi = col0 + 4 - b;
+        if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
+        if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
+        smap[(y + 1) * nW + q + 1] = word;
       }
-      const uint32_t u01 = fast_margin2<4>(W, negThBias);
-      const uint32_t u23 = fast_margin2<6>(W, negThBias);
-      uint32_t word = __byte_perm(u01, u23, 0x6420);
-      const int col0 = 4 * (q + 1);
-      const int skipLo = a - col0, skipHi = col0 + 4 - b;
-      if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
-      if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
-      smap[(y + 1) * nW + q + 1] = word;
+      const uint32_t liveMask = __ballot_sync(0xffffffffu, word != 0u);
+      if (word != 0u) queue[nQ + __popc(liveMask & ((1u << lane) - 1u))] = (uint16_t)((y << 8) | q);
+      nQ += __popc(liveMask);
       y += dy; q += dq;
       if (q >= nG) { q -= nG; y++; }
     }
   }
   __syncwarp();
+  if (nQ == 0) return;
 
   // ---- cell-local 3x3 strict non-max suppression, packed: the 8-neighbour maximum of two adjacent
-  //      pixels is 4 VIMNMX on 16x2 lanes; survivors' scores go to a second map that reuses the
-  //      patch rows (same indexing as smap) ----
-  uint32_t* kmap = tile;
+  //      pixels is 4 VIMNMX on 16x2 lanes; the survivors' scores of queue entry j go to kept[j], which
+  //      reuses the patch rows ----
+  uint32_t* kept = tile;
   const int iniByte = max(iniTh - minTh + 1, 1);  // stored value of a pixel whose score is iniTh
   uint32_t iniFlag = 0;
   {
     const uint32_t negIni = ((uint32_t)(-(iniByte - 1)) & 0xffffu) * 0x00010001u;
-    int y = y0, q = q0;
-    for (int t = lane; t < nTasks; t += 32) {
+    for (int j = lane; j < nQ; j += 32) {
+      const int e = queue[j], y = e >> 8, q = e & 0xff;
       const uint32_t* mp = &smap[y * nW + q];  // map rows y, y+1, y+2 = image rows y-1, y, y+1
       uint32_t E[3][5];                        // column pairs (3,4) (4,5) (5,6) (6,7) (7,8) of the 12-byte window
 #pragma unroll
@@ -210,7 +223,7 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
         E[r][3] = ex2<6>(w0, w1, w2);
         E[r][4] = ex2<7>(w0, w1, w2);
       }
-      uint32_t kept[2];
+      uint32_t k2[2];
 #pragma unroll
       for (int p = 0; p < 2; p++) {  // pixel pairs (0,1) and (2,3): left/centre/right pairs E[.][2p .. 2p+2]
         const uint32_t up = __vimax3_u16x2(E[0][2 * p], E[0][2 * p + 1], E[0][2 * p + 2]);
@@ -218,29 +231,20 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
         const uint32_t M = __vimax3_u16x2(up, dn, __vmaxu2(E[1][2 * p], E[1][2 * p + 2]));
         const uint32_t sc = E[1][2 * p + 1];
         const uint32_t d = __viaddmax_s16x2_relu(sc + 0x01000100u - M, 0xff00ff00u, 0u);  // max(s - M, 0)
-        kept[p] = __vminu2(sc, d << 8);                                                   // s if s > M else 0
-        iniFlag |= __viaddmax_s16x2_relu(kept[p], negIni, 0u);
+        k2[p] = __vminu2(sc, d << 8);                                                     // s if s > M else 0
+        iniFlag |= __viaddmax_s16x2_relu(k2[p], negIni, 0u);
       }
-      kmap[(y + 1) * nW + q + 1] = __byte_perm(kept[0], kept[1], 0x6420);
-      y += dy; q += dq;
-      if (q >= nG) { q -= nG; y++; }
+      kept[j] = __byte_perm(k2[0], k2[1], 0x6420);
     }
   }
   // "cell empty after NMS at iniThFAST?" (:875-883) is a warp-wide vote
   const bool useIni = __any_sync(0xffffffffu, iniFlag != 0);
   const int thByte = useIni ? iniByte : 1;
   int mine = 0;
-  {
-    int y = y0, q = q0;
-    for (int t = lane; t < nTasks; t += 32) {
-      const uint32_t word = kmap[(y + 1) * nW + q + 1];
-      if (word) {
+  for (int j = lane; j < nQ; j += 32) {  // each lane re-reads only what it wrote
+    const uint32_t word = kept[j];
 #pragma unroll
-        for (int j = 0; j < 4; j++) mine += (int)((word >> (8 * j)) & 0xff) >= thByte;
-      }
-      y += dy; q += dq;
-      if (q >= nG) { q -= nG; y++; }
-    }
+    for (int i = 0; i < 4; i++) mine += (int)((word >> (8 * i)) & 0xff) >= thByte;
   }
   // exclusive prefix of `mine` over the warp + total
   int incl = mine;
@@ -257,28 +261,23 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
     if (base + total > L.candCap) atomicExch(overflow, 1);
   }
   base = __shfl_sync(0xffffffffu, base, 0);
-  __syncwarp();
   int slot = base + incl - mine;
   const long long slotBase = L.candOff + (long long)f * L.candCap;
-  {
-    int y = y0, q = q0;
-    for (int t = lane; t < nTasks; t += 32) {
-      const uint32_t word = kmap[(y + 1) * nW + q + 1];
-      if (word) {
+  for (int j = lane; j < nQ; j += 32) {
+    const uint32_t word = kept[j];
+    if (word) {
+      const int e = queue[j], y = e >> 8, q = e & 0xff;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-          const int s = (word >> (8 * j)) & 0xff;
-          if (s >= thByte) {
-            // cv::FAST's cornerScore = s + minTh - 1; coordinates relative to minBorder:
-            // cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
-            if (slot < L.candCap)
-              cand[slotBase + slot] = pack_cand(4 * (q + 1) + j - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, s + minTh - 1);
-            slot++;
-          }
+      for (int i = 0; i < 4; i++) {
+        const int sc = (word >> (8 * i)) & 0xff;
+        if (sc >= thByte) {
+          // cv::FAST's cornerScore = sc + minTh - 1; coordinates relative to minBorder:
+          // cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
+          if (slot < L.candCap)
+            cand[slotBase + slot] = pack_cand(4 * (q + 1) + i - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, sc + minTh - 1);
+          slot++;
         }
       }
-      y += dy; q += dq;
-      if (q >= nG) { q -= nG; y++; }
     }
   }
 }
