@@ -19,8 +19,9 @@
 // Kernel shape (v3): one WARP per cell, 8 cells per CTA, shared memory sized on the host for the
 // largest cell of the shape. The cell patch is staged word-aligned in shared memory; every lane scores
 // 4 horizontally adjacent pixels per task with branch-free packed 16x2 min/max (VIMNMX3.U16x2):
-// 16 byte->16x2 unpacks and 80 three-input min/max per PAIR of pixels, no divergence, no per-pixel
-// early-outs -- the cost per pixel is content independent. (v1 was one thread per pixel with
+// the patch is staged as 16-bit lanes, so 6 of the 16 ring offsets are plain words and 10 cost one PRMT;
+// 72 packed min/max per PAIR of pixels, no divergence, no per-pixel early-outs -- the cost per pixel
+// of the scoring pass is content independent. (v1 was one thread per pixel with
 // early-outs: ALU-pipe bound at 18/32 active lanes. v2 was one 128-thread CTA per cell: 80 % lane use
 // because sh*nG tasks rarely fill whole rounds of 128; with 32-lane rounds the tail is ~5 %.)
 #include "orbx_common.cuh"
@@ -43,11 +44,20 @@ __device__ __forceinline__ uint32_t ex2(uint32_t w0, uint32_t w1, uint32_t w2) {
   }
 }
 
-// Two adjacent pixels (window bytes BASE, BASE+1 of the centre row): max(m - th, 0) in each 16-bit
-// lane, where m is the corner margin defined above. W[j] = rows y-3+j of the 12-byte window.
+// Pixels C, C+1 of a row staged as 16-bit lanes (W[k] = pixels 2k, 2k+1): free when C is even, one
+// PRMT when it straddles two words.
+template <int C>
+__device__ __forceinline__ uint32_t pair16(const uint32_t (&W)[6]) {
+  if constexpr ((C & 1) == 0) return W[C >> 1];
+  else return __byte_perm(W[C >> 1], W[(C >> 1) + 1], 0x5432);
+}
+
+// Two adjacent pixels (window columns BASE, BASE+1 of the centre row, BASE even): max(m - th, 0) in each
+// 16-bit lane, where m is the corner margin defined above. W[j] = rows y-3+j of the 12-pixel window.
+// 6 of the 16 ring offsets have an even dx and come straight out of the staged words.
 template <int BASE>
-__device__ __forceinline__ uint32_t fast_margin2(const uint32_t (&W)[7][3], uint32_t negThBias) {
-#define ORBX_RING(dx, dy) ex2<BASE + (dx)>(W[(dy) + 3][0], W[(dy) + 3][1], W[(dy) + 3][2])
+__device__ __forceinline__ uint32_t fast_margin2(const uint32_t (&W)[7][6], uint32_t negThBias) {
+#define ORBX_RING(dx, dy) pair16<BASE + (dx)>(W[(dy) + 3])
   uint32_t P[16];
   P[0] = ORBX_RING(0, 3);    P[1] = ORBX_RING(1, 3);    P[2] = ORBX_RING(2, 2);    P[3] = ORBX_RING(3, 1);
   P[4] = ORBX_RING(3, 0);    P[5] = ORBX_RING(3, -1);   P[6] = ORBX_RING(2, -2);   P[7] = ORBX_RING(1, -3);
@@ -89,18 +99,31 @@ __device__ __forceinline__ uint32_t fast_margin2(const uint32_t (&W)[7][3], uint
   return __viaddmax_s16x2_relu(m, negThBias, 0u);           // max(m - th, 0)
 }
 
-// words of shared memory one cell needs: staged patch (ch x nW) + score map ((sh+2) x nW) + the queue of
-// tasks with a non-zero score word (16 bits per task)
+// Upper bound of the margin of two adjacent pixels from the four compass ring pixels (n = (0,3), s = (0,-3),
+// e = (3,0), w = (-3,0)) alone: max(bound - th, 0) per 16-bit lane. See pass 1 of the kernel.
+__device__ __forceinline__ uint32_t fast_compass_bound(uint32_t n, uint32_t s, uint32_t e, uint32_t w, uint32_t v,
+                                                       uint32_t negThBias) {
+  const uint32_t Ac = __vimin3_u16x2(__vmaxu2(n, e), __vmaxu2(e, s), __vminu2(__vmaxu2(s, w), __vmaxu2(w, n)));
+  const uint32_t Bc = __vimax3_u16x2(__vminu2(n, e), __vminu2(e, s), __vmaxu2(__vminu2(s, w), __vminu2(w, n)));
+  const uint32_t dark = v + 0x01000100u - Ac;
+  const uint32_t bright = Bc + 0x01000100u - v;
+  return __viaddmax_s16x2_relu(__vmaxu2(dark, bright), negThBias, 0u);
+}
+
+// words of shared memory one cell needs: patch staged as 16-bit lanes (ch x 2nW) + score map ((sh+2) x nW)
+// + the queue of tasks with a non-zero score word (16 bits per task); even, so that every warp's patch
+// stays 8-byte aligned
 __host__ __device__ inline int fast_cell_words(int wCell, int hCell) {
   const int nW = ((7 + wCell - 1) >> 2) + 2;  // worst alignment: a = 7
-  return (hCell + 6) * nW + (hCell + 2) * nW + (hCell * (nW - 2) + 1) / 2 + 1;
+  const int words = (hCell + 6) * 2 * nW + (hCell + 2) * nW + (hCell * (nW - 2) + 1) / 2 + 1;
+  return (words + 1) & ~1;
 }
 
 __global__ void __launch_bounds__(kFastThreads, 4)
 fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
                   uint32_t* __restrict__ cand, int* __restrict__ candCount, int* __restrict__ overflow,
                   int wordsPerWarp) {
-  extern __shared__ uint32_t smemFast[];
+  extern __shared__ __align__(16) uint32_t smemFast[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * kFastWarps + warp;
   if (cell >= g.totalCells) return;  // warps are independent: no block-wide barrier below
@@ -131,8 +154,8 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   const int nG = (b - 1) >> 2;  // groups q = 0..nG-1 cover tile words 1..nG
   const int nW = nG + 2;        // staged words per row
 
-  uint32_t* tile = smemFast + warp * wordsPerWarp;  // ch rows x nW words
-  uint32_t* smap = tile + ch * nW;                  // (sh+2) rows x nW words, rows 0 and sh+1 stay zero
+  uint32_t* tile = smemFast + warp * wordsPerWarp;  // ch rows x 2nW words: one 16-bit lane per pixel
+  uint32_t* smap = tile + ch * 2 * nW;              // (sh+2) rows x nW words, rows 0 and sh+1 stay zero
   uint16_t* queue = reinterpret_cast<uint16_t*>(smap + (sh + 2) * nW);  // y<<8 | q of the tasks worth a second look
 
   const int pitch = pyr.pitch[level];
@@ -149,7 +172,8 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
       } else {
         w = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
       }
-      tile[r * nW + c] = w;
+      // bytes -> 16-bit lanes once here instead of once per ring offset in the scoring loop
+      *reinterpret_cast<uint2*>(&tile[(r * nW + c) * 2]) = make_uint2(__byte_perm(w, 0u, 0x4140), __byte_perm(w, 0u, 0x4342));
       r += dr; c += dc;
       if (c >= nW) { c -= nW; r++; }
     }
@@ -165,39 +189,64 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   const int dy = 32 / nG, dq = 32 - dy * nG;
   const int y0 = lane / nG, q0 = lane - y0 * nG;
 
-  // ---- score map: max(m - minTh, 0) for every scanned pixel (0 = not a corner at minTh) ----
-  // Rounds are warp-uniform (lanes past the last task idle inside the round) so that the ballot below is
-  // a full-warp one. Only a task whose word holds a corner can keep one after suppression: such tasks are
-  // queued (y<<8 | q) and everything after this loop walks the queue with all 32 lanes busy.
-  int nQ = 0;
+  // ---- pass 1, every task: compass bound. Any 9-arc of the ring contains two adjacent compass pixels
+  //      (p0, p4, p8, p12), so  A >= Ac = min over adjacent compass pairs of their max  and
+  //      B <= Bc = max over those pairs of their min, hence m <= max(v - Ac, Bc - v): a task whose four
+  //      bounds are all <= minTh has an all-zero score word and is dropped after 19 instead of 92 packed
+  //      operations per pixel pair. Survivors are queued as y<<8 | q. Rounds are warp-uniform (lanes past
+  //      the last task idle inside the round) so that the ballots are full-warp ones. ----
+  int nQ1 = 0;
   {
     int y = y0, q = q0;
     for (int t0 = 0; t0 < nTasks; t0 += 32) {
-      uint32_t word = 0u;
+      uint32_t any = 0u;
       if (t0 + lane < nTasks) {
-        const uint32_t* tp = &tile[y * nW + q];
-        uint32_t W[7][3];
-#pragma unroll
-        for (int j = 0; j < 7; j++) {
-          W[j][0] = tp[j * nW];
-          W[j][1] = tp[j * nW + 1];
-          W[j][2] = tp[j * nW + 2];
-        }
-        const uint32_t u01 = fast_margin2<4>(W, negThBias);
-        const uint32_t u23 = fast_margin2<6>(W, negThBias);
-        word = __byte_perm(u01, u23, 0x6420);
-        const int col0 = 4 * (q + 1);
-        const int skipLo = a - col0, skipHi = col0 + 4 - b;
-        if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
-        if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
-        smap[(y + 1) * nW + q + 1] = word;
+        const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);  // window = tile columns 4q..4q+11
+        const uint2 top = tp[1], bot = tp[6 * nW + 1];                             // columns 4..7 of rows y-3, y+3
+        const uint2 c01 = tp[3 * nW], c23 = tp[3 * nW + 1], c45 = tp[3 * nW + 2];
+        const uint32_t C[6] = {c01.x, c01.y, c23.x, c23.y, c45.x, c45.y};
+        any = fast_compass_bound(top.x, bot.x, pair16<7>(C), pair16<1>(C), C[2], negThBias) |
+              fast_compass_bound(top.y, bot.y, pair16<9>(C), pair16<3>(C), C[3], negThBias);
       }
-      const uint32_t liveMask = __ballot_sync(0xffffffffu, word != 0u);
-      if (word != 0u) queue[nQ + __popc(liveMask & ((1u << lane) - 1u))] = (uint16_t)((y << 8) | q);
-      nQ += __popc(liveMask);
+      const uint32_t passMask = __ballot_sync(0xffffffffu, any != 0u);
+      if (any != 0u) queue[nQ1 + __popc(passMask & ((1u << lane) - 1u))] = (uint16_t)((y << 8) | q);
+      nQ1 += __popc(passMask);
       y += dy; q += dq;
       if (q >= nG) { q -= nG; y++; }
     }
+  }
+  __syncwarp();
+  if (nQ1 == 0) return;
+
+  // ---- pass 2, queued tasks: score map max(m - minTh, 0) (0 = not a corner at minTh). Only a task whose
+  //      word holds a corner can keep one after suppression: those are re-queued in place (entry j of
+  //      round k is read before the round's ballot, written slots are <= the ones already read). ----
+  int nQ = 0;
+  for (int j0 = 0; j0 < nQ1; j0 += 32) {
+    uint32_t word = 0u;
+    int e = 0;
+    if (j0 + lane < nQ1) {
+      e = queue[j0 + lane];
+      const int y = e >> 8, q = e & 0xff;
+      const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);
+      uint32_t W[7][6];
+#pragma unroll
+      for (int j = 0; j < 7; j++) {
+        const uint2 w01 = tp[j * nW], w23 = tp[j * nW + 1], w45 = tp[j * nW + 2];
+        W[j][0] = w01.x; W[j][1] = w01.y; W[j][2] = w23.x; W[j][3] = w23.y; W[j][4] = w45.x; W[j][5] = w45.y;
+      }
+      const uint32_t u01 = fast_margin2<4>(W, negThBias);
+      const uint32_t u23 = fast_margin2<6>(W, negThBias);
+      word = __byte_perm(u01, u23, 0x6420);
+      const int col0 = 4 * (q + 1);
+      const int skipLo = a - col0, skipHi = col0 + 4 - b;
+      if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
+      if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
+      smap[(y + 1) * nW + q + 1] = word;
+    }
+    const uint32_t liveMask = __ballot_sync(0xffffffffu, word != 0u);
+    if (word != 0u) queue[nQ + __popc(liveMask & ((1u << lane) - 1u))] = (uint16_t)e;
+    nQ += __popc(liveMask);
   }
   __syncwarp();
   if (nQ == 0) return;
