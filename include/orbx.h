@@ -74,6 +74,11 @@ int orbx_extractor_tables(const orbx_extractor* h, float* scale_factors, float* 
                           float* level_sigma2, float* inv_level_sigma2, int32_t* features_per_level,
                           int32_t* umax16);
 
+/* Shape of the host-buffer pipeline of orbx_extract_batch: frames per chunk and chunks in flight (1..8).
+ * 0 keeps the library default (64 frames, 4 chunks; environment ORBX_CHUNK / ORBX_LANES). Results do not
+ * depend on it. */
+int orbx_extractor_set_pipeline(orbx_extractor* h, int32_t chunk_frames, int32_t lanes);
+
 /* One frame, host buffers: the body of operator() (R/src/ORBextractor.cpp:1120-1188).
  * img: CV_8UC1 rows of `stride` bytes. kps/desc: capacity `cap` rows. *n = keypoints found.
  * Synchronous. ORBX_ERR_CAPACITY if cap is too small (nothing written but *n). */

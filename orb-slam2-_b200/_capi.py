@@ -37,6 +37,7 @@ SIGNATURES = {
     "orbx_extractor_create": (C.c_int, [C.POINTER(Params), C.POINTER(_vp)]),
     "orbx_extractor_destroy": (None, [_vp]),
     "orbx_extractor_tables": (C.c_int, [_vp] + [_vp] * 6),
+    "orbx_extractor_set_pipeline": (C.c_int, [_vp, _i32, _i32]),
     "orbx_extract": (C.c_int, [_vp, _vp, _i32, _i32, _sz, _vp, _vp, _i32, C.POINTER(_i32)]),
     "orbx_extract_batch": (C.c_int, [_vp, C.POINTER(_vp), _i32, _i32, _i32, _sz, _vp, _vp, _i32, _vp]),
     "orbx_extract_batch_device": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _sz, _sz, _vp, _vp, _i32, _vp, _vp]),

@@ -2,11 +2,13 @@
 // setup, arena management, the launch sequence of the extraction pipeline, and host<->device copies
 // for the host-buffer entry points. No CPU implementation of any stage lives here.
 //
-// Host-buffer batches are cut into chunks of kChunk frames that rotate over up to kMaxLanes lanes (stream +
+// Host-buffer batches are cut into chunks of kChunkDefault frames that rotate over up to kMaxLanes lanes (stream +
 // arenas + pinned staging each): while chunk k runs its kernels, chunk k+1's frames cross PCIe and
 // chunk k-1's keypoints/descriptors are scattered into the caller's arrays by the host thread.
 #include <algorithm>
 #include <cstdlib>
+#include <chrono>
+#include <cstdio>
 #include <cstring>
 #include <new>
 
@@ -16,9 +18,16 @@ using namespace orbx;
 
 namespace {
 
-constexpr int kChunkDefault = 32;  // frames per lane submission on the host-buffer path
+constexpr int ChunkTrace_kMaxChunks = 256;  // most chunks one orbx_extract_batch call is cut into
 
-int chunk_frames() {  // ORBX_CHUNK overrides (tuning knob; any value gives identical results)
+// Chunking of a host-buffer batch: fixed chunks of kChunkDefault frames rotate over the lanes. Launches over few
+// frames fill the GPU badly (tools/batch_probe.py: 512 frames cost 3.6 ms in one launch set, 3.9 ms as 4 x 128,
+// 4.3 ms as 8 x 64, 5.1 ms as 16 x 32), large chunks lengthen the pipeline's fill (first H2D) and drain (last
+// D2H); 64 measured best with 4 lanes (profiles/r1_q_e2e_probe.txt; a ramp-up / taper-off schedule of chunk sizes
+// was tried and was no better). ORBX_CHUNK=<n> overrides (tuning knob; any chunking gives identical results).
+constexpr int kChunkDefault = 64;
+
+int chunk_frames() {
   static const int v = [] {
     const char* e = std::getenv("ORBX_CHUNK");
     const int x = e ? std::atoi(e) : 0;
@@ -27,11 +36,57 @@ int chunk_frames() {  // ORBX_CHUNK overrides (tuning knob; any value gives iden
   return v;
 }
 
-int lane_count() {  // ORBX_LANES overrides (1..kMaxLanes)
+struct ChunkPlan {
+  int first[ChunkTrace_kMaxChunks], count[ChunkTrace_kMaxChunks];
+  int n = 0, largest = 0;
+  void add(int f0, int c) { first[n] = f0; count[n] = c; n++; largest = std::max(largest, c); }
+};
+
+bool plan_chunks(int total, int chunk, ChunkPlan* p) {
+  for (int f0 = 0; f0 < total; f0 += chunk) {
+    if (p->n >= ChunkTrace_kMaxChunks) return false;
+    p->add(f0, std::min(chunk, total - f0));
+  }
+  return true;
+}
+
+// ORBX_TRACE=1: per-chunk device timeline of orbx_extract_batch (H2D / kernels / D2H begin-end and the host time of
+// the submit), printed to stderr after the call. A debugging aid for the host-buffer pipeline; off by default.
+struct ChunkTrace {
+  static constexpr int kMax = 64;
+  bool on = false, init = false;
+  cudaEvent_t ev[kMax][4];
+  double hostSubmit[kMax], hostDone[kMax];
+  int n = 0;
+  std::chrono::steady_clock::time_point t0;
+  bool enabled() {
+    if (!init) {
+      init = true;
+      const char* e = std::getenv("ORBX_TRACE");
+      on = e && std::atoi(e) > 0;
+      if (on) for (auto& c : ev) for (auto& x : c) cudaEventCreate(&x);
+    }
+    return on;
+  }
+  double now() const { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
+  void mark(int stage, cudaStream_t s) { if (on && n < kMax) cudaEventRecord(ev[n][stage], s); }
+  void dump() {
+    if (!on || n == 0) return;
+    std::fprintf(stderr, "orbx trace: chunk  host_submit  h2d_begin  h2d_end  kernels_end  d2h_end  host_collected  (ms)\n");
+    for (int c = 0; c < std::min(n, (int)kMax); c++) {
+      float t[4];
+      for (int k = 0; k < 4; k++) cudaEventElapsedTime(&t[k], ev[0][0], ev[c][k]);
+      std::fprintf(stderr, "orbx trace: %5d  %11.3f  %9.3f  %7.3f  %11.3f  %7.3f  %14.3f\n", c, hostSubmit[c], t[0], t[1], t[2], t[3], hostDone[c]);
+    }
+  }
+};
+thread_local ChunkTrace g_trace;
+
+int lane_count() {  // chunks in flight; ORBX_LANES overrides (1..kMaxLanes), default 4
   static const int v = [] {
     const char* e = std::getenv("ORBX_LANES");
     const int x = e ? std::atoi(e) : 0;
-    return x > 0 ? std::min(x, kMaxLanes) : kMaxLanes;
+    return x > 0 ? std::min(x, kMaxLanes) : 4;
   }();
   return v;
 }
@@ -250,11 +305,18 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
   cudaStream_t s = L.stream;
   uint8_t* l0 = static_cast<uint8_t*>(L.pyrArena.p);  // level-0 slot of the arena (planeOff 0)
   bool contiguous = true;
+  if (g_trace.on && g_trace.n < ChunkTrace::kMax) g_trace.hostSubmit[g_trace.n] = g_trace.now();
+  g_trace.mark(0, s);
   for (int f = 0; f < count; f++) {
     if (!imgs[f]) { set_error("imgs[%d] is null", f); return ORBX_ERR_ARG; }
     contiguous = contiguous && imgs[f] == imgs[0] + (size_t)f * stride * height;
   }
-  if (contiguous && g.lv[0].planeBytes == (long long)g.lv[0].pitch * height) {
+  // timing experiments only: ORBX_DEBUG_SKIP_H2D=<n> stops copying frames after the first n chunk submissions
+  // (the lanes then keep re-processing the frames they already hold)
+  static const long dbgSkipAfter = std::getenv("ORBX_DEBUG_SKIP_H2D") ? std::atol(std::getenv("ORBX_DEBUG_SKIP_H2D")) : -1;
+  static long dbgSubmits = 0;
+  if (dbgSkipAfter >= 0 && dbgSubmits++ >= dbgSkipAfter) {
+  } else if (contiguous && g.lv[0].planeBytes == (long long)g.lv[0].pitch * height) {
     // frames back to back on the host: one copy of count*height rows
     if (stride == (size_t)width && g.lv[0].pitch == width)
       ORBX_CUDA_TRY(cudaMemcpyAsync(l0, imgs[0], (size_t)width * height * count, cudaMemcpyHostToDevice, s));
@@ -265,12 +327,14 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
       ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, imgs[f], stride, width, height,
                                       cudaMemcpyHostToDevice, s));
   }
+  g_trace.mark(1, s);
   const int rows = g.keptPerFrame;
   orbx_keypoint* dK = static_cast<orbx_keypoint*>(L.outKps.p);
   uint8_t* dD = static_cast<uint8_t*>(L.outDesc.p);
   int* dN = static_cast<int*>(L.outN.p);
   int rc = run_pipeline(h, L, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, dK, dD, rows, dN, s);
   if (rc) return rc;
+  g_trace.mark(2, s);
   HostStage st = stage_of(L);
   const int* dOverflow = static_cast<const int*>(L.counts.p) + 2 * L.batchCap * g.nlevels;
   ORBX_CUDA_TRY(cudaMemcpyAsync(st.n, dN, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -286,6 +350,8 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
     ORBX_CUDA_TRY(cudaMemcpyAsync(st.kps, dK, (size_t)count * rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
     ORBX_CUDA_TRY(cudaMemcpyAsync(st.desc, dD, (size_t)count * rows * 32, cudaMemcpyDeviceToHost, s));
   }
+  g_trace.mark(3, s);
+  if (g_trace.on) g_trace.n++;
   ORBX_CUDA_TRY(cudaEventRecord(L.done, s));
   return ORBX_OK;
 }
@@ -431,31 +497,37 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
     return ORBX_ERR_ARG;
   }
   ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
-  const int chunk = std::min(chunk_frames(), count);
-  const int nchunks = (count + chunk - 1) / chunk;
-  const int nlanes = std::min(nchunks, lane_count());
+  ChunkPlan plan;
+  if (!plan_chunks(count, h->chunkFrames > 0 ? h->chunkFrames : chunk_frames(), &plan)) { set_error("batch of %d frames needs more than %d chunks (raise ORBX_CHUNK)", count, ChunkTrace_kMaxChunks); return ORBX_ERR_ARG; }
+  const int nchunks = plan.n;
+  const int nlanes = std::min(nchunks, h->laneCount > 0 ? h->laneCount : lane_count());
   int rc;
   for (int i = 0; i < nlanes; i++) {
-    if ((rc = ensure_lane(h, h->lane[i], width, height, chunk))) return rc;
+    if ((rc = ensure_lane(h, h->lane[i], width, height, plan.largest))) return rc;
     if ((rc = ensure_lane_staging(h->lane[i]))) return rc;
   }
   bool tooSmall = false;
+  if (g_trace.enabled()) { g_trace.n = 0; g_trace.t0 = std::chrono::steady_clock::now(); }
+  int collected = 0;
   const bool direct = is_pinned(kps, (size_t)count * cap * sizeof(orbx_keypoint)) && is_pinned(desc, (size_t)count * cap * 32);
   auto out_at = [&](int f0) { return HostOut{kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, direct}; };
   for (int c = 0; c <= nchunks; c++) {
     if (c < nchunks) {
-      const int f0 = c * chunk, cnt = std::min(chunk, count - f0);
+      const int f0 = plan.first[c], cnt = plan.count[c];
       if (c >= nlanes) {  // the lane's staging still holds chunk c-nlanes: scatter it before reusing the lane
-        const int g0 = (c - nlanes) * chunk, gc = std::min(chunk, count - g0);
+        const int g0 = plan.first[c - nlanes], gc = plan.count[c - nlanes];
         if ((rc = collect_chunk(h, h->lane[c % nlanes], gc, out_at(g0), n + g0, &tooSmall))) return rc;
+        if (g_trace.on && collected < ChunkTrace::kMax) g_trace.hostDone[collected++] = g_trace.now();
       }
       if ((rc = submit_chunk(h, h->lane[c % nlanes], imgs + f0, cnt, width, height, stride, out_at(f0)))) return rc;
     }
   }
   for (int c = std::max(nchunks - nlanes, 0); c < nchunks; c++) {
-    const int f0 = c * chunk, cnt = std::min(chunk, count - f0);
+    const int f0 = plan.first[c], cnt = plan.count[c];
     if ((rc = collect_chunk(h, h->lane[c % nlanes], cnt, out_at(f0), n + f0, &tooSmall))) return rc;
+    if (g_trace.on && collected < ChunkTrace::kMax) g_trace.hostDone[collected++] = g_trace.now();
   }
+  g_trace.dump();
   if (nchunks > 1) h->haveResult = false;  // introspection only covers single-chunk batches
   if (tooSmall) { set_error("keypoint capacity %d too small (see n[])", cap); return ORBX_ERR_CAPACITY; }
   return ORBX_OK;

@@ -109,6 +109,13 @@ int orbx_get_level_candidates(orbx_extractor* h, int32_t frame, int32_t level, i
 
 int64_t orbx_launch_count(const orbx_extractor* h) { return h ? h->launches : 0; }
 
+int orbx_extractor_set_pipeline(orbx_extractor* h, int32_t chunk_frames, int32_t lanes) {
+  if (!h || chunk_frames < 0 || lanes < 0 || lanes > orbx::kMaxLanes) { set_error("null/invalid argument"); return ORBX_ERR_ARG; }
+  h->chunkFrames = chunk_frames;
+  h->laneCount = lanes;
+  return ORBX_OK;
+}
+
 int orbx_set_profiling(orbx_extractor* h, int32_t enable) {
   if (!h) { set_error("null handle"); return ORBX_ERR_ARG; }
   h->profiling = enable != 0;

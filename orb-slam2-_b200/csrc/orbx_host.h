@@ -37,7 +37,7 @@ struct DeviceBuf {
 
 namespace orbx {
 
-constexpr int kMaxLanes = 4;
+constexpr int kMaxLanes = 8;
 
 // One in-flight batch: a stream, its device arenas and pinned staging. The host-buffer entry points
 // rotate over the lanes so that the H2D copy of chunk k+1, the kernels of chunk k and the D2H +
@@ -63,6 +63,7 @@ struct orbx_extractor {
   orbx::CtorTables tables;
   orbx::Lane lane[orbx::kMaxLanes];
   bool profiling = false;
+  int chunkFrames = 0, laneCount = 0;  // host-buffer pipeline shape; 0 = library default / environment
   float stageMs[6] = {};
   long long launches = 0;
 

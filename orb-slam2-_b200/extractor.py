@@ -95,6 +95,10 @@ class ORBextractor:
         check(lib().orbx_extract_batch(self._h, arr, cnt, w, h, stride, ptr(kps), ptr(desc), cap, ptr(n)))
         return [(kps[f, :n[f]].copy(), desc[f, :n[f]].copy()) for f in range(cnt)]
 
+    def set_pipeline(self, chunk_frames=0, lanes=0):
+        """Frames per chunk / chunks in flight of the host-buffer batch path (0 = library default)."""
+        check(lib().orbx_extractor_set_pipeline(self._h, chunk_frames, lanes))
+
     def extract_batch_into(self, frames, kps, desc, n):
         """orbx_extract_batch on a (B, H, W) uint8 host array (ideally pinned) into caller-owned outputs:
         kps (B, cap) KP_DTYPE, desc (B, cap, 32) uint8, n (B,) int32. No per-frame Python work: this is the

@@ -174,6 +174,7 @@ def test_chunked_host_batch_equals_single(pkg, oracle):
     B = 70
     frames = np.stack([pkg.synth.frame(320, 240, 200 + i) for i in range(B)])
     ex = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240, max_batch=128)
+    ex.set_pipeline(chunk_frames=8, lanes=3)   # 9 chunks over 3 lanes: every lane is reused twice
     cap = 700
     kps = np.empty((B, cap), pkg.KP_DTYPE)
     desc = np.empty((B, cap, 32), np.uint8)
@@ -205,6 +206,7 @@ def test_pinned_outputs_take_rows_directly(pkg, cap):
     for i in range(B):
         frames[i] = pkg.synth.frame(320, 240, 300 + i)
     ex = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240, max_batch=128)
+    ex.set_pipeline(chunk_frames=16, lanes=4)  # 5 chunks over 4 lanes
     big = 700
     rk, rd, rn = np.empty((B, big), pkg.KP_DTYPE), np.empty((B, big, 32), np.uint8), np.zeros(B, np.int32)
     ex.extract_batch_into(frames, rk, rd, rn)

@@ -14,7 +14,9 @@ sys.path.insert(0, str(ROOT))
 
 
 def one(lanes, chunk, B=512):
-    os.environ["ORBX_LANES"], os.environ["ORBX_CHUNK"] = str(lanes), str(chunk)
+    os.environ["ORBX_LANES"] = str(lanes)
+    if chunk > 0:
+        os.environ["ORBX_CHUNK"] = str(chunk)   # 0 = the library default
     pkg = importlib.import_module("orb-slam2-_b200")
     W, H = 640, 480
     frames = pkg.pinned_empty((B, H, W), np.uint8)
@@ -38,5 +40,5 @@ if __name__ == "__main__":
     if len(sys.argv) == 3:
         one(int(sys.argv[1]), int(sys.argv[2]))
     else:
-        for lanes, chunk in [(1, 512), (2, 256), (4, 128), (2, 128), (4, 64), (3, 64), (2, 64), (4, 32), (4, 16), (1, 32)]:
+        for lanes, chunk in [(4, 0), (1, 512), (2, 256), (4, 128), (3, 64), (4, 64), (6, 64), (4, 32), (8, 32), (8, 16)]:
             subprocess.run([sys.executable, __file__, str(lanes), str(chunk)], check=False)
