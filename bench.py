@@ -42,6 +42,24 @@ WORKLOAD = ("C1: ORBextractor::operator() on 640x480 u8 frames, 1000 features, 8
             "FAST 20/7 (TUM1.yaml)")
 
 
+# The other extraction shapes BASELINE.json names (parity-test cases; `--workload` reports their throughput too,
+# the default and the driver's line stay C1). Frames per step keep ~150 MB of distinct input per step.
+WORKLOADS = {
+    "C1": (640, 480, 1000, 512, METRIC, WORKLOAD),
+    "C2": (1241, 376, 2000, 320, "ORB frames/s (1241x376, 2000 kp)",
+           "C2 shape: KITTI 1241x376 stereo images, 2000 features per image (left and right frames are independent frames "
+           "of the batch; row matching is orbx_stereo_match, timed in tools/match_probe.py)"),
+    "C3": (752, 480, 1200, 416, "ORB frames/s (752x480, 1200 kp)", "C3 shape: EuRoC 752x480 frames, 1200 features, sharded by frames"),
+    "C4": (1920, 1080, 4000, 72, "ORB frames/s (1920x1080, 4000 kp)", "C4: 1920x1080 frames, 4000 features, 8 levels, batched"),
+}
+
+
+def select_workload(name):
+    global W, H, NFEAT, FRAMES_PER_STEP, E2E_FRAMES_PER_STEP, METRIC, WORKLOAD
+    W, H, NFEAT, FRAMES_PER_STEP, METRIC, WORKLOAD = WORKLOADS[name]
+    E2E_FRAMES_PER_STEP = FRAMES_PER_STEP
+
+
 def level_sizes():
     inv = [np.float32(1.0)]
     sc = [np.float32(1.0)]
@@ -455,7 +473,9 @@ def main():
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs only: skip the CPU baseline leg")
     ap.add_argument("--skip-hamming", action="store_true", help="profiling runs only: skip the Hamming (config 5) leg")
+    ap.add_argument("--workload", default="C1", choices=sorted(WORKLOADS), help="extraction shape (default: the metric's C1)")
     args = ap.parse_args()
+    select_workload(args.workload)
     if args.impl == "reference":
         return run_reference(args)
     return run_gpu(args)

@@ -25,15 +25,17 @@ constexpr int ChunkTrace_kMaxChunks = 256;  // most chunks one orbx_extract_batc
 // 4.3 ms as 8 x 64, 5.1 ms as 16 x 32), large chunks lengthen the pipeline's fill (first H2D) and drain (last
 // D2H); 64 measured best with 4 lanes (profiles/r1_q_e2e_probe.txt; a ramp-up / taper-off schedule of chunk sizes
 // was tried and was no better). ORBX_CHUNK=<n> overrides (tuning knob; any chunking gives identical results).
-constexpr int kChunkDefault = 64;
+constexpr int kChunkDefault = 64;                         // at 640x480; other shapes keep the bytes per chunk
+constexpr long long kChunkBytes = 64LL * 640 * 480;       // ~20 MB of frames per chunk
 
-int chunk_frames() {
+int chunk_frames(int width, int height) {
   static const int v = [] {
     const char* e = std::getenv("ORBX_CHUNK");
     const int x = e ? std::atoi(e) : 0;
-    return x > 0 ? x : kChunkDefault;
+    return x > 0 ? x : 0;
   }();
-  return v;
+  if (v) return v;
+  return (int)std::max(4LL, std::min((long long)kChunkDefault, kChunkBytes / ((long long)width * height)));
 }
 
 struct ChunkPlan {
@@ -318,10 +320,17 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
   if (dbgSkipAfter >= 0 && dbgSubmits++ >= dbgSkipAfter) {
   } else if (contiguous && g.lv[0].planeBytes == (long long)g.lv[0].pitch * height) {
     // frames back to back on the host: one copy of count*height rows
-    if (stride == (size_t)width && g.lv[0].pitch == width)
+    if (stride == (size_t)width && g.lv[0].pitch == width) {
       ORBX_CUDA_TRY(cudaMemcpyAsync(l0, imgs[0], (size_t)width * height * count, cudaMemcpyHostToDevice, s));
-    else
+    } else if (stride == (size_t)width) {
+      // tightly packed rows whose width is not the arena pitch (e.g. 1241): a row-by-row DMA over PCIe is slow, so
+      // the bytes cross flat into the blur arena (unused until the blur stage) and are re-pitched on the device
+      uint8_t* flat = static_cast<uint8_t*>(L.blurArena.p);
+      ORBX_CUDA_TRY(cudaMemcpyAsync(flat, imgs[0], (size_t)width * height * count, cudaMemcpyHostToDevice, s));
+      ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0, g.lv[0].pitch, flat, width, width, (size_t)height * count, cudaMemcpyDeviceToDevice, s));
+    } else {
       ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0, g.lv[0].pitch, imgs[0], stride, width, (size_t)height * count, cudaMemcpyHostToDevice, s));
+    }
   } else {
     for (int f = 0; f < count; f++)
       ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, imgs[f], stride, width, height,
@@ -480,9 +489,13 @@ int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_imgs, int32_t 
     // the kernels read rows as aligned 32-bit words: stage unaligned frames in the arena's level-0 slot
     const FrameSetGeom& g = L.geom;
     uint8_t* l0 = static_cast<uint8_t*>(L.pyrArena.p);
-    for (int f = 0; f < count; f++)
-      ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, d_imgs + (size_t)f * frame_stride,
-                                      row_stride, width, height, cudaMemcpyDeviceToDevice, s));
+    if (frame_stride == row_stride * (size_t)height && g.lv[0].planeBytes == (long long)g.lv[0].pitch * height) {
+      ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0, g.lv[0].pitch, d_imgs, row_stride, width, (size_t)height * count, cudaMemcpyDeviceToDevice, s));
+    } else {
+      for (int f = 0; f < count; f++)
+        ORBX_CUDA_TRY(cudaMemcpy2DAsync(l0 + (size_t)f * g.lv[0].planeBytes, g.lv[0].pitch, d_imgs + (size_t)f * frame_stride,
+                                        row_stride, width, height, cudaMemcpyDeviceToDevice, s));
+    }
     return run_pipeline(h, L, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, d_kps, d_desc, cap, d_n, s);
   }
   return run_pipeline(h, L, d_imgs, (int)row_stride, (long long)frame_stride, count, d_kps, d_desc, cap, d_n, s);
@@ -498,7 +511,7 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
   }
   ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
   ChunkPlan plan;
-  if (!plan_chunks(count, h->chunkFrames > 0 ? h->chunkFrames : chunk_frames(), &plan)) { set_error("batch of %d frames needs more than %d chunks (raise ORBX_CHUNK)", count, ChunkTrace_kMaxChunks); return ORBX_ERR_ARG; }
+  if (!plan_chunks(count, h->chunkFrames > 0 ? h->chunkFrames : chunk_frames(width, height), &plan)) { set_error("batch of %d frames needs more than %d chunks (raise ORBX_CHUNK)", count, ChunkTrace_kMaxChunks); return ORBX_ERR_ARG; }
   const int nchunks = plan.n;
   const int nlanes = std::min(nchunks, h->laneCount > 0 ? h->laneCount : lane_count());
   int rc;

@@ -222,3 +222,32 @@ def test_pinned_outputs_take_rows_directly(pkg, cap):
         if rn[f] <= cap:
             assert np.array_equal(pk[f, :m].view(np.uint8), rk[f, :m].view(np.uint8)), f
             assert np.array_equal(pd[f, :m], rd[f, :m]), f
+
+
+@pytest.mark.parametrize("w,h", [(321, 240), (1241, 376)])
+def test_odd_width_batch_equals_single(pkg, w, h):
+    """Tightly packed frames whose width is not a multiple of the arena pitch cross PCIe flat and are re-pitched on the
+    device (host batch), or re-pitched with one 2-D copy (device batch): same rows as single-frame calls."""
+    import torch
+    B = 6
+    frames = np.stack([pkg.synth.frame(w, h, 400 + i) for i in range(B)])
+    ex = pkg.ORBextractor(800, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    ex.set_pipeline(chunk_frames=4, lanes=2)
+    cap = 1000
+    kps, desc, n = np.empty((B, cap), pkg.KP_DTYPE), np.empty((B, cap, 32), np.uint8), np.zeros(B, np.int32)
+    ex.extract_batch_into(frames, kps, desc, n)
+    d_frames = torch.from_numpy(frames).cuda()
+    dk = torch.zeros((B, cap, 7), dtype=torch.float32, device="cuda")
+    dd = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+    dn = torch.zeros(B, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ex.extract_batch_device(d_frames.data_ptr(), B, w, h, w, w * h, dk.data_ptr(), dd.data_ptr(), cap, dn.data_ptr())
+    torch.cuda.synchronize()
+    single = pkg.ORBextractor(800, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    for f in range(B):
+        sk, sd = single(frames[f])
+        assert n[f] == len(sk) == int(dn[f])
+        assert np.array_equal(kps[f, :n[f]].view(np.uint8), sk.view(np.uint8)), f
+        assert np.array_equal(desc[f, :n[f]], sd), f
+        assert np.array_equal(dk[f, :n[f]].cpu().numpy().view(np.uint8).reshape(-1), sk.view(np.uint8).reshape(-1)), f
+        assert np.array_equal(dd[f, :n[f]].cpu().numpy(), sd), f
