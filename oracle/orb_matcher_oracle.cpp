@@ -209,11 +209,14 @@ int orb_oracle_search_for_initialization(const orb_oracle_keypoint* kps1, const 
 // R/src/ORBmatcher.cpp:63-163. The map-point side is given as arrays: projection (u,v), search radius
 // r = RadiusByViewingCos(viewCos)*th (:85-89), predicted level, projected right coordinate, descriptor.
 // has_mp[idx] != 0 <=> F.mvpMapPoints[idx] && Observations()>0 (:118-121); mp_match[iMP] = keypoint or -1.
+// mp_has_obs[iMP] != 0 <=> pMP->Observations()>0 (null: every point has observations): a keypoint taken by a point
+// WITHOUT observations stays available to later points (:118-121 test the slot's point, :157 overwrites it).
 int orb_oracle_search_by_projection_mp(const orb_oracle_keypoint* kps_un, const uint8_t* desc, int n,
                                        const float* uright, const uint8_t* has_mp, float min_x, float max_x,
                                        float min_y, float max_y, const float* mp_uv, const float* mp_r,
                                        const int32_t* mp_level, const float* mp_ur, const uint8_t* mp_desc, int nmp,
-                                       const float* scale_factors, float nnratio, int32_t* mp_match) {
+                                       const float* scale_factors, float nnratio, int32_t* mp_match,
+                                       const uint8_t* mp_has_obs) {
   Grid g;
   g.build(kps_un, n, min_x, max_x, min_y, max_y);
   std::vector<uint8_t> owned(has_mp, has_mp + n);
@@ -244,7 +247,7 @@ int orb_oracle_search_by_projection_mp(const orb_oracle_keypoint* kps_un, const 
     if (bestDist <= kThHigh) {
       if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
       mp_match[iMP] = bestIdx;
-      owned[bestIdx] = 1;  // F.mvpMapPoints[bestIdx]=pMP: later map points skip it (a tracked point has observations)
+      owned[bestIdx] = mp_has_obs ? (mp_has_obs[iMP] != 0) : 1;  // F.mvpMapPoints[bestIdx]=pMP (:157)
       nmatches++;
     }
   }
@@ -259,7 +262,7 @@ int orb_oracle_search_by_projection_frame(const orb_oracle_keypoint* kps_un, con
                                           float min_y, float max_y, const float* q_uv, const float* q_r,
                                           const int32_t* q_min_level, const int32_t* q_max_level, const float* q_ur,
                                           const float* q_angle, const uint8_t* q_desc, int nq, int th_dist,
-                                          int check_orientation, int32_t* cur_match) {
+                                          int check_orientation, int32_t* cur_match, const uint8_t* q_has_obs) {
   Grid g;
   g.build(kps_un, n, min_x, max_x, min_y, max_y);
   std::vector<uint8_t> owned(has_mp, has_mp + n);
@@ -283,7 +286,7 @@ int orb_oracle_search_by_projection_frame(const orb_oracle_keypoint* kps_un, con
     }
     if (bestDist <= th_dist) {
       cur_match[bestIdx2] = i;
-      owned[bestIdx2] = 1;
+      owned[bestIdx2] = q_has_obs ? (q_has_obs[i] != 0) : 1;  // the slot now holds pMP (:1675)
       nmatches++;
       if (check_orientation) rotHist[rot_bin(q_angle[i], kps_un[bestIdx2].angle)].push_back(bestIdx2);
     }

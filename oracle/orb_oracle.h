@@ -90,7 +90,8 @@ int orb_oracle_search_by_projection_mp(const orb_oracle_keypoint* kps_un, const 
                                        float min_x, float max_x, float min_y, float max_y,
                                        const float* mp_uv, const float* mp_r, const int32_t* mp_level,
                                        const float* mp_ur, const uint8_t* mp_desc, int nmp,
-                                       const float* scale_factors, float nnratio, int32_t* mp_match /* nmp */);
+                                       const float* scale_factors, float nnratio, int32_t* mp_match /* nmp */,
+                                       const uint8_t* mp_has_obs /* nmp: Observations()>0, or NULL = all */);
 /* SearchByProjection(Frame& cur, const Frame& last, th, mono) (ORBmatcher.cpp:1564-1718) after projection */
 int orb_oracle_search_by_projection_frame(const orb_oracle_keypoint* kps_un, const uint8_t* desc, int n,
                                           const float* uright, const uint8_t* has_mp,
@@ -98,7 +99,8 @@ int orb_oracle_search_by_projection_frame(const orb_oracle_keypoint* kps_un, con
                                           const float* q_uv, const float* q_r, const int32_t* q_min_level,
                                           const int32_t* q_max_level, const float* q_ur, const float* q_angle,
                                           const uint8_t* q_desc, int nq, int th_dist, int check_orientation,
-                                          int32_t* cur_match /* n: query index or -1 */);
+                                          int32_t* cur_match /* n: query index or -1 */,
+                                          const uint8_t* q_has_obs /* nq: Observations()>0, or NULL = all */);
 /* Frame::ComputeStereoMatches (Frame.cpp:551-770) */
 int orb_oracle_stereo_matches(const orb_oracle_keypoint* kps_l, const uint8_t* desc_l, int nl,
                               const orb_oracle_keypoint* kps_r, const uint8_t* desc_r, int nr,

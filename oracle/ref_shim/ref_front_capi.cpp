@@ -1,0 +1,231 @@
+// TEST INFRASTRUCTURE (oracle/_ref) -- C entry points around the REFERENCE's own Frame / ORBmatcher / MapPoint
+// code: R/src/Frame.cpp, R/src/ORBmatcher.cpp, R/src/MapPoint.cpp, R/src/Map.cpp and R/src/ORBextractor.cpp
+// compiled where they lie against the cv shim in this directory (Converter.h and the DBoW2 vocabulary headers
+// are shadowed by declarations-only stubs: Eigen is not installed and bag-of-words is out of the hot path).
+//
+// Used only by tests/ to pin the matcher / stereo rows of SURVEY.md 8a against the reference's code itself:
+//   Frame::Frame (mono, stereo)            R/src/Frame.cpp:67-128, 187-250   (extraction, grid, ComputeStereoMatches)
+//   ORBmatcher::SearchForInitialization    R/src/ORBmatcher.cpp:499-617
+//   ORBmatcher::SearchByProjection(F, vpMapPoints, th)           :63-163
+//   ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, ...)  :1564-1718
+// The harness builds real Frame and MapPoint objects, calls the reference's member functions and copies plain
+// arrays out. Nothing here re-implements the functions under test.
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "Frame.h"
+#include "Map.h"
+#include "MapPoint.h"
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+
+using namespace ORB_SLAM2;
+
+struct ref_keypoint { float x, y, size, angle, response; int32_t octave, class_id; };
+
+namespace {
+
+struct Front {
+  ORBextractor *left, *right;
+  cv::Mat K, distCoef;
+  float bf, thDepth;
+  Map map;
+  std::vector<MapPoint*> points;  // owned
+};
+
+void put_keys(const std::vector<cv::KeyPoint>& keys, ref_keypoint* out) {
+  if (!out) return;
+  for (size_t i = 0; i < keys.size(); i++) {
+    out[i].x = keys[i].pt.x; out[i].y = keys[i].pt.y; out[i].size = keys[i].size; out[i].angle = keys[i].angle;
+    out[i].response = keys[i].response; out[i].octave = keys[i].octave; out[i].class_id = keys[i].class_id;
+  }
+}
+
+cv::Mat wrap(const uint8_t* img, int w, int h, int stride) {
+  return cv::Mat(h, w, CV_8UC1, const_cast<uint8_t*>(img), (size_t)stride);
+}
+
+}  // namespace
+
+extern "C" {
+
+void* ref_front_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, float fx, float fy, float cx,
+                       float cy, float bf, float thDepth) {
+  Front* f = new Front();
+  f->left = new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+  f->right = new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+  f->K = cv::Mat::eye(3, 3, CV_32F);
+  f->K.at<float>(0, 0) = fx; f->K.at<float>(1, 1) = fy; f->K.at<float>(0, 2) = cx; f->K.at<float>(1, 2) = cy;
+  f->distCoef = cv::Mat::zeros(4, 1, CV_32F);  // the hot path works on the image as given
+  f->bf = bf; f->thDepth = thDepth;
+  // image bounds and grid cell sizes are process-wide statics set by the first Frame (R/src/Frame.cpp:222-240)
+  Frame::mbInitialComputations = true;
+  return f;
+}
+
+void ref_front_destroy(void* h) {
+  Front* f = static_cast<Front*>(h);
+  for (MapPoint* p : f->points) delete p;
+  delete f->left; delete f->right;
+  delete f;
+}
+
+// R/src/Frame.cpp:187-250: extraction, UndistortKeyPoints (identity here), image bounds, AssignFeaturesToGrid
+void* ref_frame_mono(void* h, const uint8_t* img, int w, int hgt, int stride) {
+  Front* f = static_cast<Front*>(h);
+  return new Frame(wrap(img, w, hgt, stride), 0.0, f->left, static_cast<ORBVocabulary*>(nullptr), f->K, f->distCoef, f->bf,
+                   f->thDepth);
+}
+
+// R/src/Frame.cpp:67-128: two extraction threads, then ComputeStereoMatches (:551-770)
+void* ref_frame_stereo(void* h, const uint8_t* imgL, const uint8_t* imgR, int w, int hgt, int stride) {
+  Front* f = static_cast<Front*>(h);
+  return new Frame(wrap(imgL, w, hgt, stride), wrap(imgR, w, hgt, stride), 0.0, f->left, f->right,
+                   static_cast<ORBVocabulary*>(nullptr), f->K, f->distCoef, f->bf, f->thDepth);
+}
+
+void ref_frame_destroy(void* fr) { delete static_cast<Frame*>(fr); }
+int ref_frame_n(void* fr) { return static_cast<Frame*>(fr)->N; }
+int ref_frame_n_right(void* fr) { return (int)static_cast<Frame*>(fr)->mvKeysRight.size(); }
+
+// any output may be null; bounds = mnMinX, mnMaxX, mnMinY, mnMaxY; mb = baseline
+void ref_frame_get(void* fr, ref_keypoint* keys, ref_keypoint* keysUn, uint8_t* desc, float* uRight, float* depth,
+                   float* bounds, float* mb) {
+  Frame& F = *static_cast<Frame*>(fr);
+  put_keys(F.mvKeys, keys);
+  put_keys(F.mvKeysUn, keysUn);
+  if (desc) for (int i = 0; i < F.N; i++) std::memcpy(desc + (size_t)i * 32, F.mDescriptors.ptr(i), 32);
+  if (uRight) for (int i = 0; i < F.N; i++) uRight[i] = F.mvuRight[i];
+  if (depth) for (int i = 0; i < F.N; i++) depth[i] = F.mvDepth[i];
+  if (bounds) { bounds[0] = Frame::mnMinX; bounds[1] = Frame::mnMaxX; bounds[2] = Frame::mnMinY; bounds[3] = Frame::mnMaxY; }
+  if (mb) *mb = F.mb;
+}
+
+void ref_frame_get_right(void* fr, ref_keypoint* keys, uint8_t* desc) {
+  Frame& F = *static_cast<Frame*>(fr);
+  put_keys(F.mvKeysRight, keys);
+  if (desc) for (size_t i = 0; i < F.mvKeysRight.size(); i++) std::memcpy(desc + i * 32, F.mDescriptorsRight.ptr((int)i), 32);
+}
+
+// level `level` of the pyramid the frame's left (side 0) / right (side 1) extractor holds
+void ref_front_level(void* h, int side, int level, int* w, int* hgt, uint8_t* dst, int dstride) {
+  Front* f = static_cast<Front*>(h);
+  const cv::Mat& m = (side ? f->right : f->left)->mvImagePyramid[level];
+  if (w) *w = m.cols;
+  if (hgt) *hgt = m.rows;
+  if (dst) for (int r = 0; r < m.rows; r++) std::memcpy(dst + (size_t)r * dstride, m.ptr(r), (size_t)m.cols);
+}
+
+// Tcw: 4x4 row-major world-to-camera pose (Frame::SetPose -> UpdatePoseMatrices, R/src/Frame.cpp:276-295)
+void ref_frame_set_pose(void* fr, const float* Tcw) {
+  cv::Mat T(4, 4, CV_32F);
+  for (int i = 0; i < 16; i++) T.at<float>(i / 4, i % 4) = Tcw[i];
+  static_cast<Frame*>(fr)->SetPose(T);
+}
+
+// vbPrevMatched (n1 x 2 floats) is read and updated like the reference's argument; returns the match count
+int ref_search_for_initialization(void* fr1, void* fr2, float* prevMatched, int* matches12, int windowSize, float nnratio,
+                                  int checkOri) {
+  Frame &F1 = *static_cast<Frame*>(fr1), &F2 = *static_cast<Frame*>(fr2);
+  std::vector<cv::Point2f> prev(F1.mvKeysUn.size());
+  for (size_t i = 0; i < prev.size(); i++) prev[i] = cv::Point2f(prevMatched[2 * i], prevMatched[2 * i + 1]);
+  std::vector<int> m12;
+  ORBmatcher matcher(nnratio, checkOri != 0);
+  const int n = matcher.SearchForInitialization(F1, F2, prev, m12, windowSize);
+  for (size_t i = 0; i < prev.size(); i++) { prevMatched[2 * i] = prev[i].x; prevMatched[2 * i + 1] = prev[i].y; }
+  for (size_t i = 0; i < m12.size(); i++) matches12[i] = m12[i];
+  return n;
+}
+
+// ---- map points ----------------------------------------------------------------------------------------
+// MapPoint(Pos, pMap, pFrame, idxF) (R/src/MapPoint.cpp:64-93): descriptor = row idxF of the frame's descriptors.
+// The frame needs a pose (ref_frame_set_pose) first. Returns an index into the front's point table.
+int ref_map_point_create(void* h, void* fr, int idx, const float* pos) {
+  Front* f = static_cast<Front*>(h);
+  cv::Mat P(3, 1, CV_32F);
+  for (int i = 0; i < 3; i++) P.at<float>(i) = pos[i];
+  f->points.push_back(new MapPoint(P, &f->map, static_cast<Frame*>(fr), idx));
+  return (int)f->points.size() - 1;
+}
+
+// the fields Frame::isInFrustum leaves on a point for SearchByProjection (R/src/Frame.cpp:360-366)
+void ref_map_point_set_track(void* h, int mp, int inView, float u, float v, float uR, int level, float viewCos) {
+  MapPoint* p = static_cast<Front*>(h)->points[mp];
+  p->mbTrackInView = inView != 0;
+  p->mTrackProjX = u; p->mTrackProjY = v; p->mTrackProjXR = uR;
+  p->mnTrackScaleLevel = level;
+  p->mTrackViewCos = viewCos;
+}
+
+// nObs is what Observations() returns (normally maintained by AddObservation with key frames, which are outside
+// this harness)
+void ref_map_point_set_nobs(void* h, int mp, int nObs) { static_cast<Front*>(h)->points[mp]->nObs = nObs; }
+
+// mp < 0 clears the slot
+void ref_frame_set_map_point(void* h, void* fr, int idx, int mp) {
+  static_cast<Frame*>(fr)->mvpMapPoints[idx] = mp < 0 ? static_cast<MapPoint*>(nullptr) : static_cast<Front*>(h)->points[mp];
+}
+void ref_frame_set_outlier(void* fr, int idx, int outlier) { static_cast<Frame*>(fr)->mvbOutlier[idx] = outlier != 0; }
+
+// out[i] = index of the map point attached to keypoint i of the frame, -1 for none
+void ref_frame_get_map_points(void* h, void* fr, int* out) {
+  Front* f = static_cast<Front*>(h);
+  Frame& F = *static_cast<Frame*>(fr);
+  for (int i = 0; i < F.N; i++) {
+    out[i] = -1;
+    if (!F.mvpMapPoints[i]) continue;
+    for (size_t k = 0; k < f->points.size(); k++)
+      if (f->points[k] == F.mvpMapPoints[i]) { out[i] = (int)k; break; }
+  }
+}
+
+// R/src/ORBmatcher.cpp:63-163 on the points mps[0..nmp)
+int ref_search_by_projection_mp(void* h, void* fr, const int* mps, int nmp, float th, float nnratio, int checkOri) {
+  Front* f = static_cast<Front*>(h);
+  std::vector<MapPoint*> v(nmp);
+  for (int i = 0; i < nmp; i++) v[i] = f->points[mps[i]];
+  ORBmatcher matcher(nnratio, checkOri != 0);
+  return matcher.SearchByProjection(*static_cast<Frame*>(fr), v, th);
+}
+
+// R/src/ORBmatcher.cpp:1564-1718
+int ref_search_by_projection_frame(void* cur, void* last, float th, int bMono, float nnratio, int checkOri) {
+  ORBmatcher matcher(nnratio, checkOri != 0);
+  return matcher.SearchByProjection(*static_cast<Frame*>(cur), *static_cast<Frame*>(last), th, bMono != 0);
+}
+
+// The projection of the last frame's points into the current frame that SearchByProjection performs before its
+// windowed search (:1574-1611, same expressions on the same Mat arithmetic), exported so that the test can hand
+// identical queries to the oracle and to the CUDA path. Per last-frame keypoint i: valid[i] (has a non-outlier
+// point that projects inside the image bounds with positive depth), u, v, invzc. Also *forward / *backward.
+void ref_project_last_frame(void* curp, void* lastp, int bMono, uint8_t* valid, float* u, float* v, float* invz,
+                            int* forward, int* backward) {
+  Frame &CurrentFrame = *static_cast<Frame*>(curp), &LastFrame = *static_cast<Frame*>(lastp);
+  const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+  const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+  const cv::Mat twc = -Rcw.t() * tcw;
+  const cv::Mat Rlw = LastFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+  const cv::Mat tlw = LastFrame.mTcw.rowRange(0, 3).col(3);
+  const cv::Mat tlc = Rlw * twc + tlw;
+  *forward = tlc.at<float>(2) > CurrentFrame.mb && !bMono;
+  *backward = -tlc.at<float>(2) > CurrentFrame.mb && !bMono;
+  for (int i = 0; i < LastFrame.N; i++) {
+    valid[i] = 0; u[i] = v[i] = invz[i] = 0;
+    MapPoint* pMP = LastFrame.mvpMapPoints[i];
+    if (!pMP || LastFrame.mvbOutlier[i]) continue;
+    cv::Mat x3Dw = pMP->GetWorldPos();
+    cv::Mat x3Dc = Rcw * x3Dw + tcw;
+    const float xc = x3Dc.at<float>(0);
+    const float yc = x3Dc.at<float>(1);
+    const float invzc = 1.0 / x3Dc.at<float>(2);
+    if (invzc < 0) continue;
+    const float uu = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+    const float vv = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+    if (uu < CurrentFrame.mnMinX || uu > CurrentFrame.mnMaxX) continue;
+    if (vv < CurrentFrame.mnMinY || vv > CurrentFrame.mnMaxY) continue;
+    valid[i] = 1; u[i] = uu; v[i] = vv; invz[i] = invzc;
+  }
+}
+
+}  // extern "C"

@@ -73,18 +73,19 @@ int mirror_search_for_initialization(orbx_matcher* m, const orbx_keypoint* k1, c
 int mirror_search_by_projection_mp(orbx_matcher* m, const orbx_keypoint* k, const unsigned char* d, int n,
                                    const float* uright, unsigned char* hasMP, const float* bounds, const float* mpUV,
                                    const float* mpR, const int* mpLevel, const float* mpUR, const unsigned char* mpDesc,
-                                   int nMP, const float* scaleFactors, float nnratio, int* mpMatch) {
+                                   int nMP, const float* scaleFactors, float nnratio, int* mpMatch,
+                                   const unsigned char* mpHasObs) {
   return orbx_host::SearchByProjection(m, view(k, d, n, bounds, uright), hasMP, mpUV, mpR, mpLevel, mpUR, mpDesc, nMP,
-                                       scaleFactors, nnratio, mpMatch);
+                                       scaleFactors, nnratio, mpMatch, mpHasObs);
 }
 
 int mirror_search_by_projection_frame(orbx_matcher* m, const orbx_keypoint* k, const unsigned char* d, int n,
                                       const float* uright, unsigned char* hasMP, const float* bounds, const float* qUV,
                                       const float* qR, const int* qMin, const int* qMax, const float* qUR,
                                       const float* qAngle, const unsigned char* qDesc, int nQ, int thDist, int checkOri,
-                                      int* curMatch) {
+                                      int* curMatch, const unsigned char* qHasObs) {
   return orbx_host::SearchByProjection(m, view(k, d, n, bounds, uright), hasMP, qUV, qR, qMin, qMax, qUR, qAngle, qDesc, nQ,
-                                       thDist, checkOri != 0, curMatch);
+                                       thDist, checkOri != 0, curMatch, qHasObs);
 }
 
 }  // extern "C"

@@ -126,7 +126,7 @@ int SearchForInitialization(orbx_matcher* m, const FrameView& F1, const FrameVie
 
 int SearchByProjection(orbx_matcher* m, const FrameView& F, unsigned char* hasMapPoint, const float* mpUV,
                        const float* mpRadius, const int* mpLevel, const float* mpUR, const unsigned char* mpDesc,
-                       int nMP, const float* scaleFactors, float nnratio, int* mpMatch) {
+                       int nMP, const float* scaleFactors, float nnratio, int* mpMatch, const unsigned char* mpHasObs) {
   std::vector<float> qxy(mpUV, mpUV + 2 * (size_t)nMP), qr(nMP);
   std::vector<int> qmin(nMP), qmax(nMP);
   for (int i = 0; i < nMP; i++) {
@@ -160,7 +160,7 @@ int SearchByProjection(orbx_matcher* m, const FrameView& F, unsigned char* hasMa
     if (bestDist <= TH_HIGH) {
       if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
       mpMatch[iMP] = bestIdx;
-      hasMapPoint[bestIdx] = 1;  // F.mvpMapPoints[bestIdx]=pMP (:157)
+      hasMapPoint[bestIdx] = mpHasObs ? (mpHasObs[iMP] != 0) : 1;  // F.mvpMapPoints[bestIdx]=pMP (:157), tested by :118-121
       nmatches++;
     }
   }
@@ -170,7 +170,7 @@ int SearchByProjection(orbx_matcher* m, const FrameView& F, unsigned char* hasMa
 int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* hasMapPoint, const float* qUV,
                        const float* qRadius, const int* qMinLevel, const int* qMaxLevel, const float* qUR,
                        const float* qAngle, const unsigned char* qDesc, int nQ, int thDist, bool checkOrientation,
-                       int* curMatch) {
+                       int* curMatch, const unsigned char* qHasObs) {
   std::vector<float> qxy(qUV, qUV + 2 * (size_t)nQ), qr(qRadius, qRadius + nQ);
   std::vector<int> qmin(qMinLevel, qMinLevel + nQ), qmax(qMaxLevel, qMaxLevel + nQ);
   Candidates c;
@@ -194,7 +194,7 @@ int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* has
     }
     if (bestDist <= thDist) {
       curMatch[bestIdx2] = i;
-      hasMapPoint[bestIdx2] = 1;  // CurrentFrame.mvpMapPoints[bestIdx2]=pMP (:1675)
+      hasMapPoint[bestIdx2] = qHasObs ? (qHasObs[i] != 0) : 1;  // CurrentFrame.mvpMapPoints[bestIdx2]=pMP (:1675)
       nmatches++;
       if (checkOrientation) rotHist[RotBin(qAngle[i], Cur.keysUn[bestIdx2].angle)].push_back(bestIdx2);
     }

@@ -41,7 +41,8 @@ int SearchForInitialization(orbx_matcher* m, const FrameView& F1, const FrameVie
 // mpMatch[iMP] = keypoint index or -1. Returns nmatches.
 int SearchByProjection(orbx_matcher* m, const FrameView& F, unsigned char* hasMapPoint, const float* mpUV,
                        const float* mpRadius, const int* mpLevel, const float* mpUR, const unsigned char* mpDesc,
-                       int nMP, const float* scaleFactors, float nnratio, int* mpMatch);
+                       int nMP, const float* scaleFactors, float nnratio, int* mpMatch,
+                       const unsigned char* mpHasObs = nullptr);
 
 // R/src/ORBmatcher.cpp:1564-1718 (last frame -> current frame) and :1723-1851 (keyframe -> frame) after
 // their projection prologues: per query (u,v), radius, level window, ur = u - mbf*invzc, the source
@@ -49,7 +50,7 @@ int SearchByProjection(orbx_matcher* m, const FrameView& F, unsigned char* hasMa
 int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* hasMapPoint, const float* qUV,
                        const float* qRadius, const int* qMinLevel, const int* qMaxLevel, const float* qUR,
                        const float* qAngle, const unsigned char* qDesc, int nQ, int thDist, bool checkOrientation,
-                       int* curMatch);
+                       int* curMatch, const unsigned char* qHasObs = nullptr);
 
 }  // namespace orbx_host
 

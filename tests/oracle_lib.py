@@ -75,9 +75,9 @@ def lib():
         L.orb_oracle_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int] + \
             [C.c_float] * 4 + [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int]
         L.orb_oracle_search_by_projection_mp.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] + \
-            [C.c_float] * 4 + [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_float, C.c_void_p]
+            [C.c_float] * 4 + [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p]
         L.orb_oracle_search_by_projection_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] + \
-            [C.c_float] * 4 + [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_int, C.c_void_p]
+            [C.c_float] * 4 + [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.orb_oracle_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int] + \
             [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
     return _lib
@@ -260,7 +260,7 @@ def search_for_initialization(kps1, desc1, kps2, desc2, bounds, prev_matched, wi
 
 
 def search_by_projection_mp(kps_un, desc, uright, has_mp, bounds, mp_uv, mp_r, mp_level, mp_ur, mp_desc, scale_factors,
-                            nnratio):
+                            nnratio, mp_has_obs=None):
     kps_un = np.ascontiguousarray(kps_un)
     desc = np.ascontiguousarray(desc, np.uint8)
     args = [np.ascontiguousarray(mp_uv, np.float32), np.ascontiguousarray(mp_r, np.float32),
@@ -272,12 +272,13 @@ def search_by_projection_mp(kps_un, desc, uright, has_mp, bounds, mp_uv, mp_r, m
     match = np.empty(len(args[1]), np.int32)
     n = lib().orb_oracle_search_by_projection_mp(_ptr(kps_un), _ptr(desc), len(kps_un), _opt(ur), _ptr(has_mp),
                                                  *[float(b) for b in bounds], *[_ptr(a) for a in args], len(args[1]),
-                                                 _ptr(sf), nnratio, _ptr(match))
+                                                 _ptr(sf), nnratio, _ptr(match),
+                                                 _opt(None if mp_has_obs is None else np.ascontiguousarray(mp_has_obs, np.uint8)))
     return n, match
 
 
 def search_by_projection_frame(kps_un, desc, uright, has_mp, bounds, q_uv, q_r, q_min_level, q_max_level, q_ur, q_angle,
-                               q_desc, th_dist, check_ori=True):
+                               q_desc, th_dist, check_ori=True, q_has_obs=None):
     kps_un = np.ascontiguousarray(kps_un)
     desc = np.ascontiguousarray(desc, np.uint8)
     args = [np.ascontiguousarray(q_uv, np.float32), np.ascontiguousarray(q_r, np.float32),
@@ -289,7 +290,8 @@ def search_by_projection_frame(kps_un, desc, uright, has_mp, bounds, q_uv, q_r, 
     match = np.empty(len(kps_un), np.int32)
     n = lib().orb_oracle_search_by_projection_frame(_ptr(kps_un), _ptr(desc), len(kps_un), _opt(ur), _ptr(has_mp),
                                                     *[float(b) for b in bounds], *[_ptr(a) for a in args], len(args[1]),
-                                                    th_dist, int(check_ori), _ptr(match))
+                                                    th_dist, int(check_ori), _ptr(match),
+                                                    _opt(None if q_has_obs is None else np.ascontiguousarray(q_has_obs, np.uint8)))
     return n, match
 
 

@@ -1,0 +1,160 @@
+"""ctypes binding of oracle/_ref/libref_front.so -- TEST INFRASTRUCTURE ONLY.
+
+The library is the reference's own Frame.cpp / ORBmatcher.cpp / MapPoint.cpp / Map.cpp / ORBextractor.cpp compiled
+where they lie against the cv shim (oracle/Makefile, oracle/ref_shim/ref_front_capi.cpp). It exists only where it was
+built in the authoring container (git-ignored; it travels to the GPU box with the snapshot). Tests skip without it.
+"""
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+LIB_PATH = ROOT / "oracle" / "_ref" / "libref_front.so"
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+P = C.c_void_p
+_lib = None
+
+
+def available():
+    return LIB_PATH.exists()
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(str(LIB_PATH))
+        L.ref_set_allocator_mode.argtypes = [C.c_int]
+        L.ref_front_create.restype = P
+        L.ref_front_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int] + [C.c_float] * 6
+        L.ref_front_destroy.argtypes = [P]
+        L.ref_frame_mono.restype = P
+        L.ref_frame_mono.argtypes = [P, P, C.c_int, C.c_int, C.c_int]
+        L.ref_frame_stereo.restype = P
+        L.ref_frame_stereo.argtypes = [P, P, P, C.c_int, C.c_int, C.c_int]
+        L.ref_frame_destroy.argtypes = [P]
+        L.ref_frame_n.argtypes = [P]
+        L.ref_frame_n_right.argtypes = [P]
+        L.ref_frame_get.argtypes = [P] * 8
+        L.ref_frame_get_right.argtypes = [P] * 3
+        L.ref_front_level.argtypes = [P, C.c_int, C.c_int, P, P, P, C.c_int]
+        L.ref_frame_set_pose.argtypes = [P, P]
+        L.ref_search_for_initialization.argtypes = [P, P, P, P, C.c_int, C.c_float, C.c_int]
+        L.ref_map_point_create.argtypes = [P, P, C.c_int, P]
+        L.ref_map_point_set_track.argtypes = [P, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float]
+        L.ref_map_point_set_nobs.argtypes = [P, C.c_int, C.c_int]
+        L.ref_frame_set_map_point.argtypes = [P, P, C.c_int, C.c_int]
+        L.ref_frame_set_outlier.argtypes = [P, C.c_int, C.c_int]
+        L.ref_frame_get_map_points.argtypes = [P, P, P]
+        L.ref_search_by_projection_mp.argtypes = [P, P, P, C.c_int, C.c_float, C.c_float, C.c_int]
+        L.ref_search_by_projection_frame.argtypes = [P, P, C.c_float, C.c_int, C.c_float, C.c_int]
+        L.ref_project_last_frame.argtypes = [P, P, C.c_int] + [P] * 6
+        L.ref_set_allocator_mode(1)   # pointer order == creation order: the canonical DistributeOctTree tie-break
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(P)
+
+
+class Frame:
+    def __init__(self, front, handle):
+        self.front, self._h = front, handle
+        self.N = lib().ref_frame_n(handle)
+        n = self.N
+        self.keys, self.keys_un = np.empty(n, KP_DTYPE), np.empty(n, KP_DTYPE)
+        self.desc = np.empty((n, 32), np.uint8)
+        self.u_right, self.depth = np.empty(n, np.float32), np.empty(n, np.float32)
+        self.bounds = np.empty(4, np.float32)
+        mb = np.empty(1, np.float32)
+        lib().ref_frame_get(handle, _p(self.keys), _p(self.keys_un), _p(self.desc), _p(self.u_right), _p(self.depth),
+                            _p(self.bounds), _p(mb))
+        self.mb = mb[0]
+        nr = lib().ref_frame_n_right(handle)
+        self.keys_right, self.desc_right = np.empty(nr, KP_DTYPE), np.empty((nr, 32), np.uint8)
+        if nr:
+            lib().ref_frame_get_right(handle, _p(self.keys_right), _p(self.desc_right))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().ref_frame_destroy(self._h)
+            self._h = None
+
+    def set_pose(self, Tcw):
+        T = np.ascontiguousarray(Tcw, np.float32).reshape(4, 4)
+        lib().ref_frame_set_pose(self._h, _p(T))
+
+    def set_map_point(self, idx, mp):
+        lib().ref_frame_set_map_point(self.front._h, self._h, idx, -1 if mp is None else mp)
+
+    def set_outlier(self, idx, flag):
+        lib().ref_frame_set_outlier(self._h, idx, int(flag))
+
+    def map_points(self):
+        out = np.empty(self.N, np.int32)
+        lib().ref_frame_get_map_points(self.front._h, self._h, _p(out))
+        return out
+
+
+class Front:
+    """Two reference ORBextractors + camera + Map, and factories for reference Frame / MapPoint objects."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7, fx=500.0, fy=500.0, cx=320.0, cy=240.0,
+                 bf=40.0, th_depth=35.0):
+        self.fx, self.fy, self.cx, self.cy, self.bf = (np.float32(v) for v in (fx, fy, cx, cy, bf))
+        self.nlevels = nlevels
+        self._h = lib().ref_front_create(nfeatures, scale, nlevels, ini_th, min_th, fx, fy, cx, cy, bf, th_depth)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().ref_front_destroy(self._h)
+            self._h = None
+
+    def frame_mono(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        return Frame(self, lib().ref_frame_mono(self._h, _p(img), img.shape[1], img.shape[0], img.strides[0]))
+
+    def frame_stereo(self, left, right):
+        left, right = np.ascontiguousarray(left, np.uint8), np.ascontiguousarray(right, np.uint8)
+        assert left.shape == right.shape
+        return Frame(self, lib().ref_frame_stereo(self._h, _p(left), _p(right), left.shape[1], left.shape[0], left.strides[0]))
+
+    def level(self, side, level):
+        w, h = C.c_int(), C.c_int()
+        lib().ref_front_level(self._h, side, level, C.byref(w), C.byref(h), None, 0)
+        out = np.empty((h.value, w.value), np.uint8)
+        lib().ref_front_level(self._h, side, level, None, None, _p(out), out.strides[0])
+        return out
+
+    def map_point(self, frame, idx, pos, n_obs=1):
+        pos = np.ascontiguousarray(pos, np.float32)
+        mp = lib().ref_map_point_create(self._h, frame._h, idx, _p(pos))
+        lib().ref_map_point_set_nobs(self._h, mp, n_obs)
+        return mp
+
+    def set_track(self, mp, in_view, u, v, u_r, level, view_cos):
+        lib().ref_map_point_set_track(self._h, mp, int(in_view), u, v, u_r, level, view_cos)
+
+    def search_for_initialization(self, f1, f2, prev_matched, window, nnratio, check_ori=True):
+        pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+        m12 = np.empty(f1.N, np.int32)
+        n = lib().ref_search_for_initialization(f1._h, f2._h, _p(pm), _p(m12), window, nnratio, int(check_ori))
+        return n, m12, pm
+
+    def search_by_projection_mp(self, frame, mps, th, nnratio, check_ori=True):
+        mps = np.ascontiguousarray(mps, np.int32)
+        return lib().ref_search_by_projection_mp(self._h, frame._h, _p(mps), len(mps), th, nnratio, int(check_ori))
+
+    def search_by_projection_frame(self, cur, last, th, mono, nnratio=0.9, check_ori=True):
+        return lib().ref_search_by_projection_frame(cur._h, last._h, th, int(mono), nnratio, int(check_ori))
+
+    def project_last_frame(self, cur, last, mono):
+        n = last.N
+        valid = np.empty(n, np.uint8)
+        u, v, invz = (np.empty(n, np.float32) for _ in range(3))
+        fwd, bwd = C.c_int(), C.c_int()
+        lib().ref_project_last_frame(cur._h, last._h, int(mono), _p(valid), _p(u), _p(v), _p(invz), C.byref(fwd), C.byref(bwd))
+        return valid.astype(bool), u, v, invz, bool(fwd.value), bool(bwd.value)

@@ -17,9 +17,9 @@ P = C.c_void_p
 def mirror():
     L = C.CDLL(str(LIB))
     L.mirror_search_for_initialization.argtypes = [P, P, P, C.c_int, P, P, C.c_int, P, P, P, C.c_int, C.c_float, C.c_int]
-    L.mirror_search_by_projection_mp.argtypes = [P, P, P, C.c_int, P, P, P, P, P, P, P, P, C.c_int, P, C.c_float, P]
+    L.mirror_search_by_projection_mp.argtypes = [P, P, P, C.c_int, P, P, P, P, P, P, P, P, C.c_int, P, C.c_float, P, P]
     L.mirror_search_by_projection_frame.argtypes = [P, P, P, C.c_int, P, P, P, P, P, P, P, P, P, P, C.c_int, C.c_int,
-                                                   C.c_int, P]
+                                                   C.c_int, P, P]
     return L
 
 
@@ -57,8 +57,8 @@ def test_search_for_initialization(pkg, oracle, mirror, two_frames, check_ori):
     assert gn2 == en2 and np.array_equal(gm12, em2)
 
 
-@pytest.mark.parametrize("stereo", [False, True])
-def test_search_by_projection_map_points(pkg, oracle, mirror, two_frames, stereo):
+@pytest.mark.parametrize("stereo,some_without_obs", [(False, False), (True, False), (True, True)])
+def test_search_by_projection_map_points(pkg, oracle, mirror, two_frames, stereo, some_without_obs):
     k1, d1, k2, d2, b, sf = two_frames
     rng = np.random.default_rng(5)
     nmp = len(k1)
@@ -70,19 +70,21 @@ def test_search_by_projection_map_points(pkg, oracle, mirror, two_frames, stereo
     uright = None
     if stereo:
         uright = np.where(rng.random(len(k2)) < 0.6, k2["x"] - rng.uniform(1, 40, len(k2)), -1).astype(np.float32)
-    en, ematch = oracle.search_by_projection_mp(k2, d2, uright, has_mp, b, uv, r, level, ur, d1, sf, np.float32(0.8))
+    obs = (rng.random(nmp) < 0.7).astype(np.uint8) if some_without_obs else None   # Observations()>0 per map point
+    en, ematch = oracle.search_by_projection_mp(k2, d2, uright, has_mp, b, uv, r, level, ur, d1, sf, np.float32(0.8), obs)
     m = pkg.ORBmatcher(0.8)
     gmatch = np.empty(nmp, np.int32)
     gh = has_mp.copy()
     gn = mirror.mirror_search_by_projection_mp(m._h, _p(k2), _p(d2), len(k2), _p(uright), _p(gh), _p(b), _p(uv), _p(r),
                                                _p(level), _p(ur), _p(np.ascontiguousarray(d1)), nmp,
-                                               _p(np.ascontiguousarray(sf, np.float32)), np.float32(0.8), _p(gmatch))
+                                               _p(np.ascontiguousarray(sf, np.float32)), np.float32(0.8), _p(gmatch), _p(obs))
     assert en > 100
     assert gn == en and np.array_equal(gmatch, ematch)
 
 
-@pytest.mark.parametrize("stereo,check_ori", [(False, 1), (True, 1), (False, 0)])
-def test_search_by_projection_frame(pkg, oracle, mirror, two_frames, stereo, check_ori):
+@pytest.mark.parametrize("stereo,check_ori,some_without_obs", [(False, 1, False), (True, 1, False), (False, 0, False),
+                                                               (True, 1, True)])
+def test_search_by_projection_frame(pkg, oracle, mirror, two_frames, stereo, check_ori, some_without_obs):
     k1, d1, k2, d2, b, sf = two_frames
     rng = np.random.default_rng(6)
     nq = len(k1)
@@ -98,13 +100,14 @@ def test_search_by_projection_frame(pkg, oracle, mirror, two_frames, stereo, che
     if stereo:
         uright = np.where(rng.random(len(k2)) < 0.6, k2["x"] - rng.uniform(1, 40, len(k2)), -1).astype(np.float32)
     angle = np.ascontiguousarray(k1["angle"], np.float32)
+    obs = (rng.random(nq) < 0.6).astype(np.uint8) if some_without_obs else None   # temporal points have none
     en, ematch = oracle.search_by_projection_frame(k2, d2, uright, has_mp, b, uv, r, lo, hi, ur, angle, d1, 100,
-                                                   bool(check_ori))
+                                                   bool(check_ori), obs)
     m = pkg.ORBmatcher(0.9)
     gmatch = np.empty(len(k2), np.int32)
     gh = has_mp.copy()
     gn = mirror.mirror_search_by_projection_frame(m._h, _p(k2), _p(d2), len(k2), _p(uright), _p(gh), _p(b), _p(uv), _p(r),
                                                   _p(lo), _p(hi), _p(ur), _p(angle), _p(np.ascontiguousarray(d1)), nq,
-                                                  100, check_ori, _p(gmatch))
+                                                  100, check_ori, _p(gmatch), _p(obs))
     assert en > 100
     assert gn == en and np.array_equal(gmatch, ematch)
