@@ -2,6 +2,9 @@
 // Follows R/src/ORBmatcher.cpp (DescriptorDistance :1901-1917, top-2 + ratio loops :266-300,
 // SearchForInitialization :499-617, SearchByProjection :63-163 / :1564-1718, ComputeThreeMaxima
 // :1854-1895) and R/src/Frame.cpp (grid :244-260, :387-452; ComputeStereoMatches :551-770).
+// PINNED: tests/test_oracle_vs_ref_front.py runs the reference's own Frame.cpp / ORBmatcher.cpp / MapPoint.cpp
+// (oracle/_ref/libref_front.so, compiled where they lie against oracle/ref_shim) on real Frame and MapPoint
+// objects and requires bit-identical results from every search and from the stereo matches.
 #include <algorithm>
 #include <climits>
 #include <cmath>

@@ -1,7 +1,6 @@
 """Known answers and properties of the matcher-side oracle (CPU): Frame grid, SearchForInitialization,
-SearchByProjection, ComputeStereoMatches, DescriptorDistance. (ORBmatcher.cpp / Frame.cpp cannot be compiled
-alone -- they need Frame/KeyFrame/MapPoint/DBoW2 -- so these rows are restated, not pinned to a reference
-binary: parity unpinned beyond these checks.)"""
+SearchByProjection, ComputeStereoMatches, DescriptorDistance. (These rows are pinned to the reference's own
+ORBmatcher.cpp / Frame.cpp in tests/test_oracle_vs_ref_front.py; the checks here need no reference build.)"""
 import numpy as np
 
 
