@@ -133,6 +133,8 @@ class ClockSampler:
 
 
 def base_frames(pkg, n=BASE_FRAMES, seed0=1000):
+    if METRIC.startswith("ORB frames/s (1241x376"):   # C2: stereo pairs, interleaved L R L R ...
+        return np.stack([im for i in range(n // 2) for im in pkg.synth.stereo_pair(W, H, seed0 + i)])
     return np.stack([pkg.synth.frame(W, H, seed0 + i) for i in range(n)])
 
 
@@ -342,9 +344,23 @@ def _run_gpu(args, torch):
     stream = torch.cuda.current_stream().cuda_stream
     assert stream != 0
 
+    # C2: the batch is a sequence of stereo pairs (L R L R ...); Frame::ComputeStereoMatches for every pair runs on the
+    # same stream right after the extraction (mb = 0: what the reference's stereo constructor runs with)
+    stereo = args.workload == "C2"
+    if stereo:
+        sm = pkg.ORBmatcher(device=local)
+        pairs = B // 2
+        d_ur = torch.empty((pairs, cap), dtype=torch.float32, device="cuda")
+        d_z = torch.empty((pairs, cap), dtype=torch.float32, device="cuda")
+        d_nm = torch.zeros(pairs, dtype=torch.int32, device="cuda")
+        mbf = float(np.float32(718.856) * np.float32(0.537))     # KITTI 00-02 fx * baseline
+
     def step():
         ex.extract_batch_device(frames.data_ptr(), B, W, H, W, W * H, d_kps.data_ptr(), d_desc.data_ptr(), cap,
                                 d_n.data_ptr(), stream)
+        if stereo:
+            sm.stereo_match_batch_device(ex, pairs, 0, 1, 2, d_kps.data_ptr(), d_desc.data_ptr(), d_n.data_ptr(), cap, mbf,
+                                         0.0, d_ur.data_ptr(), d_z.data_ptr(), d_nm.data_ptr(), stream)
 
     # ---- device-resident throughput ("value") ----
     for _ in range(max(args.warmup, 3)):
@@ -404,6 +420,12 @@ def _run_gpu(args, torch):
             dist.destroy_process_group()
         return 0
 
+    stereo_obj = None
+    if stereo:
+        stereo_obj = {"pairs_per_s": value / 2, "matched_per_pair": float(d_nm.float().mean().item()),
+                      "note": "value counts frames; every timed step also runs orbx_stereo_match_batch_device on its "
+                              f"{pairs} pairs (3 launches: row table, match + SAD refinement, median filter)"}
+
     # ---- roofline of the dominant stage, from the event times of the timed region ----
     peaks_path = ROOT / "MEASURED_PEAKS.json"
     if peaks_path.exists():
@@ -452,7 +474,8 @@ def _run_gpu(args, torch):
             "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "input_bytes_per_step_per_gpu": B * W * H,
                        "l2_policy": "inputs larger than L2 (157 MB of distinct frames per step)",
                        "keypoints_per_frame": nkp / B, "parallelism": f"frame sharding x{world}, no collective"},
-            "clocks": clocks, "e2e": e2e_obj, "gpu_launches": launches, "roofline": roof, "stages": stages,
+            "clocks": clocks, "e2e": e2e_obj, "gpu_launches": launches + (3 * args.steps if stereo else 0), "roofline": roof,
+            "stages": stages, "stereo": stereo_obj,
             "cpu_baseline": cpu, "hamming": hamming}
     print(json.dumps(line), flush=True)
     if world > 1:

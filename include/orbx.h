@@ -189,6 +189,17 @@ int orbx_stereo_match(orbx_matcher* h, orbx_extractor* left, orbx_extractor* rig
                       const orbx_keypoint* kps_r, const uint8_t* desc_r, int32_t nr, float mbf, float mb,
                       float* u_right, float* depth, int32_t* n_matched);
 
+/* The same for `pairs` stereo pairs of ONE device-resident batch (BASELINE config 2: image sequences of stereo
+ * pairs): `ex` processed the frames with orbx_extract_batch_device; pair p is left frame left_frame0 + p*frame_step
+ * and right frame right_frame0 + p*frame_step of that batch (0, 1, 2 = interleaved L R L R ...). d_kps / d_desc /
+ * d_n are that call's device outputs (cap rows per frame). Outputs, device: d_u_right / d_depth [pairs][cap]
+ * (rows >= n of the left frame are not written), d_n_matched [pairs]. Asynchronous on `stream` (NULL: the
+ * matcher's own stream, after waiting for the extractor's). Remember that the reference runs this with mb == 0. */
+int orbx_stereo_match_batch_device(orbx_matcher* h, orbx_extractor* ex, int32_t pairs, int32_t left_frame0,
+                                   int32_t right_frame0, int32_t frame_step, const orbx_keypoint* d_kps,
+                                   const uint8_t* d_desc, const int32_t* d_n, int32_t cap, float mbf, float mb,
+                                   float* d_u_right, float* d_depth, int32_t* d_n_matched, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -65,6 +65,8 @@ SIGNATURES = {
                                     _i32, C.POINTER(_i32)]),
     "orbx_stereo_match": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _i32, _f32, _f32, _vp, _vp,
                                     C.POINTER(_i32)]),
+    "orbx_stereo_match_batch_device": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _i32, _f32, _f32, _vp, _vp, _vp,
+                                                 _vp]),
     "orbx_match_merge_device": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _f32, _i32, _vp, _vp, _vp, _vp, _vp]),
 }
 

@@ -4,6 +4,7 @@
 #include <new>
 
 #include "orbx_host.h"
+#include "orbx_stereo.cuh"
 
 namespace orbx {
 int bf2_plan_chunks(int nq, long long ndb, int smCount, int* rowsPerChunk);
@@ -20,17 +21,6 @@ void launch_window(bool fill, const orbx_keypoint* kps, const uint8_t* desc, flo
                    int* candDist, cudaStream_t s);
 void launch_scan(const int* count, int n, int* off, cudaStream_t s);
 int grid_cells();
-struct StereoLevels {
-  const uint8_t* left[kMaxLevels];
-  const uint8_t* right[kMaxLevels];
-  int pitchL[kMaxLevels], pitchR[kMaxLevels];
-  int width[kMaxLevels];
-  float scale[kMaxLevels], invScale[kMaxLevels];
-  int rows0;
-};
-void launch_stereo(const StereoLevels& lv, const orbx_keypoint* kpL, const uint8_t* descL, int nl,
-                   const orbx_keypoint* kpR, const uint8_t* descR, int nr, float mbf, float mb, float* uRight,
-                   float* depth, int* sad, int* nKept, cudaStream_t s);
 }  // namespace orbx
 
 using namespace orbx;
@@ -259,6 +249,36 @@ int orbx_match_window(orbx_matcher* h, const orbx_keypoint* kps_un, const uint8_
   return ORBX_OK;
 }
 
+// pyramids of the frames the two handles processed last (single-chunk batches, lane 0)
+static int stereo_levels_of(const orbx_extractor* left, const orbx_extractor* right, StereoLevels* lv) {
+  const orbx::Lane& LL = left->lane[0];
+  const orbx::Lane& LR = right->lane[0];
+  const int nlv = LL.geom.nlevels;
+  if (LR.geom.nlevels != nlv || LL.w != LR.w || LL.h != LR.h) { set_error("left/right shapes differ"); return ORBX_ERR_ARG; }
+  for (int l = 0; l < kMaxLevels; l++) {
+    lv->left[l] = lv->right[l] = nullptr;
+    lv->strideL[l] = lv->strideR[l] = 0;
+    lv->pitchL[l] = lv->pitchR[l] = lv->width[l] = 0;
+    lv->scale[l] = lv->invScale[l] = 1.f;
+  }
+  for (int l = 0; l < nlv; l++) {
+    const LevelGeom& G = LL.geom.lv[l];
+    const LevelGeom& GR = LR.geom.lv[l];
+    if (l == 0) {
+      lv->left[0] = left->lastLevel0; lv->strideL[0] = left->lastL0FrameStride; lv->pitchL[0] = left->lastL0Pitch;
+      lv->right[0] = right->lastLevel0; lv->strideR[0] = right->lastL0FrameStride; lv->pitchR[0] = right->lastL0Pitch;
+    } else {
+      lv->left[l] = static_cast<const uint8_t*>(LL.pyrArena.p) + G.planeOff; lv->strideL[l] = G.planeBytes; lv->pitchL[l] = G.pitch;
+      lv->right[l] = static_cast<const uint8_t*>(LR.pyrArena.p) + GR.planeOff; lv->strideR[l] = GR.planeBytes; lv->pitchR[l] = GR.pitch;
+    }
+    lv->width[l] = G.w;
+    lv->scale[l] = left->tables.scale[l];
+    lv->invScale[l] = left->tables.invScale[l];
+  }
+  lv->rows0 = LL.geom.lv[0].h;
+  return ORBX_OK;
+}
+
 int orbx_stereo_match(orbx_matcher* h, orbx_extractor* left, orbx_extractor* right, int32_t frame_left,
                       int32_t frame_right, const orbx_keypoint* kps_l, const uint8_t* desc_l, int32_t nl,
                       const orbx_keypoint* kps_r, const uint8_t* desc_r, int32_t nr, float mbf, float mb,
@@ -275,50 +295,41 @@ int orbx_stereo_match(orbx_matcher* h, orbx_extractor* left, orbx_extractor* rig
     set_error("extractors and matcher live on different devices");
     return ORBX_ERR_ARG;
   }
-  const orbx::Lane& LL = left->lane[0];
-  const orbx::Lane& LR = right->lane[0];
   if (!left->haveResult || !right->haveResult || frame_left < 0 || frame_left >= left->lastCount || frame_right < 0 ||
       frame_right >= right->lastCount) {
     set_error("the extractors hold no (single-chunk) result for frames %d / %d", frame_left, frame_right);
     return ORBX_ERR_STATE;
   }
-  const int nlv = LL.geom.nlevels;
-  if (LR.geom.nlevels != nlv || LL.w != LR.w || LL.h != LR.h) { set_error("left/right shapes differ"); return ORBX_ERR_ARG; }
   StereoLevels lv;
-  for (int l = 0; l < kMaxLevels; l++) { lv.left[l] = lv.right[l] = nullptr; lv.pitchL[l] = lv.pitchR[l] = lv.width[l] = 0; lv.scale[l] = lv.invScale[l] = 1.f; }
-  for (int l = 0; l < nlv; l++) {
-    const LevelGeom& G = LL.geom.lv[l];
-    if (l == 0) {
-      lv.left[0] = left->lastLevel0 + (long long)frame_left * left->lastL0FrameStride;
-      lv.right[0] = right->lastLevel0 + (long long)frame_right * right->lastL0FrameStride;
-      lv.pitchL[0] = left->lastL0Pitch; lv.pitchR[0] = right->lastL0Pitch;
-    } else {
-      lv.left[l] = static_cast<const uint8_t*>(LL.pyrArena.p) + G.planeOff + (long long)frame_left * G.planeBytes;
-      lv.right[l] = static_cast<const uint8_t*>(LR.pyrArena.p) + LR.geom.lv[l].planeOff + (long long)frame_right * LR.geom.lv[l].planeBytes;
-      lv.pitchL[l] = G.pitch; lv.pitchR[l] = LR.geom.lv[l].pitch;
-    }
-    lv.width[l] = G.w;
-    lv.scale[l] = left->tables.scale[l];
-    lv.invScale[l] = left->tables.invScale[l];
-  }
-  lv.rows0 = LL.geom.lv[0].h;
+  if ((rc = stereo_levels_of(left, right, &lv))) return rc;
+  const int nlv = left->lane[0].geom.nlevels;
   const size_t NL = (size_t)std::max(nl, 1), NR = (size_t)std::max(nr, 1);
+  const size_t itemCap = NR * (size_t)stereo_items_per_keypoint(left->tables.scale[nlv - 1]);
   if ((rc = h->dWin.ensure(carve_size({NL * sizeof(orbx_keypoint), NL * 32, NR * sizeof(orbx_keypoint), NR * 32, NL * 4, NL * 4,
-                                       NL * 4, 4}))))
+                                       NL * 4, 4, ((size_t)lv.rows0 + 1) * 4, itemCap * 4}))))
     return rc;
   Carver c{static_cast<uint8_t*>(h->dWin.p)};
   orbx_keypoint* dKL = c.take<orbx_keypoint>(NL);
   uint8_t* dDL = c.take<uint8_t>(NL * 32);
   orbx_keypoint* dKR = c.take<orbx_keypoint>(NR);
   uint8_t* dDR = c.take<uint8_t>(NR * 32);
-  float* dU = c.take<float>(NL);
-  float* dZ = c.take<float>(NL);
-  int* dSad = c.take<int>(NL);
-  int* dKept = c.take<int>(1);
+  StereoArrays a;
+  a.kpL = dKL; a.descL = reinterpret_cast<const uint4*>(dDL); a.nL = nullptr;
+  a.kpR = dKR; a.descR = reinterpret_cast<const uint4*>(dDR); a.nR = nullptr;
+  a.uRight = c.take<float>(NL);
+  a.depth = c.take<float>(NL);
+  a.sad = c.take<int>(NL);
+  a.nKept = c.take<int>(1);
+  a.rowStart = c.take<int>((size_t)lv.rows0 + 1);
+  a.rowItems = c.take<int>(itemCap);
+  a.itemCap = (int)itemCap;
+  lv.pyrLeft0 = frame_left; lv.pyrRight0 = frame_right; lv.pyrStep = 0;
+  lv.arrLeft0 = lv.arrRight0 = 0; lv.arrStep = 0; lv.cap = 0;  // one pair: the staged arrays start at row 0
+  lv.fixedNL = nl; lv.fixedNR = nr;
   // the extractors' streams produced the pyramids; their host-buffer calls are synchronous, the device-resident
   // entry point is not: wait for both before reading
-  ORBX_CUDA_TRY(cudaStreamSynchronize(LL.stream));
-  ORBX_CUDA_TRY(cudaStreamSynchronize(LR.stream));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(left->lane[0].stream));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(right->lane[0].stream));
   cudaStream_t s = h->stream;
   if (nl > 0) {
     ORBX_CUDA_TRY(cudaMemcpyAsync(dKL, kps_l, (size_t)nl * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, s));
@@ -328,15 +339,65 @@ int orbx_stereo_match(orbx_matcher* h, orbx_extractor* left, orbx_extractor* rig
     ORBX_CUDA_TRY(cudaMemcpyAsync(dKR, kps_r, (size_t)nr * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, s));
     ORBX_CUDA_TRY(cudaMemcpyAsync(dDR, desc_r, (size_t)nr * 32, cudaMemcpyHostToDevice, s));
   }
-  launch_stereo(lv, dKL, dDL, nl, dKR, dDR, nr, mbf, mb, dU, dZ, dSad, dKept, s);
-  h->launches += 2;
+  const int le = launch_stereo(lv, a, 1, nl, mbf, mb, s);
+  if (le) { set_error("stereo kernel configuration failed: %s", cudaGetErrorString((cudaError_t)le)); return ORBX_ERR_CUDA; }
+  h->launches += nl > 0 ? 3 : 2;
   ORBX_CUDA_TRY(cudaGetLastError());
   if (nl > 0) {
-    ORBX_CUDA_TRY(cudaMemcpyAsync(u_right, dU, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA_TRY(cudaMemcpyAsync(depth, dZ, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(u_right, a.uRight, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(depth, a.depth, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
   }
-  ORBX_CUDA_TRY(cudaMemcpyAsync(n_matched, dKept, 4, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(n_matched, a.nKept, 4, cudaMemcpyDeviceToHost, s));
   ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  return ORBX_OK;
+}
+
+int orbx_stereo_match_batch_device(orbx_matcher* h, orbx_extractor* ex, int32_t pairs, int32_t left_frame0,
+                                   int32_t right_frame0, int32_t frame_step, const orbx_keypoint* d_kps,
+                                   const uint8_t* d_desc, const int32_t* d_n, int32_t cap, float mbf, float mb,
+                                   float* d_u_right, float* d_depth, int32_t* d_n_matched, void* stream) {
+  int rc = set_dev(h);
+  if (rc) return rc;
+  if (!ex || pairs <= 0 || !d_kps || !d_desc || !d_n || cap <= 0 || cap > 65535 || !d_u_right || !d_depth || !d_n_matched ||
+      left_frame0 < 0 || right_frame0 < 0) {
+    set_error("bad arguments");
+    return ORBX_ERR_ARG;
+  }
+  if (ex->params.device != h->device) { set_error("extractor and matcher live on different devices"); return ORBX_ERR_ARG; }
+  const int lastL = left_frame0 + (pairs - 1) * frame_step, lastR = right_frame0 + (pairs - 1) * frame_step;
+  if (!ex->haveResult || lastL < 0 || lastR < 0 || std::max({left_frame0, right_frame0, lastL, lastR}) >= ex->lastCount) {
+    set_error("the extractor holds no (single-chunk) result covering frames up to %d", std::max(lastL, lastR));
+    return ORBX_ERR_STATE;
+  }
+  StereoLevels lv;
+  if ((rc = stereo_levels_of(ex, ex, &lv))) return rc;
+  const int nlv = ex->lane[0].geom.nlevels;
+  const size_t P = (size_t)pairs;
+  const size_t itemCap = (size_t)cap * (size_t)stereo_items_per_keypoint(ex->tables.scale[nlv - 1]);
+  if ((rc = h->dWin.ensure(carve_size({P * cap * 4, P * ((size_t)lv.rows0 + 1) * 4, P * itemCap * 4})))) return rc;
+  Carver c{static_cast<uint8_t*>(h->dWin.p)};
+  StereoArrays a;
+  a.kpL = a.kpR = d_kps;
+  a.descL = a.descR = reinterpret_cast<const uint4*>(d_desc);
+  a.nL = a.nR = d_n;
+  a.uRight = d_u_right; a.depth = d_depth; a.nKept = d_n_matched;
+  a.sad = c.take<int>(P * cap);
+  a.rowStart = c.take<int>(P * ((size_t)lv.rows0 + 1));
+  a.rowItems = c.take<int>(P * itemCap);
+  a.itemCap = (int)itemCap;
+  lv.pyrLeft0 = lv.arrLeft0 = left_frame0;
+  lv.pyrRight0 = lv.arrRight0 = right_frame0;
+  lv.pyrStep = lv.arrStep = frame_step;
+  lv.cap = cap;
+  lv.fixedNL = lv.fixedNR = 0;
+  // stream-ordered after the extraction when both run on the caller's stream; with the handles' own streams the
+  // extraction is waited for here
+  cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : h->stream;
+  if (!stream) ORBX_CUDA_TRY(cudaStreamSynchronize(ex->lane[0].stream));
+  const int le = launch_stereo(lv, a, pairs, cap, mbf, mb, s);
+  if (le) { set_error("stereo kernel configuration failed: %s", cudaGetErrorString((cudaError_t)le)); return ORBX_ERR_CUDA; }
+  h->launches += 3;
+  ORBX_CUDA_TRY(cudaGetLastError());
   return ORBX_OK;
 }
 

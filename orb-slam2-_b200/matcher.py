@@ -94,5 +94,12 @@ class ORBmatcher:
                                       ptr(kps_r), ptr(desc_r), len(kps_r), mbf, mb, ptr(u), ptr(z), C.byref(n)))
         return u[:nl], z[:nl], n.value
 
+    def stereo_match_batch_device(self, ex, pairs, left_frame0, right_frame0, frame_step, d_kps, d_desc, d_n, cap, mbf, mb,
+                                  d_u_right, d_depth, d_n_matched, stream=0):
+        """ComputeStereoMatches for `pairs` pairs of the device-resident batch `ex` processed last (raw device
+        pointers, asynchronous): pair p = frames left_frame0 + p*frame_step / right_frame0 + p*frame_step."""
+        check(lib().orbx_stereo_match_batch_device(self._h, ex._h, pairs, left_frame0, right_frame0, frame_step, d_kps, d_desc,
+                                                   d_n, cap, mbf, mb, d_u_right, d_depth, d_n_matched, stream))
+
     def launch_count(self):
         return int(lib().orbx_matcher_launch_count(self._h))

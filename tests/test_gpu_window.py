@@ -72,3 +72,61 @@ def test_stereo_matches_bit_exact(pkg, oracle, w, h, nf, seed):
     # no right keypoints at all
     u, z, n = m.stereo_match(exl, exr, kl, dl, kr[:0], dr[:0], mbf, mb)
     assert n == 0 and (u == -1).all() and (z == -1).all()
+
+
+@pytest.mark.parametrize("interleaved", [True, False])
+def test_stereo_batch_device_equals_per_pair(pkg, oracle, interleaved):
+    """orbx_stereo_match_batch_device on one device-resident batch of stereo pairs (L R L R ... or all lefts then all
+    rights) gives every pair the result of the per-pair host call; pair 0 is also checked against the oracle."""
+    import torch
+    w, h, nf, pairs = 752, 480, 1200, 5
+    imgs = [pkg.synth.stereo_pair(w, h, 20 + p) for p in range(pairs)]
+    if interleaved:
+        frames = np.stack([im for lr in imgs for im in lr])
+        l0, r0, step = 0, 1, 2
+    else:
+        frames = np.stack([lr[0] for lr in imgs] + [lr[1] for lr in imgs])
+        l0, r0, step = 0, pairs, 1
+    B = 2 * pairs
+    cap = nf + 64
+    ex = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    d_frames = torch.from_numpy(frames).cuda()
+    dk = torch.zeros((B, cap, 7), dtype=torch.float32, device="cuda")
+    dd = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+    dn = torch.zeros(B, dtype=torch.int32, device="cuda")
+    du = torch.full((pairs, cap), -7.0, dtype=torch.float32, device="cuda")
+    dz = torch.full((pairs, cap), -7.0, dtype=torch.float32, device="cuda")
+    dm = torch.zeros(pairs, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ex.extract_batch_device(d_frames.data_ptr(), B, w, h, w, w * h, dk.data_ptr(), dd.data_ptr(), cap, dn.data_ptr())
+    m = pkg.ORBmatcher()
+    mb = np.float32(0.0)                      # what the reference's stereo constructor runs with
+    mbf = np.float32(435.2 * 0.11)
+    m.stereo_match_batch_device(ex, pairs, l0, r0, step, dk.data_ptr(), dd.data_ptr(), dn.data_ptr(), cap, mbf, mb,
+                                du.data_ptr(), dz.data_ptr(), dm.data_ptr())
+    torch.cuda.synchronize()
+    n = dn.cpu().numpy()
+    kps = dk.cpu().numpy().view(np.uint8).reshape(B, cap, 28).view(pkg.KP_DTYPE).reshape(B, cap)
+    desc = dd.cpu().numpy()
+    u_all, z_all, matched = du.cpu().numpy(), dz.cpu().numpy(), dm.cpu().numpy()
+    exl = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    exr = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    for p in range(pairs):
+        fl, fr = l0 + p * step, r0 + p * step
+        kl, dl = exl(frames[fl])
+        kr, dr = exr(frames[fr])
+        assert n[fl] == len(kl) and np.array_equal(kps[fl, :n[fl]].view(np.uint8), kl.view(np.uint8))
+        u, z, cnt = m.stereo_match(exl, exr, kl, dl, kr, dr, mbf, mb)
+        assert cnt == matched[p] > 50
+        assert np.array_equal(u_all[p, :n[fl]].view(np.uint32), u.view(np.uint32))
+        assert np.array_equal(z_all[p, :n[fl]].view(np.uint32), z.view(np.uint32))
+        assert (u_all[p, n[fl]:] == -7.0).all()
+        if p == 0:
+            ox = oracle.Extractor(nf, 1.2, 8, 20, 7)
+            ox(frames[fl])
+            pl = [ox.level(l) for l in range(8)]
+            ox(frames[fr])
+            pr = [ox.level(l) for l in range(8)]
+            t = ox.tables()
+            eu, ez, en = oracle.stereo_matches(kl, dl, kr, dr, pl, pr, t["scale"], t["inv_scale"], mbf, mb)
+            assert en == cnt and np.array_equal(u.view(np.uint32), eu.view(np.uint32)) and np.array_equal(z.view(np.uint32), ez.view(np.uint32))
