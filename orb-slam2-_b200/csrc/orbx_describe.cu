@@ -44,6 +44,7 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
                 const __grid_constant__ FrameSetGeom g, const uint32_t* __restrict__ kept,
                 const int* __restrict__ keptCount, orbx_keypoint* __restrict__ outKps,
                 uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN) {
+  pdl_wait();
   __shared__ float4 sPat[8 * 32];        // [bit][lane] = (x0, y0, x1, y1) of pattern pair lane*8+bit
   __shared__ uint32_t sWU[32 * 8];       // [row v+15][chunk]: u (s8) inside the disc, else 0
   __shared__ uint32_t sWO[32 * 8];       // [row][chunk]: 1 inside the disc, else 0
@@ -161,7 +162,7 @@ void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const Fra
                      int* outN, int nframes, cudaStream_t s) {
   const int maxKp = hGeom.keptPerFrame;
   dim3 grid((maxKp + kDescKpPerCta - 1) / kDescKpPerCta, nframes);
-  describe_kernel<<<grid, kDescWarps * 32, 0, s>>>(pyr, blurArena, hGeom, kept, keptCount, outKps, outDesc, cap, outN);
+  launch_pdl(describe_kernel, grid, dim3(kDescWarps * 32), 0, s, pyr, blurArena, hGeom, kept, keptCount, outKps, outDesc, cap, outN);
 }
 
 // ---- array versions of the float helpers, for the unit parity tests ----------------------------

@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(kFastThreads, 4)
 fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
                   uint32_t* __restrict__ cand, int* __restrict__ candCount, int* __restrict__ overflow,
                   int wordsPerWarp) {
+  pdl_wait();
   extern __shared__ __align__(16) uint32_t smemFast[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * kFastWarps + warp;
@@ -357,7 +358,7 @@ int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* can
     if (e != cudaSuccess) return (int)e;
   }
   dim3 grid((hGeom.totalCells + kFastWarps - 1) / kFastWarps, nframes);
-  fast_cells_kernel<<<grid, kFastThreads, smem, s>>>(pyr, hGeom, cand, candCount, overflow, words);
+  launch_pdl(fast_cells_kernel, grid, dim3(kFastThreads), smem, s, pyr, hGeom, cand, candCount, overflow, words);
   return 0;
 }
 

@@ -297,6 +297,7 @@ __global__ void __launch_bounds__(kOctThreads)
 octree_kernel(const FrameSetGeom* __restrict__ g, const uint32_t* __restrict__ cand,
               const int* __restrict__ candCount, uint16_t* __restrict__ nodeScratch,
               uint32_t* __restrict__ kept, int* __restrict__ keptCount, int cap) {
+  pdl_wait();
   extern __shared__ __align__(16) unsigned char smemRaw[];
   const int level = blockIdx.x, f = blockIdx.y, nl = g->nlevels;
   const LevelGeom& L = g->lv[level];
@@ -334,7 +335,7 @@ int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const ui
     configured = smem;
   }
   dim3 grid(hGeom.nlevels, nframes);
-  octree_kernel<<<grid, kOctThreads, smem, s>>>(dGeom, cand, candCount, nodeScratch, kept, keptCount, cap);
+  launch_pdl(octree_kernel, grid, dim3(kOctThreads), smem, s, dGeom, cand, candCount, nodeScratch, kept, keptCount, cap);
   return 0;
 }
 

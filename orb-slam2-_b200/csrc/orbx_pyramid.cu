@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(256)
 resize_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int srcPitch,
               uint8_t* __restrict__ dst, long long dstFrameStride, int dstPitch, int dw, int dh,
               const ResizeTap* __restrict__ xt, const ResizeTap* __restrict__ yt) {
+  pdl_wait();
   const int dx = blockIdx.x * 32 + threadIdx.x;
   const int dy = blockIdx.y * 8 + threadIdx.y;
   if (dx >= dw || dy >= dh) return;
@@ -70,6 +71,7 @@ __global__ void __launch_bounds__(32 * kResizeBands)
 resize4_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int srcPitch,
                uint8_t* __restrict__ dst, long long dstFrameStride, int dstPitch, int dw, int dh,
                const ResizeGroup* __restrict__ xg, const ResizeTap* __restrict__ yt) {
+  pdl_wait();
   const int gx = blockIdx.x * 32 + threadIdx.x;  // group of 4 destination pixels
   const int dy0 = (blockIdx.y * kResizeBands + threadIdx.y) * kResizeRows;
   if (4 * gx >= dw || dy0 >= dh) return;
@@ -122,12 +124,12 @@ void launch_resize(const uint8_t* src, long long srcFrameStride, int srcPitch, i
   if (t.xg && aligned) {
     const int rowsPerCta = kResizeRows * kResizeBands;
     dim3 grid(((dw + 3) / 4 + 31) / 32, (dh + rowsPerCta - 1) / rowsPerCta, nframes);
-    resize4_kernel<<<grid, dim3(32, kResizeBands), 0, s>>>(src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,
-                                          t.xg, t.yt);
+    launch_pdl(resize4_kernel, grid, dim3(32, kResizeBands), 0, s, src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch,
+               dw, dh, t.xg, t.yt);
   } else {
     dim3 grid((dw + 31) / 32, (dh + 7) / 8, nframes);
-    resize_kernel<<<grid, dim3(32, 8), 0, s>>>(src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,
-                                         t.xt, t.yt);
+    launch_pdl(resize_kernel, grid, dim3(32, 8), 0, s, src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,
+               t.xt, t.yt);
   }
 }
 
@@ -235,6 +237,7 @@ __device__ __forceinline__ void blur_strip8(const uint8_t* __restrict__ src, int
 __global__ void __launch_bounds__(kBlurWarps * 32)
 blur_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
             uint8_t* __restrict__ blurArena) {
+  pdl_wait();
   const int task = (blockIdx.x * kBlurWarps + (threadIdx.x >> 5)) * 4 + ((threadIdx.x & 31) >> 3);
   const bool valid = task < g.totalTiles;
   int level = 0;
@@ -285,7 +288,7 @@ void blur_tiles_for(int w, int h, int* tilesX, int* tilesY) {
 void launch_blur(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint8_t* blurArena, int nframes, cudaStream_t s) {
   const int perCta = kBlurWarps * 4;
   dim3 grid((hGeom.totalTiles + perCta - 1) / perCta, nframes);
-  blur_kernel<<<grid, kBlurWarps * 32, 0, s>>>(pyr, hGeom, blurArena);
+  launch_pdl(blur_kernel, grid, dim3(kBlurWarps * 32), 0, s, pyr, hGeom, blurArena);
 }
 
 void launch_blur_single(const uint8_t* src, int srcPitch, uint8_t* dst, int dstPitch, int w, int h, cudaStream_t s) {
