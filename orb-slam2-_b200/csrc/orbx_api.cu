@@ -313,12 +313,7 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
     if (!imgs[f]) { set_error("imgs[%d] is null", f); return ORBX_ERR_ARG; }
     contiguous = contiguous && imgs[f] == imgs[0] + (size_t)f * stride * height;
   }
-  // timing experiments only: ORBX_DEBUG_SKIP_H2D=<n> stops copying frames after the first n chunk submissions
-  // (the lanes then keep re-processing the frames they already hold)
-  static const long dbgSkipAfter = std::getenv("ORBX_DEBUG_SKIP_H2D") ? std::atol(std::getenv("ORBX_DEBUG_SKIP_H2D")) : -1;
-  static long dbgSubmits = 0;
-  if (dbgSkipAfter >= 0 && dbgSubmits++ >= dbgSkipAfter) {
-  } else if (contiguous && g.lv[0].planeBytes == (long long)g.lv[0].pitch * height) {
+  if (contiguous && g.lv[0].planeBytes == (long long)g.lv[0].pitch * height) {
     // frames back to back on the host: one copy of count*height rows
     if (stride == (size_t)width && g.lv[0].pitch == width) {
       ORBX_CUDA_TRY(cudaMemcpyAsync(l0, imgs[0], (size_t)width * height * count, cudaMemcpyHostToDevice, s));
