@@ -251,3 +251,34 @@ def test_odd_width_batch_equals_single(pkg, w, h):
         assert np.array_equal(desc[f, :n[f]], sd), f
         assert np.array_equal(dk[f, :n[f]].cpu().numpy().view(np.uint8).reshape(-1), sk.view(np.uint8).reshape(-1)), f
         assert np.array_equal(dd[f, :n[f]].cpu().numpy(), sd), f
+
+
+def test_edge_inputs(pkg, oracle):
+    """Flat images give no keypoints (the reference returns early with empty outputs, R/src/ORBextractor.cpp:1139-1146);
+    dense noise, a checkerboard, one level, very few / very many features agree with the oracle; frames whose pyramid
+    gets smaller than the reference's 30-pixel FAST grid are refused with an error instead of the reference's division
+    by zero (:844-847)."""
+    for value in (0, 255):
+        ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+        k, d = ex(np.full((480, 640), value, np.uint8))
+        assert len(k) == 0 and d is None      # _descriptors.release() (:1145)
+    cases = [("noise", np.random.default_rng(1).integers(0, 256, (480, 640), dtype=np.uint8), 1000, 8),
+             ("checker", ((np.indices((480, 640)).sum(0) // 4) % 2 * 255).astype(np.uint8), 1000, 8),
+             ("one level", pkg.synth.frame(640, 480, 3), 1000, 1),
+             ("few", pkg.synth.frame(640, 480, 3), 10, 8),
+             ("many", pkg.synth.frame(640, 480, 3), 8000, 8),
+             ("odd size", pkg.synth.frame(641, 479, 3), 1000, 8)]
+    for name, img, nf, nlev in cases:
+        ex = pkg.ORBextractor(nf, 1.2, nlev, 20, 7, max_width=img.shape[1], max_height=img.shape[0])
+        k, d = ex(img)
+        ok, od = oracle.Extractor(nf, 1.2, nlev, 20, 7)(img)
+        assert len(k) == len(ok) > 0, name
+        assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od), name
+    for w, h in ((160, 120), (64, 48)):
+        with pytest.raises(pkg.OrbxError, match="too small"):     # refused when the handle is created for that shape
+            pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    ex = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    with pytest.raises(pkg.OrbxError, match="too small"):         # ... or when such a frame reaches a larger handle
+        ex(pkg.synth.frame(160, 120, 3))
+    k, d = ex(pkg.synth.frame(640, 480, 3))                       # the handle stays usable after the refusal
+    assert len(k) > 400
