@@ -161,16 +161,14 @@ __device__ __forceinline__ void blur_hrow(uint32_t l, uint32_t c, uint32_t r, in
 }
 
 __device__ __forceinline__ uint32_t blur_vcol(const int (&H)[7][4], int r) {
-  // rows r-6..r of the rotating window are taps 0..6
-  uint32_t out = 0;
+  // rows r-6..r of the rotating window are taps 0..6. The rounding constant rides in the multiply-add chain and
+  // the four results (< 2^24, wanted bits 16..23) are packed with three PRMT instead of shift/shift/or per pixel.
+  uint32_t v[4];
 #pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const uint32_t v = 18u * (uint32_t)(H[(r - 6) % 7][j] + H[r % 7][j]) +
-                       34u * (uint32_t)(H[(r - 5) % 7][j] + H[(r - 1) % 7][j]) +
-                       48u * (uint32_t)(H[(r - 4) % 7][j] + H[(r - 2) % 7][j]) + 56u * (uint32_t)H[(r - 3) % 7][j];
-    out |= ((v + 32768u) >> 16) << (8 * j);
-  }
-  return out;
+  for (int j = 0; j < 4; j++)
+    v[j] = 18u * (uint32_t)(H[(r - 6) % 7][j] + H[r % 7][j]) + 34u * (uint32_t)(H[(r - 5) % 7][j] + H[(r - 1) % 7][j]) +
+           48u * (uint32_t)(H[(r - 4) % 7][j] + H[(r - 2) % 7][j]) + (56u * (uint32_t)H[(r - 3) % 7][j] + 32768u);
+  return __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
 }
 
 // Fast path: source rows 4-byte aligned, w >= 12. Eight lanes own a 32-px wide strip; every lane does
