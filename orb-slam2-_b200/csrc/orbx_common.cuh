@@ -35,7 +35,7 @@ constexpr int kHalfPatch = 15;    // HALF_PATCH_SIZE (:75)
 constexpr int kPatch = 31;        // PATCH_SIZE      (:74)
 constexpr int kMaxLevels = ORBX_MAX_LEVELS;
 constexpr int kMaxCellDim = 64;   // wCell/hCell upper bound handled by the FAST kernel (< 60 by construction)
-constexpr int kMaxNodes = 2048;   // per-level octree quota + slack the selection kernel can hold in smem
+constexpr int kMaxNodes = 3400;   // per-level octree quota + slack: 66 B of smem per node, 224 KB of the 227 KB a CTA may take
 
 // Geometry of one pyramid level, fixed per (frame shape, extractor parameters).
 struct LevelGeom {
