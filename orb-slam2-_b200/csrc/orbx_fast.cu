@@ -100,11 +100,13 @@ __device__ __forceinline__ uint32_t fast_margin2(const uint32_t (&W)[7][6], uint
 }
 
 // Upper bound of the margin of two adjacent pixels from the four compass ring pixels (n = (0,3), s = (0,-3),
-// e = (3,0), w = (-3,0)) alone: max(bound - th, 0) per 16-bit lane. See pass 1 of the kernel.
+// e = (3,0), w = (-3,0)) alone: max(bound - th, 0) per 16-bit lane. See pass 1 of the kernel. The minimum over
+// the four adjacent compass pairs of the pair maximum is, by distributivity, max(min(n,s), min(e,w)): 3 packed
+// operations per side instead of 6.
 __device__ __forceinline__ uint32_t fast_compass_bound(uint32_t n, uint32_t s, uint32_t e, uint32_t w, uint32_t v,
                                                        uint32_t negThBias) {
-  const uint32_t Ac = __vimin3_u16x2(__vmaxu2(n, e), __vmaxu2(e, s), __vminu2(__vmaxu2(s, w), __vmaxu2(w, n)));
-  const uint32_t Bc = __vimax3_u16x2(__vminu2(n, e), __vminu2(e, s), __vmaxu2(__vminu2(s, w), __vminu2(w, n)));
+  const uint32_t Ac = __vmaxu2(__vminu2(n, s), __vminu2(e, w));
+  const uint32_t Bc = __vminu2(__vmaxu2(n, s), __vmaxu2(e, w));
   const uint32_t dark = v + 0x01000100u - Ac;
   const uint32_t bright = Bc + 0x01000100u - v;
   return __viaddmax_s16x2_relu(__vmaxu2(dark, bright), negThBias, 0u);
@@ -202,6 +204,9 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   // per 16-bit lane: -(256 + minTh)
   const uint32_t negTh = (uint32_t)(-(256 + minTh)) & 0xffffu;
   const uint32_t negThBias = negTh | (negTh << 16);
+  // Scores are kept as max(m - minTh, 0): a pixel whose margin exceeds iniTh stores at least iniByte.
+  const int iniByte = max(iniTh - minTh + 1, 1);
+  const uint32_t negIni = ((uint32_t)(-(iniByte - 1)) & 0xffffu) * 0x00010001u;
   const int nTasks = sh * nG;
   const int dy = 32 / nG, dq = 32 - dy * nG;
   const int y0 = lane / nG, q0 = lane - y0 * nG;
@@ -209,108 +214,138 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   // ---- pass 1, every task: compass bound. Any 9-arc of the ring contains two adjacent compass pixels
   //      (p0, p4, p8, p12), so  A >= Ac = min over adjacent compass pairs of their max  and
   //      B <= Bc = max over those pairs of their min, hence m <= max(v - Ac, Bc - v): a task whose four
-  //      bounds are all <= minTh has an all-zero score word and is dropped after 19 instead of 92 packed
-  //      operations per pixel pair. Survivors are queued as y<<8 | q. Rounds are warp-uniform (lanes past
-  //      the last task idle inside the round) so that the ballots are full-warp ones. ----
-  int nQ1 = 0;
+  //      bounds are all <= minTh has an all-zero score word and is dropped after 12 instead of 92 packed
+  //      operations per pixel pair. The others are queued as y<<8 | q in two classes: list A (some bound
+  //      above iniTh) grows from the front of the queue, list B (bounds in (minTh, iniTh]) from its back.
+  //      B is only ever scored if the cell turns out empty at iniTh (phase 1 below). Rounds are warp-uniform
+  //      (lanes past the last task idle inside the round) so that the ballots are full-warp ones. ----
+  int nA = 0, nB = 0;
   {
     int y = y0, q = q0;
     for (int t0 = 0; t0 < nTasks; t0 += 32) {
-      uint32_t any = 0u;
+      uint32_t any = 0u, hi = 0u;
       if (t0 + lane < nTasks) {
         const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);  // window = tile columns 4q..4q+11
         const uint2 top = tp[1], bot = tp[6 * nW + 1];                             // columns 4..7 of rows y-3, y+3
         const uint2 c01 = tp[3 * nW], c23 = tp[3 * nW + 1], c45 = tp[3 * nW + 2];
         const uint32_t C[6] = {c01.x, c01.y, c23.x, c23.y, c45.x, c45.y};
-        any = fast_compass_bound(top.x, bot.x, pair16<7>(C), pair16<1>(C), C[2], negThBias) |
-              fast_compass_bound(top.y, bot.y, pair16<9>(C), pair16<3>(C), C[3], negThBias);
+        const uint32_t b01 = fast_compass_bound(top.x, bot.x, pair16<7>(C), pair16<1>(C), C[2], negThBias);
+        const uint32_t b23 = fast_compass_bound(top.y, bot.y, pair16<9>(C), pair16<3>(C), C[3], negThBias);
+        any = b01 | b23;
+        hi = __viaddmax_s16x2_relu(__vmaxu2(b01, b23), negIni, 0u);
       }
-      const uint32_t passMask = __ballot_sync(0xffffffffu, any != 0u);
-      if (any != 0u) queue[nQ1 + __popc(passMask & ((1u << lane) - 1u))] = (uint16_t)((y << 8) | q);
-      nQ1 += __popc(passMask);
+      const uint32_t maskA = __ballot_sync(0xffffffffu, hi != 0u);
+      const uint32_t maskB = __ballot_sync(0xffffffffu, any != 0u) & ~maskA;
+      const uint32_t below = (1u << lane) - 1u;
+      if (hi != 0u) queue[nA + __popc(maskA & below)] = (uint16_t)((y << 8) | q);
+      else if (any != 0u) queue[nTasks - 1 - nB - __popc(maskB & below)] = (uint16_t)((y << 8) | q);
+      nA += __popc(maskA);
+      nB += __popc(maskB);
       y += dy; q += dq;
       if (q >= nG) { q -= nG; y++; }
     }
   }
   __syncwarp();
-  if (nQ1 == 0) return;
+  if (nA + nB == 0) return;
 
-  // ---- pass 2, queued tasks: score map max(m - minTh, 0) (0 = not a corner at minTh). Only a task whose
-  //      word holds a corner can keep one after suppression: those are re-queued in place (entry j of
-  //      round k is read before the round's ballot, written slots are <= the ones already read). ----
-  int nQ = 0;
-  for (int j0 = 0; j0 < nQ1; j0 += 32) {
-    uint32_t word = 0u;
-    int e = 0;
-    if (j0 + lane < nQ1) {
-      e = queue[j0 + lane];
-      const int y = e >> 8, q = e & 0xff;
-      const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);
-      uint32_t W[7][6];
+  // Phase 0 scores list A and suppresses at iniTh. A pixel above iniTh can only lose to a neighbour whose margin
+  // is also above iniTh, and such a neighbour's task is in A: the phase-0 result is exactly cv::FAST(cell, iniTh).
+  // If it is empty (:875-883), phase 1 scores list B as well and suppresses everything at minTh.
+  uint32_t* kept = tile;  // survivors' score words; only written once the patch is dead (see below)
+  int nQ = 0;             // tasks whose score word holds a corner at minTh: queue[0 .. nQ)
+  int nS = 0;             // tasks that keep a corner after suppression: queue[0 .. nS), kept[0 .. nS)
+#pragma unroll 1
+  for (int phase = 0; phase < 2; phase++) {
+    const int srcBase = phase == 0 ? 0 : nTasks - nB;
+    const int srcN = phase == 0 ? nA : nB;
+    // ---- pass 2, listed tasks: score map max(m - minTh, 0) (0 = not a corner at minTh). Only a task whose
+    //      word holds a corner can keep one after suppression: those are appended to queue[0 .. nQ). Entry j of
+    //      a round is read before the round's ballot and nQ never overtakes the read position (phase 0: nQ <=
+    //      entries read; phase 1: nQ <= nA + entries of B read <= nTasks - nB + entries read). ----
+    for (int j0 = 0; j0 < srcN; j0 += 32) {
+      uint32_t word = 0u;
+      int e = 0;
+      if (j0 + lane < srcN) {
+        e = queue[srcBase + j0 + lane];
+        const int y = e >> 8, q = e & 0xff;
+        const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);
+        uint32_t W[7][6];
 #pragma unroll
-      for (int j = 0; j < 7; j++) {
-        const uint2 w01 = tp[j * nW], w23 = tp[j * nW + 1], w45 = tp[j * nW + 2];
-        W[j][0] = w01.x; W[j][1] = w01.y; W[j][2] = w23.x; W[j][3] = w23.y; W[j][4] = w45.x; W[j][5] = w45.y;
+        for (int j = 0; j < 7; j++) {
+          const uint2 w01 = tp[j * nW], w23 = tp[j * nW + 1], w45 = tp[j * nW + 2];
+          W[j][0] = w01.x; W[j][1] = w01.y; W[j][2] = w23.x; W[j][3] = w23.y; W[j][4] = w45.x; W[j][5] = w45.y;
+        }
+        const uint32_t u01 = fast_margin2<4>(W, negThBias);
+        const uint32_t u23 = fast_margin2<6>(W, negThBias);
+        word = __byte_perm(u01, u23, 0x6420);
+        const int col0 = 4 * (q + 1);
+        const int skipLo = a - col0, skipHi = col0 + 4 - b;
+        if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
+        if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
+        smap[(y + 1) * nW + q + 1] = word;
       }
-      const uint32_t u01 = fast_margin2<4>(W, negThBias);
-      const uint32_t u23 = fast_margin2<6>(W, negThBias);
-      word = __byte_perm(u01, u23, 0x6420);
-      const int col0 = 4 * (q + 1);
-      const int skipLo = a - col0, skipHi = col0 + 4 - b;
-      if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
-      if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
-      smap[(y + 1) * nW + q + 1] = word;
+      const uint32_t liveMask = __ballot_sync(0xffffffffu, word != 0u);
+      if (word != 0u) queue[nQ + __popc(liveMask & ((1u << lane) - 1u))] = (uint16_t)e;
+      nQ += __popc(liveMask);
     }
-    const uint32_t liveMask = __ballot_sync(0xffffffffu, word != 0u);
-    if (word != 0u) queue[nQ + __popc(liveMask & ((1u << lane) - 1u))] = (uint16_t)e;
-    nQ += __popc(liveMask);
-  }
-  __syncwarp();
-  if (nQ == 0) return;
+    __syncwarp();
 
-  // ---- cell-local 3x3 strict non-max suppression, packed: the 8-neighbour maximum of two adjacent
-  //      pixels is 4 VIMNMX on 16x2 lanes; the survivors' scores of queue entry j go to kept[j], which
-  //      reuses the patch rows ----
-  uint32_t* kept = tile;
-  const int iniByte = max(iniTh - minTh + 1, 1);  // stored value of a pixel whose score is iniTh
-  uint32_t iniFlag = 0;
-  {
-    const uint32_t negIni = ((uint32_t)(-(iniByte - 1)) & 0xffffu) * 0x00010001u;
-    for (int j = lane; j < nQ; j += 32) {
-      const int e = queue[j], y = e >> 8, q = e & 0xff;
-      const uint32_t* mp = &smap[y * nW + q];  // map rows y, y+1, y+2 = image rows y-1, y, y+1
-      uint32_t E[3][5];                        // column pairs (3,4) (4,5) (5,6) (6,7) (7,8) of the 12-byte window
+    // ---- cell-local 3x3 strict non-max suppression, packed: the 8-neighbour maximum of two adjacent pixels is
+    //      4 VIMNMX on 16x2 lanes. Scores below this phase's threshold are cleared and the tasks that keep a
+    //      corner are compacted in place once more, their score words going to kept[], which reuses the patch
+    //      rows: a word is only stored when a survivor exists, i.e. when no further phase needs the patch (and
+    //      then nothing was compacted either: queue[0 .. nQ) is still whole for phase 1). ----
+    const uint32_t negKeep = phase == 0 ? negIni : 0u;
+    for (int j0 = 0; j0 < nQ; j0 += 32) {
+      uint32_t word = 0u;
+      int e = 0;
+      if (j0 + lane < nQ) {
+        e = queue[j0 + lane];
+        const int y = e >> 8, q = e & 0xff;
+        const uint32_t* mp = &smap[y * nW + q];  // map rows y, y+1, y+2 = image rows y-1, y, y+1
+        uint32_t E[3][5];                        // column pairs (3,4) (4,5) (5,6) (6,7) (7,8) of the 12-byte window
 #pragma unroll
-      for (int r = 0; r < 3; r++) {
-        const uint32_t w0 = mp[r * nW], w1 = mp[r * nW + 1], w2 = mp[r * nW + 2];
-        E[r][0] = ex2<3>(w0, w1, w2);
-        E[r][1] = ex2<4>(w0, w1, w2);
-        E[r][2] = ex2<5>(w0, w1, w2);
-        E[r][3] = ex2<6>(w0, w1, w2);
-        E[r][4] = ex2<7>(w0, w1, w2);
-      }
-      uint32_t k2[2];
+        for (int r = 0; r < 3; r++) {
+          const uint32_t w0 = mp[r * nW], w1 = mp[r * nW + 1], w2 = mp[r * nW + 2];
+          E[r][0] = ex2<3>(w0, w1, w2);
+          E[r][1] = ex2<4>(w0, w1, w2);
+          E[r][2] = ex2<5>(w0, w1, w2);
+          E[r][3] = ex2<6>(w0, w1, w2);
+          E[r][4] = ex2<7>(w0, w1, w2);
+        }
+        uint32_t k2[2];
 #pragma unroll
-      for (int p = 0; p < 2; p++) {  // pixel pairs (0,1) and (2,3): left/centre/right pairs E[.][2p .. 2p+2]
-        const uint32_t up = __vimax3_u16x2(E[0][2 * p], E[0][2 * p + 1], E[0][2 * p + 2]);
-        const uint32_t dn = __vimax3_u16x2(E[2][2 * p], E[2][2 * p + 1], E[2][2 * p + 2]);
-        const uint32_t M = __vimax3_u16x2(up, dn, __vmaxu2(E[1][2 * p], E[1][2 * p + 2]));
-        const uint32_t sc = E[1][2 * p + 1];
-        const uint32_t d = __viaddmax_s16x2_relu(sc + 0x01000100u - M, 0xff00ff00u, 0u);  // max(s - M, 0)
-        k2[p] = __vminu2(sc, d << 8);                                                     // s if s > M else 0
-        iniFlag |= __viaddmax_s16x2_relu(k2[p], negIni, 0u);
+        for (int p = 0; p < 2; p++) {  // pixel pairs (0,1) and (2,3): left/centre/right pairs E[.][2p .. 2p+2]
+          const uint32_t up = __vimax3_u16x2(E[0][2 * p], E[0][2 * p + 1], E[0][2 * p + 2]);
+          const uint32_t dn = __vimax3_u16x2(E[2][2 * p], E[2][2 * p + 1], E[2][2 * p + 2]);
+          const uint32_t M = __vimax3_u16x2(up, dn, __vmaxu2(E[1][2 * p], E[1][2 * p + 2]));
+          const uint32_t sc = E[1][2 * p + 1];
+          const uint32_t d = __viaddmax_s16x2_relu(sc + 0x01000100u - M, 0xff00ff00u, 0u);  // max(s - M, 0)
+          const uint32_t won = __vminu2(sc, d << 8);                                         // s if s > M else 0
+          // keep s only if s >= threshold byte: max(s - (th-1), 0) != 0 per lane
+          const uint32_t over = __viaddmax_s16x2_relu(won, negKeep, 0u);
+          k2[p] = __vminu2(won, over * 0xffu);  // over <= 255 per lane: over*255 >= won iff over != 0
+        }
+        word = __byte_perm(k2[0], k2[1], 0x6420);
       }
-      kept[j] = __byte_perm(k2[0], k2[1], 0x6420);
+      const uint32_t keepMask = __ballot_sync(0xffffffffu, word != 0u);
+      if (word != 0u) {
+        const int slot = nS + __popc(keepMask & ((1u << lane) - 1u));
+        queue[slot] = (uint16_t)e;
+        kept[slot] = word;
+      }
+      nS += __popc(keepMask);
     }
+    __syncwarp();
+    if (nS > 0 || iniByte == 1) break;  // iniByte == 1: phase 0 already was the suppression at minTh
   }
-  // "cell empty after NMS at iniThFAST?" (:875-883) is a warp-wide vote
-  const bool useIni = __any_sync(0xffffffffu, iniFlag != 0);
-  const int thByte = useIni ? iniByte : 1;
+  if (nS == 0) return;
+
   int mine = 0;
-  for (int j = lane; j < nQ; j += 32) {  // each lane re-reads only what it wrote
+  for (int j = lane; j < nS; j += 32) {
     const uint32_t word = kept[j];
 #pragma unroll
-    for (int i = 0; i < 4; i++) mine += (int)((word >> (8 * i)) & 0xff) >= thByte;
+    for (int i = 0; i < 4; i++) mine += ((word >> (8 * i)) & 0xff) != 0;
   }
   // exclusive prefix of `mine` over the warp + total
   int incl = mine;
@@ -320,7 +355,6 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
     if (lane >= o) incl += v;
   }
   const int total = __shfl_sync(0xffffffffu, incl, 31);
-  if (total == 0) return;
   int base = 0;
   if (lane == 0) {
     base = atomicAdd(&candCount[f * nl + level], total);
@@ -329,20 +363,18 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   base = __shfl_sync(0xffffffffu, base, 0);
   int slot = base + incl - mine;
   const long long slotBase = L.candOff + (long long)f * L.candCap;
-  for (int j = lane; j < nQ; j += 32) {
+  for (int j = lane; j < nS; j += 32) {
     const uint32_t word = kept[j];
-    if (word) {
-      const int e = queue[j], y = e >> 8, q = e & 0xff;
+    const int e = queue[j], y = e >> 8, q = e & 0xff;
 #pragma unroll
-      for (int i = 0; i < 4; i++) {
-        const int sc = (word >> (8 * i)) & 0xff;
-        if (sc >= thByte) {
-          // cv::FAST's cornerScore = sc + minTh - 1; coordinates relative to minBorder:
-          // cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
-          if (slot < L.candCap)
-            cand[slotBase + slot] = pack_cand(4 * (q + 1) + i - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, sc + minTh - 1);
-          slot++;
-        }
+    for (int i = 0; i < 4; i++) {
+      const int sc = (word >> (8 * i)) & 0xff;
+      if (sc) {
+        // cv::FAST's cornerScore = sc + minTh - 1; coordinates relative to minBorder:
+        // cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
+        if (slot < L.candCap)
+          cand[slotBase + slot] = pack_cand(4 * (q + 1) + i - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, sc + minTh - 1);
+        slot++;
       }
     }
   }

@@ -82,6 +82,18 @@ def test_pyramid_blur_and_fast_candidates(pkg, oracle, w, h, nf, kind):
             assert np.array_equal(ex.image_pyramid_level(l, blurred=True), ox.level(l, blurred=True)), f"blur {l}"
 
 
+def test_fast_candidates_weak_corner_in_cell_with_strong_bounds_only(pkg, oracle):
+    """A cell whose only corners are weak (minThFAST < margin <= iniThFAST) while every pixel that passes the kernel's
+    cheap first test has a bound ABOVE iniThFAST: the fallback suppression at minThFAST must still run although the
+    list of weakly bounded tasks is empty (frame 3 of the synthetic set has such a cell on level 0)."""
+    img = pkg.synth.frame(640, 480, 3)
+    ex = pkg.ORBextractor(1000, 1.2, 1, 20, 7, max_width=640, max_height=480)
+    ox = oracle.Extractor(1000, 1.2, 1, 20, 7)
+    ex(img)
+    ox(img)
+    assert _cands_set(ex.level_candidates(0)) == _cands_set(ox.candidates(0))
+
+
 def test_octree_matches_oracle_in_order(pkg, oracle):
     ox = oracle.Extractor(1000, 1.2, 8, 20, 7)
     for seed, kind in [(31, "shapes"), (32, "shapes"), (33, "noise")]:
