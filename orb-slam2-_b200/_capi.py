@@ -1,12 +1,14 @@
 """ctypes binding of liborbx.so (include/orbx.h). Fails loudly when the CUDA library is missing:
 there is no CPU fallback anywhere in this package."""
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
 
 HERE = Path(__file__).resolve().parent
-LIB_PATH = HERE / "liborbx.so"
+# ORBX_LIB: an experiment build of the same library (orb-slam2-_b200/build.py build_variant); never a different backend
+LIB_PATH = Path(os.environ["ORBX_LIB"]) if os.environ.get("ORBX_LIB") else HERE / "liborbx.so"
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])

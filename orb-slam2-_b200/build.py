@@ -62,6 +62,33 @@ def build(force=False, verbose=False):
     return LIB
 
 
+def build_variant(name, defines):
+    """Experiment aid (tools/variants.sh): the whole library again with extra -D flags ->
+    orb-slam2-_b200/variants/liborbx_<name>.so, picked up by the Python mirror through ORBX_LIB=<path>."""
+    objdir = CSRC / f"build_{name}"
+    objdir.mkdir(exist_ok=True)
+    out = HERE / "variants"
+    out.mkdir(exist_ok=True)
+    lib = out / f"liborbx_{name}.so"
+
+    def compile_one(src):
+        obj = objdir / (src.stem + ".o")
+        r = subprocess.run([NVCC] + FLAGS + [f"-D{d}" for d in defines] + ["-c", str(src), "-o", str(obj)],
+                           capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed on {src.name}:\n{r.stdout}\n{r.stderr}")
+        (objdir / (src.stem + ".ptxas.txt")).write_text(r.stderr)
+        return obj
+
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        objs = list(ex.map(compile_one, sources()))
+    r = subprocess.run([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(lib)] +
+                       [str(o) for o in objs], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    return lib
+
+
 def build_host_mirror(force=False):
     """host/libmirror_test.so: the C++ drop-in ORBextractor (host/ORBextractor.{h,cc}) compiled against the
     cv shim (OpenCV C++ is not installed here) plus C test entry points; linked to liborbx.so. Used by

@@ -24,12 +24,34 @@
 // of the scoring pass is content independent. (v1 was one thread per pixel with
 // early-outs: ALU-pipe bound at 18/32 active lanes. v2 was one 128-thread CTA per cell: 80 % lane use
 // because sh*nG tasks rarely fill whole rounds of 128; with 32-lane rounds the tail is ~5 %.)
+#include <type_traits>
+
 #include "orbx_common.cuh"
 
 namespace orbx {
 
-constexpr int kFastWarps = 8;                 // cells per CTA
+#ifndef ORBX_FAST_WARPS
+#define ORBX_FAST_WARPS 8
+#endif
+#ifndef ORBX_FAST_MINB
+#define ORBX_FAST_MINB 4
+#endif
+constexpr int kFastWarps = ORBX_FAST_WARPS;   // cells per CTA
 constexpr int kFastThreads = kFastWarps * 32;
+
+// cInv16[n] = 65536/n + 1: (i * cInv16[n]) >> 16 == i / n for n <= 64, i <= 1023 (and for i <= 4096 when n <= 26);
+// the kernel has no integer division on its path.
+struct Inv16Table { uint32_t v[65]; };  // v[1] = 65537 needs 17 bits
+constexpr Inv16Table make_inv16() {
+  Inv16Table t{};
+  t.v[0] = 0;
+  for (int n = 1; n <= 64; n++) t.v[n] = (uint32_t)(65536 / n + 1);
+  return t;
+}
+__constant__ Inv16Table cInv16 = make_inv16();
+__device__ __forceinline__ int div_small(int i, int n) {  // see cInv16
+  return (int)(((uint32_t)i * cInv16.v[n]) >> 16);
+}
 
 // bytes I, I+1 of the 12-byte window (w0,w1,w2) as two 16-bit lanes
 template <int I>
@@ -121,7 +143,7 @@ __host__ __device__ inline int fast_cell_words(int wCell, int hCell) {
   return (words + 1) & ~1;
 }
 
-__global__ void __launch_bounds__(kFastThreads, 4)
+__global__ void __launch_bounds__(kFastThreads, ORBX_FAST_MINB)
 fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
                   uint32_t* __restrict__ cand, int* __restrict__ candCount, int* __restrict__ overflow,
                   int wordsPerWarp) {
@@ -135,7 +157,8 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   while (level + 1 < nl && cell >= g.lv[level + 1].cellBase) level++;
   const LevelGeom& L = g.lv[level];
   const int cidx = cell - L.cellBase;
-  const int ci = cidx / L.nCols, cj = cidx - ci * L.nCols;
+  const int ci = (L.nCols <= 64 && cidx < 1024) ? div_small(cidx, L.nCols) : cidx / L.nCols;
+  const int cj = cidx - ci * L.nCols;
   const int f = blockIdx.y;
 
   // cell rectangle (R/src/ORBextractor.cpp:851-870)
@@ -165,37 +188,48 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   const uint8_t* src = pyr.lvl[level] + (long long)f * pyr.frameStride[level] + (long long)iniY * pitch + gx0;
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)pitch) & 3) == 0;
   {
-    // Word idx of the patch (row idx / nW, word idx % nW) goes to tile[2 idx]. Eight loads are in flight per
-    // lane before the first one is used: with one load per loop trip the warp sat out a full DRAM latency
-    // 13 times per cell (ncu r1_r: 39 % of the kernel's stall samples were on that one dependency).
+    // Word idx of the patch (row idx / nW, word idx % nW) goes to tile[2 idx]; lane handles idx = lane, lane+32, ...
+    // Row and column advance incrementally (32 = dr * nW + dc per step), so a word costs a pointer add, the load,
+    // two PRMT and one 8-byte store. Eight loads are in flight per lane before the first one is used: with one
+    // load per loop trip the warp sat out a full DRAM latency 13 times per cell.
     const int total = ch * nW;
-    const bool fastDiv = nW <= 26 && total <= 4096;      // (idx * inv) >> 16 == idx / nW on that range
-    const uint32_t inv = 65536u / (uint32_t)nW + 1u;
+    const int dr = div_small(32, nW), dc = 32 - dr * nW;
+    int r = div_small(lane, nW);
+    int c = lane - r * nW;
+    const uint8_t* p = src + (long long)r * pitch + 4 * c;
+    const long long stepNoWrap = (long long)dr * pitch + 4 * dc;
+    const long long stepWrap = stepNoWrap + pitch - 4 * nW;
     constexpr int kInFlight = 8;
-    for (int base = lane; base < total; base += 32 * kInFlight) {
-      uint32_t w[kInFlight];
+    auto stage = [&](auto alignedTag) {
+      constexpr bool kAligned = decltype(alignedTag)::value;
+      for (int base = lane; base < total; base += 32 * kInFlight) {
+        uint32_t w[kInFlight];
 #pragma unroll
-      for (int k = 0; k < kInFlight; k++) {
-        const int idx = base + 32 * k;
-        w[k] = 0u;
-        if (idx < total) {
-          const int r = fastDiv ? (int)(((uint32_t)idx * inv) >> 16) : idx / nW;
-          const uint8_t* p = src + (long long)r * pitch + 4 * (idx - r * nW);
-          if (aligned) {
-            w[k] = *reinterpret_cast<const uint32_t*>(p);
-          } else {
-            w[k] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+        for (int k = 0; k < kInFlight; k++) {
+          w[k] = 0u;
+          if (base + 32 * k < total) {
+            if constexpr (kAligned) {
+              w[k] = *reinterpret_cast<const uint32_t*>(p);
+            } else {
+              w[k] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+            }
           }
+          c += dc;
+          const bool wrap = c >= nW;
+          p += wrap ? stepWrap : stepNoWrap;
+          if (wrap) c -= nW;
+        }
+#pragma unroll
+        for (int k = 0; k < kInFlight; k++) {
+          // bytes -> 16-bit lanes once here instead of once per ring offset in the scoring loop
+          if (base + 32 * k < total)
+            *reinterpret_cast<uint2*>(&tile[2 * (base + 32 * k)]) =
+                make_uint2(__byte_perm(w[k], 0u, 0x4140), __byte_perm(w[k], 0u, 0x4342));
         }
       }
-#pragma unroll
-      for (int k = 0; k < kInFlight; k++) {
-        const int idx = base + 32 * k;
-        // bytes -> 16-bit lanes once here instead of once per ring offset in the scoring loop
-        if (idx < total)
-          *reinterpret_cast<uint2*>(&tile[2 * idx]) = make_uint2(__byte_perm(w[k], 0u, 0x4140), __byte_perm(w[k], 0u, 0x4342));
-      }
-    }
+    };
+    if (aligned) stage(std::true_type{});
+    else stage(std::false_type{});
   }
   for (int i = lane; i < (sh + 2) * nW; i += 32) smap[i] = 0u;
   __syncwarp();
@@ -208,8 +242,9 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   const int iniByte = max(iniTh - minTh + 1, 1);
   const uint32_t negIni = ((uint32_t)(-(iniByte - 1)) & 0xffffu) * 0x00010001u;
   const int nTasks = sh * nG;
-  const int dy = 32 / nG, dq = 32 - dy * nG;
-  const int y0 = lane / nG, q0 = lane - y0 * nG;
+  const int dy = div_small(32, nG), dq = 32 - dy * nG;
+  const int y0 = div_small(lane, nG), q0 = lane - y0 * nG;
+  const uint32_t below = (1u << lane) - 1u;
 
   // ---- pass 1, every task: compass bound. Any 9-arc of the ring contains two adjacent compass pixels
   //      (p0, p4, p8, p12), so  A >= Ac = min over adjacent compass pairs of their max  and
@@ -219,7 +254,7 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   //      above iniTh) grows from the front of the queue, list B (bounds in (minTh, iniTh]) from its back.
   //      B is only ever scored if the cell turns out empty at iniTh (phase 1 below). Rounds are warp-uniform
   //      (lanes past the last task idle inside the round) so that the ballots are full-warp ones. ----
-  int nA = 0, nB = 0;
+  int nA = 0, backB = nTasks - 1;  // next free slot of list B
   {
     int y = y0, q = q0;
     for (int t0 = 0; t0 < nTasks; t0 += 32) {
@@ -236,16 +271,19 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
       }
       const uint32_t maskA = __ballot_sync(0xffffffffu, hi != 0u);
       const uint32_t maskB = __ballot_sync(0xffffffffu, any != 0u) & ~maskA;
-      const uint32_t below = (1u << lane) - 1u;
-      if (hi != 0u) queue[nA + __popc(maskA & below)] = (uint16_t)((y << 8) | q);
-      else if (any != 0u) queue[nTasks - 1 - nB - __popc(maskB & below)] = (uint16_t)((y << 8) | q);
+      if (any != 0u) {  // one store: front slot for class A, back slot for class B
+        const bool isA = hi != 0u;
+        const int rank = __popc((isA ? maskA : maskB) & below);
+        queue[isA ? nA + rank : backB - rank] = (uint16_t)((y << 8) | q);
+      }
       nA += __popc(maskA);
-      nB += __popc(maskB);
+      backB -= __popc(maskB);
       y += dy; q += dq;
       if (q >= nG) { q -= nG; y++; }
     }
   }
   __syncwarp();
+  const int nB = nTasks - 1 - backB;
   if (nA + nB == 0) return;
 
   // Phase 0 scores list A and suppresses at iniTh. A pixel above iniTh can only lose to a neighbour whose margin
@@ -285,7 +323,7 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
         smap[(y + 1) * nW + q + 1] = word;
       }
       const uint32_t liveMask = __ballot_sync(0xffffffffu, word != 0u);
-      if (word != 0u) queue[nQ + __popc(liveMask & ((1u << lane) - 1u))] = (uint16_t)e;
+      if (word != 0u) queue[nQ + __popc(liveMask & (below))] = (uint16_t)e;
       nQ += __popc(liveMask);
     }
     __syncwarp();
@@ -330,7 +368,7 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
       }
       const uint32_t keepMask = __ballot_sync(0xffffffffu, word != 0u);
       if (word != 0u) {
-        const int slot = nS + __popc(keepMask & ((1u << lane) - 1u));
+        const int slot = nS + __popc(keepMask & (below));
         queue[slot] = (uint16_t)e;
         kept[slot] = word;
       }

@@ -25,7 +25,12 @@
 
 namespace orbx {
 
-constexpr int kOctThreads = 512;
+constexpr int kOctThreads = 512;       // launch bound; a lone frame runs its 8 CTAs this wide (latency)
+// A batch runs narrow CTAs instead: the selection is a chain of short barrier-separated steps, so what pays is many
+// resident CTAs per SM, not threads per CTA (512 frames on a B200: 0.35 ms at 512 threads, 0.21 at 256, 0.165 at
+// 128, 0.23 at 64; one frame: 138 us per extraction at 512 threads, 155 at 128).
+constexpr int kOctThreadsBatch = 128;
+constexpr int kOctBatchFrames = 32;    // from this many frames per launch on
 constexpr int kMaxRoots = 64;
 
 struct OctTask {
@@ -335,7 +340,7 @@ int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const ui
     configured = smem;
   }
   dim3 grid(hGeom.nlevels, nframes);
-  launch_pdl(octree_kernel, grid, dim3(kOctThreads), smem, s, dGeom, cand, candCount, nodeScratch, kept, keptCount, cap);
+  launch_pdl(octree_kernel, grid, dim3(nframes >= kOctBatchFrames ? kOctThreadsBatch : kOctThreads), smem, s, dGeom, cand, candCount, nodeScratch, kept, keptCount, cap);
   return 0;
 }
 
