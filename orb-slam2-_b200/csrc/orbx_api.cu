@@ -141,7 +141,7 @@ int ensure_taps(orbx_extractor* h, const FrameSetGeom& g, int w, int hh, cudaStr
     h->taps[l].yt = tbase + all.size();
     all.insert(all.end(), ty.begin(), ty.end());
     h->taps[l].xg = nullptr;
-    if (build_resize_groups(tx, &xg)) {
+    if (build_resize_groups(tx, ty, &xg)) {
       h->taps[l].xg = gbase + groups.size();
       groups.insert(groups.end(), xg.begin(), xg.end());
     }

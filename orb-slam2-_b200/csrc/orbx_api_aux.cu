@@ -147,7 +147,7 @@ int orbx_resize_u8(int32_t device, const uint8_t* src, int32_t sw, int32_t sh, s
   build_resize_axis(sw, dw, &tx);
   build_resize_axis_y(sh, dh, &ty);
   std::vector<ResizeGroup> xg;
-  const bool haveGroups = build_resize_groups(tx, &xg);
+  const bool haveGroups = build_resize_groups(tx, ty, &xg);
   TempBuf dS, dD, dT, dG;
   const int sp = (sw + 15) & ~15, dp = (dw + 15) & ~15;
   if ((rc = dS.alloc((size_t)sp * sh + 64)) || (rc = dD.alloc((size_t)dp * dh)) ||

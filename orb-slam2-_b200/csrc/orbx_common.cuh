@@ -91,7 +91,7 @@ void set_error(const char* fmt, ...);
   } while (0)
 
 // ---- kernel launchers (defined in the .cu files) ------------------------------------------------
-struct ResizeTap { short p0, p1, c0, c1; };  // two source indices and their 11-bit weights
+struct alignas(8) ResizeTap { short p0, p1, c0, c1; };  // two source indices and their 11-bit weights
 // Four consecutive destination pixels of a row (resize4_kernel): the <= 8 source bytes they read start
 // at byte 4*word + shift/8 of the source row; sel01/sel23 are PRMT selectors gathering
 // (left0,right0,left1,right1) / (left2,right2,left3,right3) from those 8 bytes; c[j] = c0 | c1<<16.

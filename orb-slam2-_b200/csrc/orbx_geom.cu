@@ -98,7 +98,10 @@ void build_resize_axis_y(int srcLen, int dstLen, std::vector<ResizeTap>* taps) {
   build_resize_axis(srcLen, dstLen, taps, false);
 }
 
-bool build_resize_groups(const std::vector<ResizeTap>& tx, std::vector<ResizeGroup>* groups) {
+bool build_resize_groups(const std::vector<ResizeTap>& tx, const std::vector<ResizeTap>& ty,
+                         std::vector<ResizeGroup>* groups) {
+  for (const ResizeTap& t : ty)  // resize4_kernel's vertical pass wants non-negative rows and weights
+    if (t.p0 < 0 || t.p1 < 0 || t.c0 < 0 || t.c1 < 0) return false;
   const int dw = (int)tx.size();
   groups->assign((dw + 3) / 4, ResizeGroup());
   for (int gi = 0; gi < (int)groups->size(); gi++) {

@@ -18,8 +18,10 @@ void build_ctor_tables(int nfeatures, float scaleFactor, int nlevels, CtorTables
 // cv::resize INTER_LINEAR coefficient tables for one axis (OpenCV imgproc resize.cpp semantics).
 void build_resize_axis(int srcLen, int dstLen, std::vector<ResizeTap>* taps);    // x: clamp + zero fraction
 void build_resize_axis_y(int srcLen, int dstLen, std::vector<ResizeTap>* taps);  // y: rows clipped, fraction kept
-// 4-pixel groups for resize4_kernel from the x taps; false when some group spans more than 8 source bytes.
-bool build_resize_groups(const std::vector<ResizeTap>& tx, std::vector<ResizeGroup>* groups);
+// 4-pixel groups for resize4_kernel from the x taps; false when some group spans more than 8 source bytes or a
+// weight is negative on either axis.
+bool build_resize_groups(const std::vector<ResizeTap>& tx, const std::vector<ResizeTap>& ty,
+                         std::vector<ResizeGroup>* groups);
 const char* last_error();
 
 // Fill the per-level geometry for a (w,h) frame and `batchCap` frames per arena.

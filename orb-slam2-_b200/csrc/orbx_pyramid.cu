@@ -49,26 +49,41 @@ resize_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int src
   dst[(long long)blockIdx.z * dstFrameStride + (long long)dy * dstPitch + dx] = (uint8_t)min(max(v, 0), 255);
 }
 
-__device__ __forceinline__ void resize_row4(const uint32_t* __restrict__ row, const ResizeGroup& G, int maxWord,
-                                            uint32_t (&h)[4]) {
-  const uint32_t w0 = row[G.word];
-  const uint32_t w1 = row[min(G.word + 1, maxWord)];
-  const uint32_t w2 = row[min(G.word + 2, maxWord)];
+// One horizontally interpolated source row for the group's four pixels from its three aligned words, already >> 4
+// (the vertical pass only ever uses that form, resize.cpp VResizeLinear).
+__device__ __forceinline__ void resize_hrow4(uint32_t w0, uint32_t w1, uint32_t w2, const ResizeGroup& G, uint32_t (&h)[4]) {
   const uint32_t lo = __funnelshift_r(w0, w1, G.shift);
   const uint32_t hi = __funnelshift_r(w1, w2, G.shift);
   const uint32_t b01 = __byte_perm(lo, hi, G.sel01);  // (L0, R0, L1, R1)
   const uint32_t b23 = __byte_perm(lo, hi, G.sel23);
-  h[0] = __dp2a_lo(G.c[0], b01, 0u);
-  h[1] = __dp2a_hi(G.c[1], b01, 0u);
-  h[2] = __dp2a_lo(G.c[2], b23, 0u);
-  h[3] = __dp2a_hi(G.c[3], b23, 0u);
+  h[0] = __dp2a_lo(G.c[0], b01, 0u) >> 4;
+  h[1] = __dp2a_hi(G.c[1], b01, 0u) >> 4;
+  h[2] = __dp2a_lo(G.c[2], b23, 0u) >> 4;
+  h[3] = __dp2a_hi(G.c[3], b23, 0u) >> 4;
 }
 
-constexpr int kResizeRows = 8;   // destination rows per thread (source rows are reused between them)
-constexpr int kResizeBands = 4;  // threadIdx.y
+#ifndef ORBX_RESIZE_ROWS
+#define ORBX_RESIZE_ROWS 8
+#endif
+#ifndef ORBX_RESIZE_BANDS
+#define ORBX_RESIZE_BANDS 4
+#endif
+#ifndef ORBX_RESIZE_PREFETCH
+#define ORBX_RESIZE_PREFETCH 0
+#endif
+constexpr int kResizeRows = ORBX_RESIZE_ROWS;    // destination rows per thread (source rows are reused between them)
+constexpr int kResizeBands = ORBX_RESIZE_BANDS;  // threadIdx.y
 
-__global__ void __launch_bounds__(32 * kResizeBands)
-resize4_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int srcPitch,
+// Requires non-negative weights (build_resize_groups checks both axes; always true when shrinking): then
+// (c * (h >> 4)) >> 16 == umulhi(c << 16, h >> 4), two IMAD.HI per pixel instead of multiply + shift twice, and
+// the result needs no clamp: c0 + c1 == 2048 and h >> 4 <= 32640 bound it by (1020 + 2) >> 2 = 255.
+// A thread walks down consecutive source rows, so the words of the row after the last one used are requested one
+// destination row ahead (the kernel was waiting on exactly these loads 59 % of the time).
+#ifndef ORBX_RESIZE_MINB
+#define ORBX_RESIZE_MINB 12
+#endif
+__global__ void __launch_bounds__(32 * kResizeBands, ORBX_RESIZE_MINB)
+resize4_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int srcPitch, int sh,
                uint8_t* __restrict__ dst, long long dstFrameStride, int dstPitch, int dw, int dh,
                const ResizeGroup* __restrict__ xg, const ResizeTap* __restrict__ yt) {
   pdl_wait();
@@ -76,56 +91,83 @@ resize4_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int sr
   const int dy0 = (blockIdx.y * kResizeBands + threadIdx.y) * kResizeRows;
   if (4 * gx >= dw || dy0 >= dh) return;
   const uint8_t* S = src + (long long)blockIdx.z * srcFrameStride;
-  uint8_t* D = dst + (long long)blockIdx.z * dstFrameStride + 4 * gx;
+  uint8_t* D = dst + (long long)blockIdx.z * dstFrameStride + 4 * gx + (long long)dy0 * dstPitch;
   const ResizeGroup G = xg[gx];
   const int maxWord = (srcPitch >> 2) - 1;
+  // byte offsets of the three aligned words of a row that hold the group's <= 8 source bytes. (Keeping three
+  // 64-bit column pointers instead saves instructions but costs 16 registers, and this kernel lives on occupancy:
+  // it spends most of its time waiting for the row loads.)
+  const uint32_t o0 = 4u * (uint32_t)G.word, o1 = 4u * (uint32_t)min(G.word + 1, maxWord),
+                 o2 = 4u * (uint32_t)min(G.word + 2, maxWord);
+  int nxtRow = -1;
+  uint32_t n0 = 0, n1 = 0, n2 = 0;  // words of source row nxtRow, in flight (ORBX_RESIZE_PREFETCH)
+  auto request = [&](int r, uint32_t& a, uint32_t& b, uint32_t& c) {
+    const uint32_t row = (uint32_t)r * (uint32_t)srcPitch;
+    a = *reinterpret_cast<const uint32_t*>(S + (row + o0));
+    b = *reinterpret_cast<const uint32_t*>(S + (row + o1));
+    c = *reinterpret_cast<const uint32_t*>(S + (row + o2));
+  };
+  auto take = [&](int r, uint32_t (&h)[4]) {
+    uint32_t a, b, c;
+#if ORBX_RESIZE_PREFETCH
+    if (r == nxtRow) { a = n0; b = n1; c = n2; }
+    else request(r, a, b, c);
+    nxtRow = min(r + 1, sh - 1);
+    request(nxtRow, n0, n1, n2);
+#else
+    request(r, a, b, c);
+#endif
+    resize_hrow4(a, b, c, G, h);
+  };
   // horizontally interpolated source rows ia / ib are kept between destination rows (dy is uniform
   // across the warp, so the reuse branches do not diverge)
   int ia = -1, ib = -1;
   uint32_t ha[4] = {0, 0, 0, 0}, hb[4] = {0, 0, 0, 0};
   const int dyEnd = min(dy0 + kResizeRows, dh);
+  uint2 tyNext = *reinterpret_cast<const uint2*>(&yt[dy0]);
   for (int dy = dy0; dy < dyEnd; dy++) {
-    const ResizeTap ty = yt[dy];
-    if (ty.p0 != ia) {
-      if (ty.p0 == ib) {
+    const uint2 ty = tyNext;  // (p0 | p1 << 16, c0 | c1 << 16), all >= 0
+    tyNext = *reinterpret_cast<const uint2*>(&yt[min(dy + 1, dh - 1)]);
+    const int p0 = (int)(ty.x & 0xffffu), p1 = (int)(ty.x >> 16);
+    const uint32_t c0s = ty.y << 16, c1s = ty.y & 0xffff0000u;
+    if (p0 != ia) {
+      if (p0 == ib) {
 #pragma unroll
         for (int j = 0; j < 4; j++) ha[j] = hb[j];
       } else {
-        resize_row4(reinterpret_cast<const uint32_t*>(S + (long long)ty.p0 * srcPitch), G, maxWord, ha);
+        take(p0, ha);
       }
-      ia = ty.p0;
+      ia = p0;
     }
-    if (ty.p1 != ib) {
-      if (ty.p1 == ia) {
+    if (p1 != ib) {
+      if (p1 == ia) {
 #pragma unroll
         for (int j = 0; j < 4; j++) hb[j] = ha[j];
       } else {
-        resize_row4(reinterpret_cast<const uint32_t*>(S + (long long)ty.p1 * srcPitch), G, maxWord, hb);
+        take(p1, hb);
       }
-      ib = ty.p1;
+      ib = p1;
     }
-    uint32_t out = 0;
+    uint32_t v[4];
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const int v = ((((int)ty.c0 * (int)(ha[j] >> 4)) >> 16) + (((int)ty.c1 * (int)(hb[j] >> 4)) >> 16) + 2) >> 2;
-      out |= (uint32_t)min(max(v, 0), 255) << (8 * j);
-    }
+    for (int j = 0; j < 4; j++) v[j] = (__umulhi(c0s, ha[j]) + __umulhi(c1s, hb[j]) + 2u) >> 2;
     // destination planes are ours: pitch is a multiple of 16, so the whole word is inside the row
-    *reinterpret_cast<uint32_t*>(D + (long long)dy * dstPitch) = out;
+    *reinterpret_cast<uint32_t*>(D) = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+    D += dstPitch;
   }
 }
 
 void launch_resize(const uint8_t* src, long long srcFrameStride, int srcPitch, int sw, int sh,
                    uint8_t* dst, long long dstFrameStride, int dstPitch, int dw, int dh,
                    const ResizeTables& t, int nframes, cudaStream_t s) {
-  (void)sw; (void)sh;
+  (void)sw;
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)srcPitch | (uintptr_t)srcFrameStride |
                          reinterpret_cast<uintptr_t>(dst) | (uintptr_t)dstPitch | (uintptr_t)dstFrameStride) & 3) == 0;
   if (t.xg && aligned) {
     const int rowsPerCta = kResizeRows * kResizeBands;
     dim3 grid(((dw + 3) / 4 + 31) / 32, (dh + rowsPerCta - 1) / rowsPerCta, nframes);
-    launch_pdl(resize4_kernel, grid, dim3(32, kResizeBands), 0, s, src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch,
-               dw, dh, t.xg, t.yt);
+    launch_pdl(resize4_kernel, grid, dim3(32, kResizeBands), 0, s, src, srcFrameStride, srcPitch, sh, dst, dstFrameStride,
+               dstPitch, dw, dh, t.xg, t.yt);
   } else {
     dim3 grid((dw + 31) / 32, (dh + 7) / 8, nframes);
     launch_pdl(resize_kernel, grid, dim3(32, 8), 0, s, src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,
@@ -136,9 +178,12 @@ void launch_resize(const uint8_t* src, long long srcFrameStride, int srcPitch, i
 // ------------------------------------------------------------------------------------------------
 // blur
 // ------------------------------------------------------------------------------------------------
-constexpr int kBlurStripW = 32, kBlurStripH = 32;  // one strip = 8 lanes x 4 px, 32 output rows
+#ifndef ORBX_BLUR_H
+#define ORBX_BLUR_H 30
+#endif
+constexpr int kBlurStripW = 32, kBlurStripH = ORBX_BLUR_H;  // one strip = 8 lanes x 4 px, a multiple of 6 output rows
 constexpr int kBlurWarps = 4;                      // 4 strips per warp, 16 per CTA
-constexpr int kBlurPrefetch = 4;                   // rows in flight per lane
+constexpr int kBlurPrefetch = 6;                   // rows in flight per lane
 
 __device__ __forceinline__ int reflect101(int p, int len) {
   // len >= 4 on every level we accept, so one reflection per side is enough for a 3-pixel halo
@@ -160,14 +205,16 @@ __device__ __forceinline__ void blur_hrow(uint32_t l, uint32_t c, uint32_t r, in
   H[3] = (int)__dp4a(c, C3, __dp4a(r, R3, 0u));
 }
 
-__device__ __forceinline__ uint32_t blur_vcol(const int (&H)[7][4], int r) {
-  // rows r-6..r of the rotating window are taps 0..6. The rounding constant rides in the multiply-add chain and
-  // the four results (< 2^24, wanted bits 16..23) are packed with three PRMT instead of shift/shift/or per pixel.
+// Vertical pass on packed rows: P[k] holds (H[k-1], H[k]) as two 16-bit lanes (H <= 255*256), so the seven taps of
+// the output row centred on r-3 are four IDP.2A (16-bit x 8-bit) over P[r-5], P[r-3], P[r-1], P[r], the rounding
+// constant riding in the accumulator; the four results (< 2^24, wanted bits 16..23) are packed with three PRMT.
+__device__ __forceinline__ uint32_t blur_vcol(const uint32_t (&P)[6][4], int r) {
+  constexpr uint32_t K01 = 18u | (34u << 8), K23 = 48u | (56u << 8), K45 = 48u | (34u << 8), K6 = 18u << 8;
   uint32_t v[4];
 #pragma unroll
   for (int j = 0; j < 4; j++)
-    v[j] = 18u * (uint32_t)(H[(r - 6) % 7][j] + H[r % 7][j]) + 34u * (uint32_t)(H[(r - 5) % 7][j] + H[(r - 1) % 7][j]) +
-           48u * (uint32_t)(H[(r - 4) % 7][j] + H[(r - 2) % 7][j]) + (56u * (uint32_t)H[(r - 3) % 7][j] + 32768u);
+    v[j] = __dp2a_lo(P[(r + 1) % 6][j], K01,
+                     __dp2a_lo(P[(r + 3) % 6][j], K23, __dp2a_lo(P[(r + 5) % 6][j], K45, __dp2a_lo(P[r % 6][j], K6, 32768u))));
   return __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
 }
 
@@ -175,7 +222,12 @@ __device__ __forceinline__ uint32_t blur_vcol(const int (&H)[7][4], int r) {
 // one aligned 32-bit load per row (plus one halo load on the strip's first and last lane); image
 // borders (BORDER_REFLECT_101) are rebuilt from the loaded words with PRMT selectors that are fixed
 // per strip. `valid` is false for the lanes of a quarter-warp without a strip: they run the
-// shuffles with everybody else and store nothing.
+// shuffles with everybody else and store nothing. kInterior: rows y0-3 .. y0+kBlurStripH+2 all exist, so the row
+// pointer just advances by the pitch and no store needs a row test.
+// Rows go by in groups of six (the period of the packed window): the first group only fills the window, the
+// others are one rolled loop around six unrolled rows. (Unrolling all 38 rows of a 32-row strip twice -- interior
+// and border form -- made 74 KB of code and a quarter of the stall samples were instruction-cache misses.)
+template <bool kInterior>
 __device__ __forceinline__ void blur_strip8(const uint8_t* __restrict__ src, int srcPitch, uint8_t* __restrict__ dst,
                                             int dstPitch, int w, int h, int x0, int y0, bool valid) {
   const int sub = threadIdx.x & 7;
@@ -194,42 +246,77 @@ __device__ __forceinline__ void blur_strip8(const uint8_t* __restrict__ src, int
   }
   const uint32_t selOwn = isLastWord ? selC : 0x7654u;                       // applied to (l, raw)
   const uint32_t selHalo = (x + 4 == lastX) ? selC : 0x7654u;                // applied to (own, rawRight)
-  const bool haloL = valid && first && x > 0;
-  const bool haloR = valid && last && x + 4 <= lastX;
-  const int xr = min(x + 4, lastX);
+  // the halo word sits at -4 (first lane) / +4 (last lane) from the lane's own word: the first lane of a strip has
+  // x <= lastX, and a last lane only loads its halo when x + 4 <= lastX, so the clamp in xl never applies to a
+  // lane that loads one
+  const bool halo = valid && ((first && x > 0) || (last && x + 4 <= lastX));
+  const int haloOff = first ? -4 : 4;
+  const bool storeOk = valid && x <= lastX;
 
-  uint32_t qc[kBlurPrefetch], ql[kBlurPrefetch], qr[kBlurPrefetch];
+  const uint8_t* colBase = src + xl;
+  const uint8_t* fp = colBase + (long long)(y0 - 3) * srcPitch;  // kInterior only
+  uint8_t* dp = dst + (long long)y0 * dstPitch + x;
+  uint32_t qc[kBlurPrefetch], qh[kBlurPrefetch];
   auto fetch = [&](int r, int slot) {
-    const int yy = reflect101(min(y0 + r - 3, h + 2), h);
-    const uint8_t* row = src + (long long)yy * srcPitch;
-    qc[slot] = valid ? *reinterpret_cast<const uint32_t*>(row + xl) : 0u;
-    ql[slot] = haloL ? *reinterpret_cast<const uint32_t*>(row + x - 4) : 0u;
-    qr[slot] = haloR ? *reinterpret_cast<const uint32_t*>(row + xr) : 0u;
+    const uint8_t* row;
+    if constexpr (kInterior) {
+      row = fp;
+      fp += srcPitch;
+    } else {
+      row = colBase + (long long)reflect101(min(y0 + r - 3, h + 2), h) * srcPitch;
+    }
+    qc[slot] = valid ? *reinterpret_cast<const uint32_t*>(row) : 0u;
+    qh[slot] = halo ? *reinterpret_cast<const uint32_t*>(row + haloOff) : 0u;
   };
-#pragma unroll
-  for (int r = 0; r < kBlurPrefetch; r++) fetch(r, r);
-
-  int H[7][4];
-#pragma unroll
-  for (int r = 0; r < kBlurStripH + 6; r++) {
-    const uint32_t raw = qc[r % kBlurPrefetch];
-    const uint32_t hl = ql[r % kBlurPrefetch], hr = qr[r % kBlurPrefetch];
-    if (r + kBlurPrefetch < kBlurStripH + 6) fetch(r + kBlurPrefetch, r % kBlurPrefetch);
+  uint32_t P[6][4];
+  int Hprev[4] = {0, 0, 0, 0};
+  // row r = 6 * group + k: horizontal pass into the packed window (k = r % 6 at compile time)
+  auto hpass = [&](int k) {
+    const uint32_t raw = qc[k], hw = qh[k];
     uint32_t l = __shfl_up_sync(0xffffffffu, raw, 1, 8);
-    if (first) l = hl;                                    // x == 0 is fixed below, once r is known
+    if (first) l = hw;                                    // x == 0 is fixed below
     const uint32_t c = __byte_perm(l, raw, selOwn);
     uint32_t rr = __shfl_down_sync(0xffffffffu, c, 1, 8);
-    if (last) rr = __byte_perm(c, hr, selHalo);
+    if (last) rr = __byte_perm(c, hw, selHalo);
     if (isLastWord) rr = __byte_perm(l, raw, selR);
     if (x == 0) l = __byte_perm(c, rr, 0x1234);           // columns -4..-1 = columns 4,3,2,1
-    blur_hrow(l, c, rr, H[r % 7]);
-    if (r >= 6) {
-      const int y = y0 + r - 6;
-      const uint32_t out = blur_vcol(H, r);
+    int H[4];
+    blur_hrow(l, c, rr, H);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      P[k][j] = __byte_perm((uint32_t)Hprev[j], (uint32_t)H[j], 0x5410);
+      Hprev[j] = H[j];
+    }
+  };
+  static_assert(kBlurPrefetch == 6 && kBlurStripH % 6 == 0, "rows are processed in groups of six");
+#pragma unroll
+  for (int k = 0; k < 6; k++) fetch(k, k);
+#pragma unroll
+  for (int k = 0; k < 6; k++) {  // group 0 fills the window
+    hpass(k);
+    fetch(6 + k, k);
+  }
+#pragma unroll 1
+  for (int g = 1; g <= kBlurStripH / 6; g++) {
+    const bool more = g < kBlurStripH / 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      hpass(k);
+      if (more) fetch(6 * g + 6 + k, k);
+      const uint32_t out = blur_vcol(P, k);
       // destination planes are ours (pitch multiple of 16): the word never leaves the row
-      if (valid && x <= lastX && y < h) *reinterpret_cast<uint32_t*>(dst + (long long)y * dstPitch + x) = out;
+      if (storeOk && (kInterior || y0 + 6 * g + k - 6 < h)) *reinterpret_cast<uint32_t*>(dp) = out;
+      dp += dstPitch;
     }
   }
+}
+
+// interior strips take the cheaper row addressing when the whole warp agrees (its four strips are neighbours)
+__device__ __forceinline__ void blur_strip_dispatch(const uint8_t* __restrict__ src, int srcPitch, uint8_t* __restrict__ dst,
+                                                    int dstPitch, int w, int h, int x0, int y0, bool valid) {
+  const bool interior = !valid || (y0 >= 3 && y0 + kBlurStripH + 3 <= h);
+  if (__all_sync(0xffffffffu, interior)) blur_strip8<true>(src, srcPitch, dst, dstPitch, w, h, x0, y0, valid);
+  else blur_strip8<false>(src, srcPitch, dst, dstPitch, w, h, x0, y0, valid);
 }
 
 __global__ void __launch_bounds__(kBlurWarps * 32)
@@ -247,7 +334,7 @@ blur_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ Fra
   const int f = blockIdx.y;
   const uint8_t* src = pyr.lvl[level] + (long long)f * pyr.frameStride[level];
   uint8_t* dst = blurArena + L.planeOff + (long long)f * L.planeBytes;
-  blur_strip8(src, pyr.pitch[level], dst, L.pitch, L.w, L.h, tx * kBlurStripW, ty * kBlurStripH, valid);
+  blur_strip_dispatch(src, pyr.pitch[level], dst, L.pitch, L.w, L.h, tx * kBlurStripW, ty * kBlurStripH, valid);
 }
 
 __global__ void __launch_bounds__(kBlurWarps * 32)
@@ -257,7 +344,7 @@ blur_single_kernel(const uint8_t* __restrict__ src, int srcPitch, uint8_t* __res
   const bool valid = task < tiles;
   const int t = valid ? task : 0;
   const int ty = t / tilesX, tx = t - ty * tilesX;
-  blur_strip8(src, srcPitch, dst, dstPitch, w, h, tx * kBlurStripW, ty * kBlurStripH, valid);
+  blur_strip_dispatch(src, srcPitch, dst, dstPitch, w, h, tx * kBlurStripW, ty * kBlurStripH, valid);
 }
 
 // General form (any alignment, any size >= 4x4): one thread per pixel, used by orbx_blur7_u8 for images
