@@ -200,6 +200,30 @@ int orbx_stereo_match_batch_device(orbx_matcher* h, orbx_extractor* ex, int32_t 
                                    const uint8_t* d_desc, const int32_t* d_n, int32_t cap, float mbf, float mb,
                                    float* d_u_right, float* d_depth, int32_t* d_n_matched, void* stream);
 
+/* Node-restricted distance blocks: the data-parallel half of ORBmatcher::SearchByBoW (R/src/ORBmatcher.cpp:220-365
+ * key frame -> frame, :632-772 key frame -> key frame) and SearchForTriangulation (:785-983). Block k is one
+ * vocabulary node both DBoW2::FeatureVectors hold (the merge-join of the two maps, :229-231 / :328-340, is the
+ * caller's): it pairs rows a_idx[a_off[k] .. a_off[k+1]) of desc_a with rows b_idx[b_off[k] .. b_off[k+1]) of
+ * desc_b. dist[dist_off[k] + ia*nb_k + ib] = DescriptorDistance(desc_a[a_idx[a_off[k]+ia]], desc_b[b_idx[b_off[k]+ib]]).
+ * dist_off (nblocks+1 entries) is written by the call; *n_dist = dist_off[nblocks]. Host buffers, synchronous.
+ * ORBX_ERR_CAPACITY when dist_cap < *n_dist (dist_off and *n_dist are valid). The order-dependent resolve runs on
+ * the host (orb-slam2-_b200/host/orbx_search.h). */
+int orbx_match_blocks(orbx_matcher* h, const uint8_t* desc_a, int32_t na, const uint8_t* desc_b, int32_t nb,
+                      const int32_t* a_off, const int32_t* a_idx, const int32_t* b_off, const int32_t* b_idx,
+                      int32_t nblocks, int64_t* dist_off, uint16_t* dist, int64_t dist_cap, int64_t* n_dist);
+
+/* MapPoint::ComputeDistinctiveDescriptors (R/src/MapPoint.cpp:306-385) for `npoints` map points in one launch
+ * (LocalMapping calls it per created / fused point, R/src/LocalMapping.cpp). Point p observes the descriptor rows
+ * desc[obs_off[p] .. obs_off[p+1]) -- gathered by the caller in the iteration order of its mObservations map,
+ * bad key frames skipped (:326-333). best[p] = position within the group of the first row whose sorted distance
+ * row has the least median vDists[0.5*(N-1)] (:357-375), best_median[p] that median; -1 / -1 for a point without
+ * rows (the reference returns without touching mDescriptor, :335-336). Host buffers, synchronous. */
+int orbx_distinctive(orbx_matcher* h, const uint8_t* desc, const int32_t* obs_off, int32_t npoints, int32_t* best,
+                     int32_t* best_median);
+/* Device-resident, asynchronous on `stream` (NULL: the matcher's own stream). */
+int orbx_distinctive_device(orbx_matcher* h, const uint8_t* d_desc, const int32_t* d_obs_off, int32_t npoints,
+                            int32_t* d_best, int32_t* d_best_median, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

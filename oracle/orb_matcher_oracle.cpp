@@ -406,3 +406,227 @@ extern "C" int orb_oracle_stereo_matches(const orb_oracle_keypoint* kps_l, const
   }
   return kept;
 }
+
+// ======================================================================================================
+// bag-of-words restricted searches and the distinctive descriptor of a map point.
+// PINNED: tests/test_oracle_vs_ref_front.py runs the reference's own ORBmatcher::SearchByBoW (both overloads),
+// SearchForTriangulation and MapPoint::ComputeDistinctiveDescriptors on real KeyFrame / MapPoint objects
+// (R/src/KeyFrame.cpp compiled where it lies into oracle/_ref/libref_front.so) and requires identical results.
+//
+// A DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) is passed flattened: node ids ascending,
+// CSR offsets, feature indices in insertion order -- the iteration order of the map.
+// ======================================================================================================
+namespace orb_oracle {
+
+struct FeatVec { const int32_t *nodes, *off, *idx; int n; };
+
+// the merge-join both SearchByBoW overloads and SearchForTriangulation use (:232, :331-340, :654, :758-767):
+// calls f(i1, i2) for every node id both vectors hold, ascending
+template <class F>
+static void for_common_nodes(const FeatVec& a, const FeatVec& b, F f) {
+  int i = 0, j = 0;
+  while (i < a.n && j < b.n) {
+    if (a.nodes[i] == b.nodes[j]) { f(i, j); i++; j++; }
+    else if (a.nodes[i] < b.nodes[j]) i = (int)(std::lower_bound(a.nodes, a.nodes + a.n, b.nodes[j]) - a.nodes);
+    else j = (int)(std::lower_bound(b.nodes, b.nodes + b.n, a.nodes[i]) - b.nodes);
+  }
+}
+
+}  // namespace orb_oracle
+
+extern "C" {
+
+/* block distances, same layout as orbx_match_blocks */
+void orb_oracle_block_distances(const uint8_t* desc_a, const uint8_t* desc_b, const int32_t* a_off, const int32_t* a_idx,
+                                const int32_t* b_off, const int32_t* b_idx, int nblocks, int64_t* dist_off, uint16_t* dist) {
+  int64_t t = 0;
+  dist_off[0] = 0;
+  for (int k = 0; k < nblocks; k++) {
+    for (int ia = a_off[k]; ia < a_off[k + 1]; ia++)
+      for (int ib = b_off[k]; ib < b_off[k + 1]; ib++)
+        dist[t++] = (uint16_t)descriptor_distance(desc_a + (size_t)a_idx[ia] * 32, desc_b + (size_t)b_idx[ib] * 32);
+    dist_off[k + 1] = t;
+  }
+}
+
+/* R/src/ORBmatcher.cpp:220-365. kf_usable[i] = vpMapPointsKF[i] && !isBad(). match_f[iF] = key-frame feature whose
+ * map point was assigned to frame keypoint iF, or -1. Returns nmatches. */
+int orb_oracle_search_by_bow_kf_frame(const uint8_t* desc_kf, const float* angle_kf, const uint8_t* kf_usable,
+                                      const int32_t* kf_nodes, const int32_t* kf_off, const int32_t* kf_idx, int kf_nn,
+                                      const uint8_t* desc_f, const float* angle_f, int n_f, const int32_t* f_nodes,
+                                      const int32_t* f_off, const int32_t* f_idx, int f_nn, float nnratio,
+                                      int check_orientation, int32_t* match_f) {
+  for (int i = 0; i < n_f; i++) match_f[i] = -1;   // vpMapPointMatches = vector<MapPoint*>(F.N, NULL) (:224)
+  std::vector<int> rotHist[kHistoLength];
+  int nmatches = 0;
+  const FeatVec kf{kf_nodes, kf_off, kf_idx, kf_nn}, f{f_nodes, f_off, f_idx, f_nn};
+  for_common_nodes(kf, f, [&](int nk, int nf) {
+    for (int iKF = kf_off[nk]; iKF < kf_off[nk + 1]; iKF++) {
+      const int realIdxKF = kf_idx[iKF];
+      if (!kf_usable[realIdxKF]) continue;                       // :247-253
+      const uint8_t* dKF = desc_kf + (size_t)realIdxKF * 32;
+      int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+      for (int iF = f_off[nf]; iF < f_off[nf + 1]; iF++) {
+        const int realIdxF = f_idx[iF];
+        if (match_f[realIdxF] >= 0) continue;                    // :265
+        const int dist = descriptor_distance(dKF, desc_f + (size_t)realIdxF * 32);
+        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+        else if (dist < bestDist2) bestDist2 = dist;
+      }
+      if (bestDist1 <= kThLow && (float)bestDist1 < nnratio * (float)bestDist2) {   // :285-287
+        match_f[bestIdxF] = realIdxKF;
+        if (check_orientation) rotHist[rot_bin(angle_kf[realIdxKF], angle_f[bestIdxF])].push_back(bestIdxF);
+        nmatches++;
+      }
+    }
+  });
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    compute_three_maxima(rotHist, kHistoLength, ind1, ind2, ind3);
+    for (int i = 0; i < kHistoLength; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int j : rotHist[i]) { match_f[j] = -1; nmatches--; }
+    }
+  }
+  return nmatches;
+}
+
+/* R/src/ORBmatcher.cpp:632-772. usable1/2[i] = vpMapPoints[i] && !isBad(). matches12[i1] = i2 or -1. */
+int orb_oracle_search_by_bow_kf_kf(const uint8_t* desc1, const float* angle1, const uint8_t* usable1, int n1,
+                                   const int32_t* nodes1, const int32_t* off1, const int32_t* idx1, int nn1,
+                                   const uint8_t* desc2, const float* angle2, const uint8_t* usable2, int n2,
+                                   const int32_t* nodes2, const int32_t* off2, const int32_t* idx2, int nn2, float nnratio,
+                                   int check_orientation, int32_t* matches12) {
+  for (int i = 0; i < n1; i++) matches12[i] = -1;
+  std::vector<uint8_t> vbMatched2((size_t)n2, 0);
+  std::vector<int> rotHist[kHistoLength];
+  int nmatches = 0;
+  const FeatVec f1{nodes1, off1, idx1, nn1}, f2{nodes2, off2, idx2, nn2};
+  for_common_nodes(f1, f2, [&](int k1, int k2) {
+    for (int e1 = off1[k1]; e1 < off1[k1 + 1]; e1++) {
+      const int i1 = idx1[e1];
+      if (!usable1[i1]) continue;
+      const uint8_t* d1 = desc1 + (size_t)i1 * 32;
+      int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+      for (int e2 = off2[k2]; e2 < off2[k2 + 1]; e2++) {
+        const int i2 = idx2[e2];
+        if (vbMatched2[i2] || !usable2[i2]) continue;            // :682-688
+        const int dist = descriptor_distance(d1, desc2 + (size_t)i2 * 32);
+        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = i2; }
+        else if (dist < bestDist2) bestDist2 = dist;
+      }
+      if (bestDist1 < kThLow && (float)bestDist1 < nnratio * (float)bestDist2) {    // :707-709 (strict <)
+        matches12[i1] = bestIdx2;
+        vbMatched2[bestIdx2] = 1;
+        if (check_orientation) rotHist[rot_bin(angle1[i1], angle2[bestIdx2])].push_back(i1);
+        nmatches++;
+      }
+    }
+  });
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    compute_three_maxima(rotHist, kHistoLength, ind1, ind2, ind3);
+    for (int i = 0; i < kHistoLength; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int j : rotHist[i]) { matches12[j] = -1; nmatches--; }
+    }
+  }
+  return nmatches;
+}
+
+/* R/src/ORBmatcher.cpp:785-983 after its prologue (:790-803: epipole ex, ey of camera 1 in image 2).
+ * CheckDistEpipolarLine :175-203 with the contractions GCC -O3 emits for it (vfmadd231ss: a = fma(x,F00,y*F10)+F20,
+ * den = fma(a,a,b*b), num = fma(b,y2,a*x2) + c; checked in the disassembly of the reference's object file).
+ * has_mp1/2[i] = GetMapPoint(i) != NULL; uright1/2 = mvuRight; kps = mvKeysUn. matches12[i1] = i2 or -1. */
+int orb_oracle_search_for_triangulation(const orb_oracle_keypoint* kps1, const uint8_t* desc1, const uint8_t* has_mp1,
+                                        const float* uright1, int n1, const int32_t* nodes1, const int32_t* off1,
+                                        const int32_t* idx1, int nn1, const orb_oracle_keypoint* kps2, const uint8_t* desc2,
+                                        const uint8_t* has_mp2, const float* uright2, int n2, const int32_t* nodes2,
+                                        const int32_t* off2, const int32_t* idx2, int nn2, const float* F12 /* 3x3 */,
+                                        float ex, float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                        int only_stereo, int check_orientation, int32_t* matches12) {
+  for (int i = 0; i < n1; i++) matches12[i] = -1;
+  std::vector<uint8_t> vbMatched2((size_t)n2, 0);
+  std::vector<int> rotHist[kHistoLength];
+  int nmatches = 0;
+  auto epipolar_ok = [&](const orb_oracle_keypoint& kp1, const orb_oracle_keypoint& kp2) {
+    const float a = std::fma(kp1.x, F12[0], kp1.y * F12[3]) + F12[6];
+    const float b = std::fma(kp1.x, F12[1], kp1.y * F12[4]) + F12[7];
+    const float c = std::fma(kp1.y, F12[5], kp1.x * F12[2]) + F12[8];
+    const float num = c + std::fma(b, kp2.y, a * kp2.x);
+    const float den = std::fma(a, a, b * b);
+    if (den == 0) return false;
+    const float dsqr = num * num / den;
+    return (double)dsqr < 3.84 * (double)level_sigma2_2[kp2.octave];
+  };
+  const FeatVec f1{nodes1, off1, idx1, nn1}, f2{nodes2, off2, idx2, nn2};
+  for_common_nodes(f1, f2, [&](int k1, int k2) {
+    for (int e1 = off1[k1]; e1 < off1[k1 + 1]; e1++) {
+      const int i1 = idx1[e1];
+      if (has_mp1[i1]) continue;                                  // :833-836
+      const bool bStereo1 = uright1[i1] >= 0;
+      if (only_stereo && !bStereo1) continue;
+      const orb_oracle_keypoint& kp1 = kps1[i1];
+      const uint8_t* d1 = desc1 + (size_t)i1 * 32;
+      int bestDist = kThLow, bestIdx2 = -1;
+      for (int e2 = off2[k2]; e2 < off2[k2 + 1]; e2++) {
+        const int i2 = idx2[e2];
+        if (vbMatched2[i2] || has_mp2[i2]) continue;              // :858-859
+        const bool bStereo2 = uright2[i2] >= 0;
+        if (only_stereo && !bStereo2) continue;
+        const int dist = descriptor_distance(d1, desc2 + (size_t)i2 * 32);
+        if (dist > kThLow || dist > bestDist) continue;           // :872
+        const orb_oracle_keypoint& kp2 = kps2[i2];
+        if (!bStereo1 && !bStereo2) {
+          const float distex = ex - kp2.x, distey = ey - kp2.y;
+          if (std::fma(distex, distex, distey * distey) < 100 * scale_factors2[kp2.octave]) continue;   // :881-883
+        }
+        if (epipolar_ok(kp1, kp2)) { bestIdx2 = i2; bestDist = dist; }
+      }
+      if (bestIdx2 >= 0) {
+        matches12[i1] = bestIdx2;
+        vbMatched2[bestIdx2] = 1;
+        nmatches++;
+        if (check_orientation) rotHist[rot_bin(kp1.angle, kps2[bestIdx2].angle)].push_back(i1);
+      }
+    }
+  });
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    compute_three_maxima(rotHist, kHistoLength, ind1, ind2, ind3);
+    for (int i = 0; i < kHistoLength; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int j : rotHist[i]) { matches12[j] = -1; nmatches--; }
+    }
+  }
+  return nmatches;
+}
+
+/* R/src/MapPoint.cpp:306-385 for npoints points: rows desc[obs_off[p] .. obs_off[p+1]) in observation order */
+void orb_oracle_distinctive(const uint8_t* desc, const int32_t* obs_off, int npoints, int32_t* best, int32_t* best_median) {
+  for (int p = 0; p < npoints; p++) {
+    const uint8_t* D = desc + (size_t)obs_off[p] * 32;
+    const size_t N = (size_t)(obs_off[p + 1] - obs_off[p]);
+    if (N == 0) { best[p] = -1; best_median[p] = -1; continue; }
+    std::vector<std::vector<float>> Distances(N, std::vector<float>(N, 0));
+    for (size_t i = 0; i < N; i++) {
+      Distances[i][i] = 0;
+      for (size_t j = i + 1; j < N; j++) {
+        const int distij = descriptor_distance(D + i * 32, D + j * 32);
+        Distances[i][j] = (float)distij;
+        Distances[j][i] = (float)distij;
+      }
+    }
+    int BestMedian = INT_MAX, BestIdx = 0;
+    for (size_t i = 0; i < N; i++) {
+      std::vector<int> vDists(Distances[i].begin(), Distances[i].end());
+      std::sort(vDists.begin(), vDists.end());
+      const int median = vDists[(size_t)(0.5 * (double)(N - 1))];
+      if (median < BestMedian) { BestMedian = median; BestIdx = (int)i; }
+    }
+    best[p] = BestIdx;
+    best_median[p] = BestMedian;
+  }
+}
+
+}  // extern "C"

@@ -109,6 +109,33 @@ int orb_oracle_stereo_matches(const orb_oracle_keypoint* kps_l, const uint8_t* d
                               const float* scale_factors, const float* inv_scale_factors,
                               float mbf, float max_d, float* u_right, float* depth);
 
+/* ---- SURVEY.md 8f rows 1-2 (orb_matcher_oracle.cpp, second half). A DBoW2::FeatureVector is passed flattened:
+ * node ids ascending, CSR offsets, feature indices in insertion order. ---- */
+void orb_oracle_block_distances(const uint8_t* desc_a, const uint8_t* desc_b, const int32_t* a_off, const int32_t* a_idx,
+                                const int32_t* b_off, const int32_t* b_idx, int nblocks, int64_t* dist_off, uint16_t* dist);
+/* SearchByBoW(KeyFrame*, Frame&, ...) ORBmatcher.cpp:220-365 */
+int orb_oracle_search_by_bow_kf_frame(const uint8_t* desc_kf, const float* angle_kf, const uint8_t* kf_usable,
+                                      const int32_t* kf_nodes, const int32_t* kf_off, const int32_t* kf_idx, int kf_nn,
+                                      const uint8_t* desc_f, const float* angle_f, int n_f, const int32_t* f_nodes,
+                                      const int32_t* f_off, const int32_t* f_idx, int f_nn, float nnratio,
+                                      int check_orientation, int32_t* match_f);
+/* SearchByBoW(KeyFrame*, KeyFrame*, ...) ORBmatcher.cpp:632-772 */
+int orb_oracle_search_by_bow_kf_kf(const uint8_t* desc1, const float* angle1, const uint8_t* usable1, int n1,
+                                   const int32_t* nodes1, const int32_t* off1, const int32_t* idx1, int nn1,
+                                   const uint8_t* desc2, const float* angle2, const uint8_t* usable2, int n2,
+                                   const int32_t* nodes2, const int32_t* off2, const int32_t* idx2, int nn2, float nnratio,
+                                   int check_orientation, int32_t* matches12);
+/* SearchForTriangulation ORBmatcher.cpp:785-983 (+ CheckDistEpipolarLine :175-203) */
+int orb_oracle_search_for_triangulation(const orb_oracle_keypoint* kps1, const uint8_t* desc1, const uint8_t* has_mp1,
+                                        const float* uright1, int n1, const int32_t* nodes1, const int32_t* off1,
+                                        const int32_t* idx1, int nn1, const orb_oracle_keypoint* kps2, const uint8_t* desc2,
+                                        const uint8_t* has_mp2, const float* uright2, int n2, const int32_t* nodes2,
+                                        const int32_t* off2, const int32_t* idx2, int nn2, const float* F12,
+                                        float ex, float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                        int only_stereo, int check_orientation, int32_t* matches12);
+/* MapPoint::ComputeDistinctiveDescriptors MapPoint.cpp:306-385, many points */
+void orb_oracle_distinctive(const uint8_t* desc, const int32_t* obs_off, int npoints, int32_t* best, int32_t* best_median);
+
 #ifdef __cplusplus
 }
 #endif

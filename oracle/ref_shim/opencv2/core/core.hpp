@@ -162,6 +162,12 @@ class Mat {
     m.create(rows, cols, type_);
     for (int r = 0; r < rows; r++) std::memcpy(m.ptr(r), ptr(r), (size_t)cols * elemSize());
   }
+  // copyTo into a temporary header (Twc.rowRange(0,3).col(3) as OutputArray, R/src/KeyFrame.cpp:87-88): a view of
+  // matching size and type is filled in place, like cv::Mat::create on a matching allocation
+  void copyTo(Mat&& view) const {
+    assert(view.rows == rows && view.cols == cols && view.type_ == type_ && view.data);
+    for (int r = 0; r < rows; r++) std::memcpy(view.ptr(r), ptr(r), (size_t)cols * elemSize());
+  }
   // depth conversion; only what R/src/Frame.cpp:676,698 needs (8-bit window -> float), in place allowed
   void convertTo(Mat& m, int type) const {
     assert(type == CV_32F && (depth() == CV_8U || depth() == CV_32F) && channels() == 1);

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "Frame.h"
+#include "KeyFrame.h"
 #include "Map.h"
 #include "MapPoint.h"
 #include "ORBextractor.h"
@@ -32,7 +33,14 @@ struct Front {
   float bf, thDepth;
   Map map;
   std::vector<MapPoint*> points;  // owned
+  std::vector<KeyFrame*> keyFrames;  // owned
 };
+
+int point_index(const Front* f, const MapPoint* p) {
+  if (!p) return -1;
+  for (size_t k = 0; k < f->points.size(); k++) if (f->points[k] == p) return (int)k;
+  return -2;
+}
 
 void put_keys(const std::vector<cv::KeyPoint>& keys, ref_keypoint* out) {
   if (!out) return;
@@ -67,6 +75,7 @@ void* ref_front_create(int nfeatures, float scaleFactor, int nlevels, int iniTh,
 void ref_front_destroy(void* h) {
   Front* f = static_cast<Front*>(h);
   for (MapPoint* p : f->points) delete p;
+  for (KeyFrame* k : f->keyFrames) delete k;
   delete f->left; delete f->right;
   delete f;
 }
@@ -226,6 +235,116 @@ void ref_project_last_frame(void* curp, void* lastp, int bMono, uint8_t* valid, 
     if (vv < CurrentFrame.mnMinY || vv > CurrentFrame.mnMaxY) continue;
     valid[i] = 1; u[i] = uu; v[i] = vv; invz[i] = invzc;
   }
+}
+
+// ---- key frames (R/src/KeyFrame.cpp compiled where it lies) ------------------------------------------------
+// KeyFrame(F, pMap, pKFDB) (R/src/KeyFrame.cpp:30-58): copies keypoints, descriptors, grid, feature vector and pose
+// of the frame (which needs ref_frame_set_pose first). The key frame database is outside the harness (NULL).
+void* ref_keyframe_create(void* h, void* fr) {
+  Front* f = static_cast<Front*>(h);
+  KeyFrame* kf = new KeyFrame(*static_cast<Frame*>(fr), &f->map, static_cast<KeyFrameDatabase*>(nullptr));
+  f->keyFrames.push_back(kf);
+  return kf;
+}
+
+// mFeatVec is what DBoW2's transform() leaves (outside the path: the vocabulary file is not shipped); the harness
+// fills it through DBoW2::FeatureVector::addFeature (Thirdparty/DBoW2/DBoW2/FeatureVector.cpp:31-45): node[i] is the
+// vocabulary node of feature i, features are added in index order like transform() does
+void ref_frame_set_featvec(void* fr, const int* node, int n) {
+  Frame& F = *static_cast<Frame*>(fr);
+  F.mFeatVec.clear();
+  for (int i = 0; i < n; i++) if (node[i] >= 0) F.mFeatVec.addFeature((DBoW2::NodeId)node[i], (unsigned)i);
+}
+void ref_keyframe_set_featvec(void* kfp, const int* node, int n) {
+  KeyFrame& K = *static_cast<KeyFrame*>(kfp);
+  K.mFeatVec.clear();
+  for (int i = 0; i < n; i++) if (node[i] >= 0) K.mFeatVec.addFeature((DBoW2::NodeId)node[i], (unsigned)i);
+}
+
+// KeyFrame::AddMapPoint + MapPoint::AddObservation, as LocalMapping / Tracking do for a new association
+void ref_keyframe_add_map_point(void* h, void* kfp, int idx, int mp) {
+  MapPoint* p = static_cast<Front*>(h)->points[mp];
+  KeyFrame* kf = static_cast<KeyFrame*>(kfp);
+  kf->AddMapPoint(p, (size_t)idx);
+  p->AddObservation(kf, (size_t)idx);
+}
+int ref_keyframe_address_rank(void* h, void* kfp) {   // position of the key frame in pointer order (std::map<KeyFrame*,...>)
+  Front* f = static_cast<Front*>(h);
+  int r = 0;
+  for (KeyFrame* k : f->keyFrames) if (k < static_cast<KeyFrame*>(kfp)) r++;
+  return r;
+}
+
+// R/src/ORBmatcher.cpp:220-365; out[iF] = index of the map point assigned to frame keypoint iF or -1
+int ref_search_by_bow_kf_frame(void* h, void* kfp, void* fr, float nnratio, int checkOri, int* out) {
+  Frame& F = *static_cast<Frame*>(fr);
+  std::vector<MapPoint*> v;
+  ORBmatcher matcher(nnratio, checkOri != 0);
+  const int n = matcher.SearchByBoW(static_cast<KeyFrame*>(kfp), F, v);
+  for (int i = 0; i < F.N; i++) out[i] = point_index(static_cast<Front*>(h), v[i]);
+  return n;
+}
+
+// R/src/ORBmatcher.cpp:632-772; out[i1] = index of the matched map point of key frame 2 or -1
+int ref_search_by_bow_kf_kf(void* h, void* kf1, void* kf2, float nnratio, int checkOri, int* out) {
+  std::vector<MapPoint*> v;
+  ORBmatcher matcher(nnratio, checkOri != 0);
+  const int n = matcher.SearchByBoW(static_cast<KeyFrame*>(kf1), static_cast<KeyFrame*>(kf2), v);
+  for (size_t i = 0; i < v.size(); i++) out[i] = point_index(static_cast<Front*>(h), v[i]);
+  return n;
+}
+
+// The epipole of camera 1 in image 2 as SearchForTriangulation's prologue computes it (R/src/ORBmatcher.cpp:790-803,
+// same Mat arithmetic; the final expression carries the contraction GCC emits there: fma(fx*C2x, invz, cx)), exported so
+// that the test hands identical inputs to the oracle and to the CUDA path.
+void ref_epipole(void* kf1p, void* kf2p, float* ex, float* ey) {
+  KeyFrame *pKF1 = static_cast<KeyFrame*>(kf1p), *pKF2 = static_cast<KeyFrame*>(kf2p);
+  cv::Mat Cw = pKF1->GetCameraCenter();
+  cv::Mat R2w = pKF2->GetRotation();
+  cv::Mat t2w = pKF2->GetTranslation();
+  cv::Mat C2 = R2w * Cw + t2w;
+  const float invz = 1.0f / C2.at<float>(2);
+  *ex = __builtin_fmaf(pKF2->fx * C2.at<float>(0), invz, pKF2->cx);
+  *ey = __builtin_fmaf(pKF2->fy * C2.at<float>(1), invz, pKF2->cy);
+}
+
+// R/src/ORBmatcher.cpp:785-983; pairs = (idx1, idx2) x return value
+int ref_search_for_triangulation(void* kf1, void* kf2, const float* F12, int onlyStereo, float nnratio, int checkOri,
+                                 int* pairs, int cap) {
+  cv::Mat F(3, 3, CV_32F);
+  for (int i = 0; i < 9; i++) F.at<float>(i / 3, i % 3) = F12[i];
+  std::vector<std::pair<size_t, size_t> > v;
+  ORBmatcher matcher(nnratio, checkOri != 0);
+  const int n = matcher.SearchForTriangulation(static_cast<KeyFrame*>(kf1), static_cast<KeyFrame*>(kf2), F, v, onlyStereo != 0);
+  for (size_t i = 0; i < v.size() && (int)i < cap; i++) { pairs[2 * i] = (int)v[i].first; pairs[2 * i + 1] = (int)v[i].second; }
+  return n == (int)v.size() ? n : -1000000;
+}
+
+void ref_keyframe_tables(void* kfp, float* scaleFactors, float* levelSigma2) {
+  KeyFrame& K = *static_cast<KeyFrame*>(kfp);
+  for (size_t i = 0; i < K.mvScaleFactors.size(); i++) { scaleFactors[i] = K.mvScaleFactors[i]; levelSigma2[i] = K.mvLevelSigma2[i]; }
+}
+
+// ---- MapPoint::ComputeDistinctiveDescriptors (R/src/MapPoint.cpp:306-385) -----------------------------------
+// rows: the descriptors the function gathers (:326-333), in the iteration order of the observations map -- the
+// flattening a drop-in caller performs. Returns their count.
+int ref_map_point_observed_rows(void* h, int mp, uint8_t* rows, int cap) {
+  MapPoint* p = static_cast<Front*>(h)->points[mp];
+  std::map<KeyFrame*, size_t> obs = p->GetObservations();
+  int n = 0;
+  for (std::map<KeyFrame*, size_t>::iterator it = obs.begin(); it != obs.end(); ++it) {
+    if (it->first->isBad()) continue;
+    if (n < cap) std::memcpy(rows + (size_t)n * 32, it->first->mDescriptors.ptr((int)it->second), 32);
+    n++;
+  }
+  return n;
+}
+// runs the reference's function and returns the descriptor it chose
+void ref_map_point_distinctive(void* h, int mp, uint8_t* out32) {
+  MapPoint* p = static_cast<Front*>(h)->points[mp];
+  p->ComputeDistinctiveDescriptors();
+  cv::Mat d = p->GetDescriptor();
+  std::memcpy(out32, d.ptr(0), 32);
 }
 
 }  // extern "C"

@@ -70,6 +70,9 @@ SIGNATURES = {
     "orbx_stereo_match_batch_device": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _i32, _f32, _f32, _vp, _vp, _vp,
                                                  _vp]),
     "orbx_match_merge_device": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _f32, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "orbx_match_blocks": (C.c_int, [_vp, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i64, C.POINTER(_i64)]),
+    "orbx_distinctive": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp]),
+    "orbx_distinctive_device": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp]),
 }
 
 _lib = None

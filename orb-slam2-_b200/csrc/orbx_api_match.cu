@@ -2,6 +2,7 @@
 #include <algorithm>
 #include <initializer_list>
 #include <new>
+#include <vector>
 
 #include "orbx_host.h"
 #include "orbx_stereo.cuh"
@@ -21,6 +22,10 @@ void launch_window(bool fill, const orbx_keypoint* kps, const uint8_t* desc, flo
                    int* candDist, cudaStream_t s);
 void launch_scan(const int* count, int n, int* off, cudaStream_t s);
 int grid_cells();
+void launch_block_distance(const uint8_t* descA, const uint8_t* descB, const int* aOff, const int* aIdx, const int* bOff,
+                           const int* bIdx, const int* entryBlock, const long long* dOff, int nEntries,
+                           unsigned short* dist, cudaStream_t s);
+void launch_distinctive(const uint8_t* desc, const int* obsOff, int nPoints, int* best, int* bestMedian, cudaStream_t s);
 }  // namespace orbx
 
 using namespace orbx;
@@ -398,6 +403,107 @@ int orbx_stereo_match_batch_device(orbx_matcher* h, orbx_extractor* ex, int32_t 
   if (le) { set_error("stereo kernel configuration failed: %s", cudaGetErrorString((cudaError_t)le)); return ORBX_ERR_CUDA; }
   h->launches += 3;
   ORBX_CUDA_TRY(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbx_match_blocks(orbx_matcher* h, const uint8_t* desc_a, int32_t na, const uint8_t* desc_b, int32_t nb,
+                      const int32_t* a_off, const int32_t* a_idx, const int32_t* b_off, const int32_t* b_idx,
+                      int32_t nblocks, int64_t* dist_off, uint16_t* dist, int64_t dist_cap, int64_t* n_dist) {
+  int rc = set_dev(h);
+  if (rc) return rc;
+  if (!dist_off || !n_dist || nblocks < 0 || na < 0 || nb < 0 || (nblocks > 0 && (!a_off || !b_off))) {
+    set_error("bad arguments");
+    return ORBX_ERR_ARG;
+  }
+  // host pass: matrix offsets, entry -> block table, index validation
+  long long total = 0;
+  dist_off[0] = 0;
+  for (int k = 0; k < nblocks; k++) {
+    const long long ca = (long long)a_off[k + 1] - a_off[k], cb = (long long)b_off[k + 1] - b_off[k];
+    if (ca < 0 || cb < 0 || (k == 0 && (a_off[0] != 0 || b_off[0] != 0))) { set_error("offsets of block %d are not a CSR", k); return ORBX_ERR_ARG; }
+    total += ca * cb;
+    dist_off[k + 1] = total;
+  }
+  *n_dist = total;
+  const int TA = nblocks ? a_off[nblocks] : 0, TB = nblocks ? b_off[nblocks] : 0;
+  if ((TA > 0 && (!a_idx || !desc_a)) || (TB > 0 && (!b_idx || !desc_b))) { set_error("bad arguments"); return ORBX_ERR_ARG; }
+  for (int i = 0; i < TA; i++) if (a_idx[i] < 0 || a_idx[i] >= na) { set_error("a_idx[%d] = %d out of range", i, a_idx[i]); return ORBX_ERR_ARG; }
+  for (int i = 0; i < TB; i++) if (b_idx[i] < 0 || b_idx[i] >= nb) { set_error("b_idx[%d] = %d out of range", i, b_idx[i]); return ORBX_ERR_ARG; }
+  if (total > dist_cap || (total > 0 && !dist)) { set_error("distance capacity %lld < %lld", (long long)dist_cap, total); return ORBX_ERR_CAPACITY; }
+  if (total == 0) return ORBX_OK;
+  std::vector<int> entryBlock((size_t)TA);
+  for (int k = 0; k < nblocks; k++) for (int e = a_off[k]; e < a_off[k + 1]; e++) entryBlock[e] = k;
+  const size_t NA = (size_t)na, NB = (size_t)nb, K = (size_t)nblocks;
+  if ((rc = h->dWin.ensure(carve_size({NA * 32, NB * 32, (K + 1) * 4, (size_t)TA * 4, (K + 1) * 4, (size_t)TB * 4, (size_t)TA * 4,
+                                       (K + 1) * 8, (size_t)total * 2}))))
+    return rc;
+  Carver c{static_cast<uint8_t*>(h->dWin.p)};
+  uint8_t* dA = c.take<uint8_t>(NA * 32);
+  uint8_t* dB = c.take<uint8_t>(NB * 32);
+  int* dAoff = c.take<int>(K + 1);
+  int* dAidx = c.take<int>(TA);
+  int* dBoff = c.take<int>(K + 1);
+  int* dBidx = c.take<int>(TB);
+  int* dEntry = c.take<int>(TA);
+  long long* dDoff = c.take<long long>(K + 1);
+  unsigned short* dDist = c.take<unsigned short>((size_t)total);
+  cudaStream_t s = h->stream;
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dA, desc_a, NA * 32, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dB, desc_b, NB * 32, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dAoff, a_off, (K + 1) * 4, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dAidx, a_idx, (size_t)TA * 4, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dBoff, b_off, (K + 1) * 4, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dBidx, b_idx, (size_t)TB * 4, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dEntry, entryBlock.data(), (size_t)TA * 4, cudaMemcpyHostToDevice, s));
+  static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dDoff, dist_off, (K + 1) * 8, cudaMemcpyHostToDevice, s));
+  // entryBlock is pageable: the copy above has been staged by the time cudaMemcpyAsync returns
+  launch_block_distance(dA, dB, dAoff, dAidx, dBoff, dBidx, dEntry, dDoff, TA, dDist, s);
+  h->launches++;
+  ORBX_CUDA_TRY(cudaGetLastError());
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dist, dDist, (size_t)total * 2, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  return ORBX_OK;
+}
+
+int orbx_distinctive_device(orbx_matcher* h, const uint8_t* d_desc, const int32_t* d_obs_off, int32_t npoints,
+                            int32_t* d_best, int32_t* d_best_median, void* stream) {
+  int rc = set_dev(h);
+  if (rc) return rc;
+  if (npoints < 0 || (npoints > 0 && (!d_desc || !d_obs_off || !d_best || !d_best_median))) { set_error("bad arguments"); return ORBX_ERR_ARG; }
+  if (npoints == 0) return ORBX_OK;
+  launch_distinctive(d_desc, d_obs_off, npoints, d_best, d_best_median, stream ? static_cast<cudaStream_t>(stream) : h->stream);
+  h->launches++;
+  ORBX_CUDA_TRY(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbx_distinctive(orbx_matcher* h, const uint8_t* desc, const int32_t* obs_off, int32_t npoints, int32_t* best,
+                     int32_t* best_median) {
+  int rc = set_dev(h);
+  if (rc) return rc;
+  if (npoints < 0 || (npoints > 0 && (!obs_off || !best || !best_median))) { set_error("bad arguments"); return ORBX_ERR_ARG; }
+  if (npoints == 0) return ORBX_OK;
+  if (obs_off[0] != 0) { set_error("obs_off[0] must be 0"); return ORBX_ERR_ARG; }
+  for (int p = 0; p < npoints; p++) {
+    const long long n = (long long)obs_off[p + 1] - obs_off[p];
+    if (n < 0 || n >= (1 << 20)) { set_error("point %d has %lld observations (supported: 0 .. 2^20-1)", p, n); return ORBX_ERR_ARG; }
+  }
+  const size_t R = (size_t)obs_off[npoints], P = (size_t)npoints;
+  if (R > 0 && !desc) { set_error("bad arguments"); return ORBX_ERR_ARG; }
+  if ((rc = h->dWin.ensure(carve_size({std::max<size_t>(R, 1) * 32, (P + 1) * 4, P * 4, P * 4})))) return rc;
+  Carver c{static_cast<uint8_t*>(h->dWin.p)};
+  uint8_t* dD = c.take<uint8_t>(std::max<size_t>(R, 1) * 32);
+  int* dOff = c.take<int>(P + 1);
+  int* dBest = c.take<int>(P);
+  int* dMed = c.take<int>(P);
+  cudaStream_t s = h->stream;
+  if (R > 0) ORBX_CUDA_TRY(cudaMemcpyAsync(dD, desc, R * 32, cudaMemcpyHostToDevice, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dOff, obs_off, (P + 1) * 4, cudaMemcpyHostToDevice, s));
+  if ((rc = orbx_distinctive_device(h, dD, dOff, npoints, dBest, dMed, s))) return rc;
+  ORBX_CUDA_TRY(cudaMemcpyAsync(best, dBest, P * 4, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(best_median, dMed, P * 4, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(s));
   return ORBX_OK;
 }
 

@@ -88,4 +88,43 @@ int mirror_search_by_projection_frame(orbx_matcher* m, const orbx_keypoint* k, c
                                        thDist, checkOri != 0, curMatch, qHasObs);
 }
 
+static orbx_host::BowView bow_view(const orbx_keypoint* k, const unsigned char* d, int n, const int* nodes, const int* off,
+                                   const int* idx, int nn, const unsigned char* flag, const float* ur) {
+  orbx_host::BowView v;
+  v.keysUn = k; v.descriptors = d; v.N = n; v.featVec.nodes = nodes; v.featVec.off = off; v.featVec.idx = idx; v.featVec.n = nn;
+  v.flag = flag; v.uRight = ur;
+  return v;
+}
+
+int mirror_search_by_bow_kf_frame(orbx_matcher* m, const orbx_keypoint* kKF, const unsigned char* dKF, int nKF,
+                                  const int* nodesKF, const int* offKF, const int* idxKF, int nnKF, const unsigned char* usable,
+                                  const orbx_keypoint* kF, const unsigned char* dF, int nF, const int* nodesF, const int* offF,
+                                  const int* idxF, int nnF, float nnratio, int checkOri, int* matchF) {
+  return orbx_host::SearchByBoW(m, bow_view(kKF, dKF, nKF, nodesKF, offKF, idxKF, nnKF, usable, 0),
+                                bow_view(kF, dF, nF, nodesF, offF, idxF, nnF, 0, 0), nnratio, checkOri != 0, matchF);
+}
+
+int mirror_search_by_bow_kf_kf(orbx_matcher* m, const orbx_keypoint* k1, const unsigned char* d1, int n1, const int* nodes1,
+                               const int* off1, const int* idx1, int nn1, const unsigned char* usable1, const orbx_keypoint* k2,
+                               const unsigned char* d2, int n2, const int* nodes2, const int* off2, const int* idx2, int nn2,
+                               const unsigned char* usable2, float nnratio, int checkOri, int* matches12) {
+  return orbx_host::SearchByBoWKeyFrames(m, bow_view(k1, d1, n1, nodes1, off1, idx1, nn1, usable1, 0),
+                                         bow_view(k2, d2, n2, nodes2, off2, idx2, nn2, usable2, 0), nnratio, checkOri != 0,
+                                         matches12);
+}
+
+int mirror_search_for_triangulation(orbx_matcher* m, const orbx_keypoint* k1, const unsigned char* d1, int n1, const int* nodes1,
+                                    const int* off1, const int* idx1, int nn1, const unsigned char* hasMP1, const float* ur1,
+                                    const orbx_keypoint* k2, const unsigned char* d2, int n2, const int* nodes2, const int* off2,
+                                    const int* idx2, int nn2, const unsigned char* hasMP2, const float* ur2, const float* F12,
+                                    float ex, float ey, const float* scaleFactors2, const float* levelSigma2_2, int onlyStereo,
+                                    int checkOri, int* pairs) {
+  std::vector<std::pair<int, int> > v;
+  const int n = orbx_host::SearchForTriangulation(m, bow_view(k1, d1, n1, nodes1, off1, idx1, nn1, hasMP1, ur1),
+                                                  bow_view(k2, d2, n2, nodes2, off2, idx2, nn2, hasMP2, ur2), F12, ex, ey,
+                                                  scaleFactors2, levelSigma2_2, onlyStereo != 0, checkOri != 0, &v);
+  for (size_t i = 0; i < v.size(); i++) { pairs[2 * i] = v[i].first; pairs[2 * i + 1] = v[i].second; }
+  return n == (int)v.size() ? n : -1000000;
+}
+
 }  // extern "C"

@@ -2,6 +2,7 @@
 // Hamming distances come from the device.
 #include "orbx_search.h"
 
+#include <algorithm>
 #include <climits>
 #include <cmath>
 #include <cstdio>
@@ -210,6 +211,198 @@ int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* has
           nmatches--;
         }
   }
+  return nmatches;
+}
+
+// ---- bag-of-words restricted searches ------------------------------------------------------------------------
+namespace {
+
+// The vocabulary nodes both feature vectors hold, in ascending order (the while / lower_bound walk of :232-340), and the
+// distance matrix of every such node from the device.
+struct NodeBlocks {
+  std::vector<int> aOff, aIdx, bOff, bIdx;
+  std::vector<long long> dOff;
+  std::vector<unsigned short> dist;
+  int n() const { return (int)aOff.size() - 1; }
+};
+
+void CommonNodeDistances(orbx_matcher* m, const BowView& A, const BowView& B, NodeBlocks* nb) {
+  nb->aOff.assign(1, 0);
+  nb->bOff.assign(1, 0);
+  nb->aIdx.clear();
+  nb->bIdx.clear();
+  const FeatVecView &fa = A.featVec, &fb = B.featVec;
+  int i = 0, j = 0;
+  while (i < fa.n && j < fb.n) {
+    if (fa.nodes[i] == fb.nodes[j]) {
+      nb->aIdx.insert(nb->aIdx.end(), fa.idx + fa.off[i], fa.idx + fa.off[i + 1]);
+      nb->bIdx.insert(nb->bIdx.end(), fb.idx + fb.off[j], fb.idx + fb.off[j + 1]);
+      nb->aOff.push_back((int)nb->aIdx.size());
+      nb->bOff.push_back((int)nb->bIdx.size());
+      i++; j++;
+    } else if (fa.nodes[i] < fb.nodes[j]) {
+      i = (int)(std::lower_bound(fa.nodes, fa.nodes + fa.n, fb.nodes[j]) - fa.nodes);
+    } else {
+      j = (int)(std::lower_bound(fb.nodes, fb.nodes + fb.n, fa.nodes[i]) - fb.nodes);
+    }
+  }
+  const int K = nb->n();
+  nb->dOff.assign(K + 1, 0);
+  long long total = 0;
+  for (int k = 0; k < K; k++) total += (long long)(nb->aOff[k + 1] - nb->aOff[k]) * (nb->bOff[k + 1] - nb->bOff[k]);
+  nb->dist.resize((size_t)std::max<long long>(total, 1));
+  int64_t need = 0;
+  static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
+  const int rc = orbx_match_blocks(m, A.descriptors, A.N, B.descriptors, B.N, &nb->aOff[0], nb->aIdx.empty() ? nullptr : &nb->aIdx[0],
+                                   &nb->bOff[0], nb->bIdx.empty() ? nullptr : &nb->bIdx[0], K,
+                                   reinterpret_cast<int64_t*>(&nb->dOff[0]), &nb->dist[0], (int64_t)nb->dist.size(), &need);
+  if (rc != ORBX_OK) Fail("orbx_match_blocks");
+}
+
+// removes the matches outside the three dominant rotation bins (:342-362, :744-768, :947-967); returns how many
+template <class Clear>
+int PruneRotation(const std::vector<int>* rotHist, Clear clear) {
+  int ind1 = -1, ind2 = -1, ind3 = -1, removed = 0;
+  ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+  for (int i = 0; i < HISTO_LENGTH; i++) {
+    if (i == ind1 || i == ind2 || i == ind3) continue;
+    for (size_t j = 0; j < rotHist[i].size(); j++) { clear(rotHist[i][j]); removed++; }
+  }
+  return removed;
+}
+
+}  // namespace
+
+int SearchByBoW(orbx_matcher* m, const BowView& KF, const BowView& F, float nnratio, bool checkOrientation, int* matchF) {
+  for (int i = 0; i < F.N; i++) matchF[i] = -1;
+  NodeBlocks nb;
+  CommonNodeDistances(m, KF, F, &nb);
+  std::vector<int> rotHist[HISTO_LENGTH];
+  int nmatches = 0;
+  for (int k = 0; k < nb.n(); k++) {
+    const int nF = nb.bOff[k + 1] - nb.bOff[k];
+    const int* idxF = nF ? &nb.bIdx[nb.bOff[k]] : nullptr;
+    for (int e = nb.aOff[k]; e < nb.aOff[k + 1]; e++) {
+      const int realIdxKF = nb.aIdx[e];
+      if (!KF.flag[realIdxKF]) continue;                               // :247-253
+      const unsigned short* d = &nb.dist[nb.dOff[k] + (long long)(e - nb.aOff[k]) * nF];
+      int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+      for (int iF = 0; iF < nF; iF++) {
+        const int realIdxF = idxF[iF];
+        if (matchF[realIdxF] >= 0) continue;                           // :265
+        const int dist = d[iF];
+        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+        else if (dist < bestDist2) bestDist2 = dist;
+      }
+      if (bestDist1 <= TH_LOW && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {   // :285-287
+        matchF[bestIdxF] = realIdxKF;
+        if (checkOrientation) rotHist[RotBin(KF.keysUn[realIdxKF].angle, F.keysUn[bestIdxF].angle)].push_back(bestIdxF);
+        nmatches++;
+      }
+    }
+  }
+  if (checkOrientation) nmatches -= PruneRotation(rotHist, [&](int iF) { matchF[iF] = -1; });
+  return nmatches;
+}
+
+int SearchByBoWKeyFrames(orbx_matcher* m, const BowView& KF1, const BowView& KF2, float nnratio, bool checkOrientation,
+                         int* matches12) {
+  for (int i = 0; i < KF1.N; i++) matches12[i] = -1;
+  NodeBlocks nb;
+  CommonNodeDistances(m, KF1, KF2, &nb);
+  std::vector<unsigned char> vbMatched2((size_t)std::max(KF2.N, 1), 0);
+  std::vector<int> rotHist[HISTO_LENGTH];
+  int nmatches = 0;
+  for (int k = 0; k < nb.n(); k++) {
+    const int n2 = nb.bOff[k + 1] - nb.bOff[k];
+    const int* list2 = n2 ? &nb.bIdx[nb.bOff[k]] : nullptr;
+    for (int e = nb.aOff[k]; e < nb.aOff[k + 1]; e++) {
+      const int idx1 = nb.aIdx[e];
+      if (!KF1.flag[idx1]) continue;                                   // :667-673
+      const unsigned short* d = &nb.dist[nb.dOff[k] + (long long)(e - nb.aOff[k]) * n2];
+      int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+      for (int i2 = 0; i2 < n2; i2++) {
+        const int idx2 = list2[i2];
+        if (vbMatched2[idx2] || !KF2.flag[idx2]) continue;             // :682-688
+        const int dist = d[i2];
+        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+        else if (dist < bestDist2) bestDist2 = dist;
+      }
+      if (bestDist1 < TH_LOW && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {   // :707-709
+        matches12[idx1] = bestIdx2;
+        vbMatched2[bestIdx2] = 1;
+        if (checkOrientation) rotHist[RotBin(KF1.keysUn[idx1].angle, KF2.keysUn[bestIdx2].angle)].push_back(idx1);
+        nmatches++;
+      }
+    }
+  }
+  if (checkOrientation) nmatches -= PruneRotation(rotHist, [&](int i1) { matches12[i1] = -1; });
+  return nmatches;
+}
+
+namespace {
+// R/src/ORBmatcher.cpp:175-203. The reference is built with -O3 and GCC's default -ffp-contract=fast; the fused
+// operations below are the ones its object code holds, written out so that this file gives the
+// same bits under any contraction setting.
+bool CheckDistEpipolarLine(const orbx_keypoint& kp1, const orbx_keypoint& kp2, const float* F12, const float* levelSigma2_2) {
+  const float a = fmaf(kp1.x, F12[0], kp1.y * F12[3]) + F12[6];
+  const float b = fmaf(kp1.x, F12[1], kp1.y * F12[4]) + F12[7];
+  const float c = fmaf(kp1.y, F12[5], kp1.x * F12[2]) + F12[8];
+  const float num = c + fmaf(b, kp2.y, a * kp2.x);
+  const float den = fmaf(a, a, b * b);
+  if (den == 0) return false;
+  const float dsqr = num * num / den;
+  return dsqr < 3.84 * levelSigma2_2[kp2.octave];
+}
+}  // namespace
+
+int SearchForTriangulation(orbx_matcher* m, const BowView& KF1, const BowView& KF2, const float* F12, float ex, float ey,
+                           const float* scaleFactors2, const float* levelSigma2_2, bool onlyStereo, bool checkOrientation,
+                           std::vector<std::pair<int, int> >* vMatchedPairs) {
+  NodeBlocks nb;
+  CommonNodeDistances(m, KF1, KF2, &nb);
+  std::vector<unsigned char> vbMatched2((size_t)std::max(KF2.N, 1), 0);
+  std::vector<int> vMatches12((size_t)KF1.N, -1);
+  std::vector<int> rotHist[HISTO_LENGTH];
+  int nmatches = 0;
+  for (int k = 0; k < nb.n(); k++) {
+    const int n2 = nb.bOff[k + 1] - nb.bOff[k];
+    const int* list2 = n2 ? &nb.bIdx[nb.bOff[k]] : nullptr;
+    for (int e = nb.aOff[k]; e < nb.aOff[k + 1]; e++) {
+      const int idx1 = nb.aIdx[e];
+      if (KF1.flag[idx1]) continue;                                    // :833-836: already has a map point
+      const bool bStereo1 = KF1.uRight && KF1.uRight[idx1] >= 0;
+      if (onlyStereo && !bStereo1) continue;
+      const orbx_keypoint& kp1 = KF1.keysUn[idx1];
+      const unsigned short* d = &nb.dist[nb.dOff[k] + (long long)(e - nb.aOff[k]) * n2];
+      int bestDist = TH_LOW, bestIdx2 = -1;
+      for (int i2 = 0; i2 < n2; i2++) {
+        const int idx2 = list2[i2];
+        if (vbMatched2[idx2] || KF2.flag[idx2]) continue;              // :858-859
+        const bool bStereo2 = KF2.uRight && KF2.uRight[idx2] >= 0;
+        if (onlyStereo && !bStereo2) continue;
+        const int dist = d[i2];
+        if (dist > TH_LOW || dist > bestDist) continue;                // :872
+        const orbx_keypoint& kp2 = KF2.keysUn[idx2];
+        if (!bStereo1 && !bStereo2) {
+          const float distex = ex - kp2.x, distey = ey - kp2.y;
+          if (fmaf(distex, distex, distey * distey) < 100 * scaleFactors2[kp2.octave]) continue;   // :881-883
+        }
+        if (CheckDistEpipolarLine(kp1, kp2, F12, levelSigma2_2)) { bestIdx2 = idx2; bestDist = dist; }
+      }
+      if (bestIdx2 >= 0) {
+        vMatches12[idx1] = bestIdx2;
+        vbMatched2[bestIdx2] = 1;
+        nmatches++;
+        if (checkOrientation) rotHist[RotBin(kp1.angle, KF2.keysUn[bestIdx2].angle)].push_back(idx1);
+      }
+    }
+  }
+  if (checkOrientation) nmatches -= PruneRotation(rotHist, [&](int i1) { vMatches12[i1] = -1; });
+  vMatchedPairs->clear();
+  vMatchedPairs->reserve(nmatches);
+  for (int i = 0; i < KF1.N; i++)
+    if (vMatches12[i] >= 0) vMatchedPairs->push_back(std::make_pair(i, vMatches12[i]));
   return nmatches;
 }
 

@@ -9,6 +9,7 @@
 #ifndef ORBX_SEARCH_H_
 #define ORBX_SEARCH_H_
 
+#include <utility>
 #include <vector>
 
 #include "orbx.h"
@@ -51,6 +52,43 @@ int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* has
                        const float* qRadius, const int* qMinLevel, const int* qMaxLevel, const float* qUR,
                        const float* qAngle, const unsigned char* qDesc, int nQ, int thDist, bool checkOrientation,
                        int* curMatch, const unsigned char* qHasObs = nullptr);
+
+// ---- bag-of-words restricted searches ---------------------------------------------------
+// A DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) flattened in map order: node ids ascending,
+// CSR offsets, feature indices. A replacement ORBmatcher.cpp builds it with one pass over mFeatVec.
+struct FeatVecView {
+  const int* nodes;
+  const int* off;
+  const int* idx;
+  int n;
+};
+
+// A KeyFrame (or Frame) as these searches see it: mvKeysUn, mDescriptors, mFeatVec, mvuRight (NULL: monocular) and,
+// per keypoint, a flag whose meaning the function states (it flattens GetMapPointMatches() / GetMapPoint(i)).
+struct BowView {
+  const orbx_keypoint* keysUn;
+  const unsigned char* descriptors;
+  int N;
+  FeatVecView featVec;
+  const unsigned char* flag;
+  const float* uRight;
+};
+
+// R/src/ORBmatcher.cpp:220-365. KF.flag[i] != 0 <=> vpMapPointsKF[i] && !isBad(). F.flag is not read.
+// matchF[iF] (F.N entries) = key-frame feature whose map point goes to vpMapPointMatches[iF], or -1. Returns nmatches.
+int SearchByBoW(orbx_matcher* m, const BowView& KF, const BowView& F, float nnratio, bool checkOrientation, int* matchF);
+
+// R/src/ORBmatcher.cpp:632-772. flag[i] != 0 <=> vpMapPoints[i] && !isBad() in both key frames.
+// matches12[i1] (KF1.N entries) = feature of key frame 2 whose map point goes to vpMatches12[i1], or -1.
+int SearchByBoWKeyFrames(orbx_matcher* m, const BowView& KF1, const BowView& KF2, float nnratio, bool checkOrientation,
+                         int* matches12);
+
+// R/src/ORBmatcher.cpp:785-983 after its prologue (:790-803, cv::Mat algebra, stays with the caller): (ex, ey) = the
+// epipole of camera 1 in image 2; F12 = 3x3 row-major; flag[i] != 0 <=> GetMapPoint(i) != NULL; scaleFactors2 /
+// levelSigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2. vMatchedPairs = (idx1, idx2) in idx1 order. Returns nmatches.
+int SearchForTriangulation(orbx_matcher* m, const BowView& KF1, const BowView& KF2, const float* F12, float ex, float ey,
+                           const float* scaleFactors2, const float* levelSigma2_2, bool onlyStereo, bool checkOrientation,
+                           std::vector<std::pair<int, int> >* vMatchedPairs);
 
 }  // namespace orbx_host
 

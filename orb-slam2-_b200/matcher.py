@@ -101,5 +101,36 @@ class ORBmatcher:
         check(lib().orbx_stereo_match_batch_device(self._h, ex._h, pairs, left_frame0, right_frame0, frame_step, d_kps, d_desc,
                                                    d_n, cap, mbf, mb, d_u_right, d_depth, d_n_matched, stream))
 
+    def match_blocks(self, desc_a, desc_b, a_off, a_idx, b_off, b_idx):
+        """Distance matrices of the vocabulary nodes two feature vectors share (SearchByBoW / SearchForTriangulation,
+        R/src/ORBmatcher.cpp:220-365, :632-772, :785-983): (dist_off[nblocks+1] int64, dist uint16), block k row-major
+        [a entries][b entries] at dist[dist_off[k]:dist_off[k+1]]."""
+        desc_a = np.ascontiguousarray(desc_a, np.uint8).reshape(-1, 32)
+        desc_b = np.ascontiguousarray(desc_b, np.uint8).reshape(-1, 32)
+        a_off, a_idx = np.ascontiguousarray(a_off, np.int32), np.ascontiguousarray(a_idx, np.int32)
+        b_off, b_idx = np.ascontiguousarray(b_off, np.int32), np.ascontiguousarray(b_idx, np.int32)
+        if len(a_off) != len(b_off) or len(a_off) < 1:
+            raise ValueError("a_off and b_off must hold nblocks+1 entries each")
+        nblocks = len(a_off) - 1
+        off = np.zeros(nblocks + 1, np.int64)
+        need = int(np.sum(np.diff(a_off).astype(np.int64) * np.diff(b_off).astype(np.int64))) if nblocks else 0
+        dist = np.empty(max(need, 1), np.uint16)
+        n = C.c_int64(0)
+        check(lib().orbx_match_blocks(self._h, ptr(desc_a), len(desc_a), ptr(desc_b), len(desc_b), ptr(a_off), ptr(a_idx),
+                                      ptr(b_off), ptr(b_idx), nblocks, ptr(off), ptr(dist), len(dist), C.byref(n)))
+        return off, dist[:n.value]
+
+    def distinctive(self, desc, obs_off):
+        """MapPoint::ComputeDistinctiveDescriptors (R/src/MapPoint.cpp:306-385) for many points: point p observes rows
+        desc[obs_off[p]:obs_off[p+1]]; returns (best position within the group or -1, its median distance)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        obs_off = np.ascontiguousarray(obs_off, np.int32)
+        npoints = len(obs_off) - 1
+        if npoints < 0 or (npoints > 0 and obs_off[-1] != len(desc)):
+            raise ValueError("obs_off must be a CSR over the descriptor rows")
+        best, med = np.empty(max(npoints, 1), np.int32), np.empty(max(npoints, 1), np.int32)
+        check(lib().orbx_distinctive(self._h, ptr(desc), ptr(obs_off), npoints, ptr(best), ptr(med)))
+        return best[:npoints], med[:npoints]
+
     def launch_count(self):
         return int(lib().orbx_matcher_launch_count(self._h))

@@ -80,6 +80,15 @@ def lib():
             [C.c_float] * 4 + [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.orb_oracle_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int] + \
             [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        V, I, F = C.c_void_p, C.c_int, C.c_float
+        L.orb_oracle_block_distances.argtypes = [V] * 6 + [I, V, V]
+        L.orb_oracle_block_distances.restype = None
+        L.orb_oracle_search_by_bow_kf_frame.argtypes = [V, V, V, V, V, V, I, V, V, I, V, V, V, I, F, I, V]
+        L.orb_oracle_search_by_bow_kf_kf.argtypes = [V, V, V, I, V, V, V, I, V, V, V, I, V, V, V, I, F, I, V]
+        L.orb_oracle_search_for_triangulation.argtypes = [V, V, V, V, I, V, V, V, I, V, V, V, V, I, V, V, V, I, V, F, F, V, V,
+                                                          I, I, V]
+        L.orb_oracle_distinctive.argtypes = [V, V, I, V, V]
+        L.orb_oracle_distinctive.restype = None
     return _lib
 
 
@@ -314,3 +323,90 @@ def stereo_matches(kps_l, desc_l, kps_r, desc_r, pyr_l, pyr_r, scale_factors, in
                                         PL, PR, _ptr(w), _ptr(h), _ptr(st), nlev, _ptr(sf), _ptr(isf), mbf, mb,
                                         _ptr(u), _ptr(z))
     return u[:len(kps_l)], z[:len(kps_l)], n
+
+
+# ---- bag-of-words restricted searches, distinctive descriptors -----------------------
+def featvec(node):
+    """Flatten what DBoW2::FeatureVector::addFeature builds when features are added in index order: node[i] = vocabulary
+    node of feature i (< 0: none). Returns (node ids ascending, CSR offsets, feature indices) as int32 arrays."""
+    node = np.asarray(node, np.int64)
+    keep = np.nonzero(node >= 0)[0]
+    order = keep[np.argsort(node[keep], kind="stable")]
+    ids, counts = np.unique(node[keep], return_counts=True)
+    off = np.zeros(len(ids) + 1, np.int32)
+    off[1:] = np.cumsum(counts)
+    return ids.astype(np.int32), off, order.astype(np.int32)
+
+
+def common_blocks(fv_a, fv_b):
+    """The nodes both feature vectors hold, as the (a_off, a_idx, b_off, b_idx) CSR orbx_match_blocks takes."""
+    ids_a, off_a, idx_a = fv_a
+    ids_b, off_b, idx_b = fv_b
+    common, ia, ib = np.intersect1d(ids_a, ids_b, return_indices=True)
+    a_off, b_off, a_idx, b_idx = [0], [0], [], []
+    for x, y in zip(ia, ib):
+        a_idx.append(idx_a[off_a[x]:off_a[x + 1]])
+        b_idx.append(idx_b[off_b[y]:off_b[y + 1]])
+        a_off.append(a_off[-1] + len(a_idx[-1]))
+        b_off.append(b_off[-1] + len(b_idx[-1]))
+    cat = lambda v: np.concatenate(v).astype(np.int32) if v else np.zeros(0, np.int32)
+    return np.array(a_off, np.int32), cat(a_idx), np.array(b_off, np.int32), cat(b_idx)
+
+
+def block_distances(desc_a, desc_b, a_off, a_idx, b_off, b_idx):
+    desc_a, desc_b = np.ascontiguousarray(desc_a, np.uint8), np.ascontiguousarray(desc_b, np.uint8)
+    arrs = [np.ascontiguousarray(a, np.int32) for a in (a_off, a_idx, b_off, b_idx)]
+    nblocks = len(arrs[0]) - 1
+    total = int(np.sum(np.diff(arrs[0]).astype(np.int64) * np.diff(arrs[2]).astype(np.int64)))
+    off = np.zeros(nblocks + 1, np.int64)
+    dist = np.empty(max(total, 1), np.uint16)
+    lib().orb_oracle_block_distances(_ptr(desc_a), _ptr(desc_b), *[_ptr(a) for a in arrs], nblocks, _ptr(off), _ptr(dist))
+    return off, dist[:total]
+
+
+def search_by_bow_kf_frame(desc_kf, angle_kf, kf_usable, fv_kf, desc_f, angle_f, fv_f, nnratio, check_ori=True):
+    desc_kf, desc_f = np.ascontiguousarray(desc_kf, np.uint8), np.ascontiguousarray(desc_f, np.uint8)
+    angle_kf, angle_f = np.ascontiguousarray(angle_kf, np.float32), np.ascontiguousarray(angle_f, np.float32)
+    usable = np.ascontiguousarray(kf_usable, np.uint8)
+    match = np.empty(max(len(desc_f), 1), np.int32)
+    n = lib().orb_oracle_search_by_bow_kf_frame(_ptr(desc_kf), _ptr(angle_kf), _ptr(usable), *[_ptr(a) for a in fv_kf],
+                                                len(fv_kf[0]), _ptr(desc_f), _ptr(angle_f), len(desc_f),
+                                                *[_ptr(a) for a in fv_f], len(fv_f[0]), nnratio, int(check_ori), _ptr(match))
+    return n, match[:len(desc_f)]
+
+
+def search_by_bow_kf_kf(desc1, angle1, usable1, fv1, desc2, angle2, usable2, fv2, nnratio, check_ori=True):
+    desc1, desc2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    angle1, angle2 = np.ascontiguousarray(angle1, np.float32), np.ascontiguousarray(angle2, np.float32)
+    u1, u2 = np.ascontiguousarray(usable1, np.uint8), np.ascontiguousarray(usable2, np.uint8)
+    match = np.empty(max(len(desc1), 1), np.int32)
+    n = lib().orb_oracle_search_by_bow_kf_kf(_ptr(desc1), _ptr(angle1), _ptr(u1), len(desc1), *[_ptr(a) for a in fv1],
+                                             len(fv1[0]), _ptr(desc2), _ptr(angle2), _ptr(u2), len(desc2),
+                                             *[_ptr(a) for a in fv2], len(fv2[0]), nnratio, int(check_ori), _ptr(match))
+    return n, match[:len(desc1)]
+
+
+def search_for_triangulation(kps1, desc1, has_mp1, uright1, fv1, kps2, desc2, has_mp2, uright2, fv2, F12, ex, ey,
+                             scale_factors2, level_sigma2_2, only_stereo, check_ori=True):
+    kps1, kps2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    desc1, desc2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    h1, h2 = np.ascontiguousarray(has_mp1, np.uint8), np.ascontiguousarray(has_mp2, np.uint8)
+    u1, u2 = np.ascontiguousarray(uright1, np.float32), np.ascontiguousarray(uright2, np.float32)
+    F = np.ascontiguousarray(F12, np.float32).reshape(9)
+    sf, ls = np.ascontiguousarray(scale_factors2, np.float32), np.ascontiguousarray(level_sigma2_2, np.float32)
+    match = np.empty(max(len(kps1), 1), np.int32)
+    n = lib().orb_oracle_search_for_triangulation(_ptr(kps1), _ptr(desc1), _ptr(h1), _ptr(u1), len(kps1),
+                                                  *[_ptr(a) for a in fv1], len(fv1[0]), _ptr(kps2), _ptr(desc2), _ptr(h2),
+                                                  _ptr(u2), len(kps2), *[_ptr(a) for a in fv2], len(fv2[0]), _ptr(F),
+                                                  float(ex), float(ey), _ptr(sf), _ptr(ls), int(only_stereo), int(check_ori),
+                                                  _ptr(match))
+    return n, match[:len(kps1)]
+
+
+def distinctive(desc, obs_off):
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    obs_off = np.ascontiguousarray(obs_off, np.int32)
+    npoints = len(obs_off) - 1
+    best, med = np.empty(max(npoints, 1), np.int32), np.empty(max(npoints, 1), np.int32)
+    lib().orb_oracle_distinctive(_ptr(desc), _ptr(obs_off), npoints, _ptr(best), _ptr(med))
+    return best[:npoints], med[:npoints]

@@ -51,6 +51,19 @@ def lib():
         L.ref_search_by_projection_mp.argtypes = [P, P, P, C.c_int, C.c_float, C.c_float, C.c_int]
         L.ref_search_by_projection_frame.argtypes = [P, P, C.c_float, C.c_int, C.c_float, C.c_int]
         L.ref_project_last_frame.argtypes = [P, P, C.c_int] + [P] * 6
+        L.ref_keyframe_create.restype = P
+        L.ref_keyframe_create.argtypes = [P, P]
+        L.ref_frame_set_featvec.argtypes = [P, P, C.c_int]
+        L.ref_keyframe_set_featvec.argtypes = [P, P, C.c_int]
+        L.ref_keyframe_add_map_point.argtypes = [P, P, C.c_int, C.c_int]
+        L.ref_keyframe_address_rank.argtypes = [P, P]
+        L.ref_search_by_bow_kf_frame.argtypes = [P, P, P, C.c_float, C.c_int, P]
+        L.ref_search_by_bow_kf_kf.argtypes = [P, P, P, C.c_float, C.c_int, P]
+        L.ref_epipole.argtypes = [P, P, P, P]
+        L.ref_search_for_triangulation.argtypes = [P, P, P, C.c_int, C.c_float, C.c_int, P, C.c_int]
+        L.ref_keyframe_tables.argtypes = [P, P, P]
+        L.ref_map_point_observed_rows.argtypes = [P, C.c_int, P, C.c_int]
+        L.ref_map_point_distinctive.argtypes = [P, C.c_int, P]
         L.ref_set_allocator_mode(1)   # pointer order == creation order: the canonical DistributeOctTree tie-break
         _lib = L
     return _lib
@@ -97,6 +110,31 @@ class Frame:
         out = np.empty(self.N, np.int32)
         lib().ref_frame_get_map_points(self.front._h, self._h, _p(out))
         return out
+
+    def set_featvec(self, node):
+        node = np.ascontiguousarray(node, np.int32)
+        lib().ref_frame_set_featvec(self._h, _p(node), len(node))
+
+
+class KeyFrame:
+    """A reference KeyFrame built from a reference Frame (owned by the Front)."""
+
+    def __init__(self, front, frame):
+        self.front, self.frame = front, frame
+        self._h = lib().ref_keyframe_create(front._h, frame._h)
+        self.N = frame.N
+
+    def set_featvec(self, node):
+        node = np.ascontiguousarray(node, np.int32)
+        lib().ref_keyframe_set_featvec(self._h, _p(node), len(node))
+
+    def add_map_point(self, idx, mp):
+        lib().ref_keyframe_add_map_point(self.front._h, self._h, idx, mp)
+
+    def tables(self):
+        sf, ls = np.empty(self.front.nlevels, np.float32), np.empty(self.front.nlevels, np.float32)
+        lib().ref_keyframe_tables(self._h, _p(sf), _p(ls))
+        return sf, ls
 
 
 class Front:
@@ -158,3 +196,41 @@ class Front:
         fwd, bwd = C.c_int(), C.c_int()
         lib().ref_project_last_frame(cur._h, last._h, int(mono), _p(valid), _p(u), _p(v), _p(invz), C.byref(fwd), C.byref(bwd))
         return valid.astype(bool), u, v, invz, bool(fwd.value), bool(bwd.value)
+
+    # ---- key frames, bag-of-words restricted searches, distinctive descriptors ----
+    def keyframe(self, frame):
+        return KeyFrame(self, frame)
+
+    def search_by_bow_kf_frame(self, kf, frame, nnratio, check_ori=True):
+        out = np.empty(max(frame.N, 1), np.int32)
+        n = lib().ref_search_by_bow_kf_frame(self._h, kf._h, frame._h, nnratio, int(check_ori), _p(out))
+        return n, out[:frame.N]
+
+    def search_by_bow_kf_kf(self, kf1, kf2, nnratio, check_ori=True):
+        out = np.empty(max(kf1.N, 1), np.int32)
+        n = lib().ref_search_by_bow_kf_kf(self._h, kf1._h, kf2._h, nnratio, int(check_ori), _p(out))
+        return n, out[:kf1.N]
+
+    def epipole(self, kf1, kf2):
+        ex, ey = C.c_float(), C.c_float()
+        lib().ref_epipole(kf1._h, kf2._h, C.byref(ex), C.byref(ey))
+        return np.float32(ex.value), np.float32(ey.value)
+
+    def search_for_triangulation(self, kf1, kf2, F12, only_stereo, nnratio=0.6, check_ori=False):
+        F = np.ascontiguousarray(F12, np.float32).reshape(9)
+        pairs = np.empty((max(kf1.N, 1), 2), np.int32)
+        n = lib().ref_search_for_triangulation(kf1._h, kf2._h, _p(F), int(only_stereo), nnratio, int(check_ori), _p(pairs),
+                                               len(pairs))
+        assert n >= 0
+        return n, pairs[:n]
+
+    def observed_rows(self, mp):
+        n = lib().ref_map_point_observed_rows(self._h, mp, None, 0)
+        rows = np.empty((max(n, 1), 32), np.uint8)
+        lib().ref_map_point_observed_rows(self._h, mp, _p(rows), n)
+        return rows[:n]
+
+    def distinctive(self, mp):
+        out = np.empty(32, np.uint8)
+        lib().ref_map_point_distinctive(self._h, mp, _p(out))
+        return out
