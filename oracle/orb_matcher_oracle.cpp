@@ -630,3 +630,54 @@ void orb_oracle_distinctive(const uint8_t* desc, const int32_t* obs_off, int npo
 }
 
 }  // extern "C"
+
+extern "C" {
+
+/* The windowed best-match loop shared by ORBmatcher::Fuse (R/src/ORBmatcher.cpp:995-1160, with its chi-square
+ * gates :1070-1099; :1164-1296 without), SearchByProjection(KeyFrame*, Scw, ...) (:370-497, `taken` = vpMatched)
+ * and both directions of SearchBySim3 (:1305-1547), after their projection prologues: per query (u, v), radius =
+ * th * mvScaleFactors[level], predicted level, ur = u - bf*invz (gate only), descriptor. Candidates =
+ * KeyFrame::GetFeaturesInArea(u, v, radius) (R/src/KeyFrame.cpp:702-743) with octave in [level-1, level].
+ * inv_level_sigma2 != NULL switches the gates on: e2 = ex*ex + ey*ey (+ er*er when mvuRight[idx] >= 0) with the
+ * contractions of the reference's object code (fma(ex,ex,ey*ey), fma(er,er,.)), rejected when e2*invSigma2 > 5.99
+ * (7.8 stereo). taken != NULL: keypoints with taken[idx] are skipped and a query that ends with best <= th takes its
+ * keypoint (:453-454, :479-483). PINNED: tests/test_oracle_vs_ref_bow.py (Fuse and SearchByProjection on real objects). */
+void orb_oracle_search_best_in_window(const orb_oracle_keypoint* kps_un, const uint8_t* desc, int n, const float* uright,
+                                      float min_x, float max_x, float min_y, float max_y, const float* inv_level_sigma2,
+                                      const float* q_uv, const float* q_ur, const float* q_radius, const int32_t* q_level,
+                                      const uint8_t* q_desc, int nq, uint8_t* taken, int th, int32_t* best_idx,
+                                      int32_t* best_dist) {
+  Grid g;
+  g.build(kps_un, n, min_x, max_x, min_y, max_y);
+  std::vector<int> vIndices;
+  for (int i = 0; i < nq; i++) {
+    const float u = q_uv[2 * i], v = q_uv[2 * i + 1];
+    const int nPredictedLevel = q_level[i];
+    g.query(u, v, q_radius[i], -1, -1, vIndices);
+    int bestDist = 256, bestIdx = -1;
+    for (int idx : vIndices) {
+      if (taken && taken[idx]) continue;
+      const orb_oracle_keypoint& kp = kps_un[idx];
+      const int kpLevel = kp.octave;
+      if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+      if (inv_level_sigma2) {
+        const float ex = u - kp.x, ey = v - kp.y;
+        const float e2m = std::fma(ex, ex, ey * ey);
+        if (uright && uright[idx] >= 0) {
+          const float er = q_ur[i] - uright[idx];
+          const float e2 = std::fma(er, er, e2m);
+          if ((double)(e2 * inv_level_sigma2[kpLevel]) > 7.8) continue;
+        } else {
+          if ((double)(e2m * inv_level_sigma2[kpLevel]) > 5.99) continue;
+        }
+      }
+      const int dist = descriptor_distance(q_desc + (size_t)i * 32, desc + (size_t)idx * 32);
+      if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+    }
+    best_idx[i] = bestIdx;
+    best_dist[i] = bestDist;
+    if (taken && bestDist <= th) taken[bestIdx] = 1;
+  }
+}
+
+}  // extern "C"

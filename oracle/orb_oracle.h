@@ -136,6 +136,14 @@ int orb_oracle_search_for_triangulation(const orb_oracle_keypoint* kps1, const u
 /* MapPoint::ComputeDistinctiveDescriptors MapPoint.cpp:306-385, many points */
 void orb_oracle_distinctive(const uint8_t* desc, const int32_t* obs_off, int npoints, int32_t* best, int32_t* best_median);
 
+/* windowed best-match core of Fuse x2 / SearchByProjection(KeyFrame*, Scw) / SearchBySim3 (ORBmatcher.cpp:995-1296,
+ * :370-497, :1305-1547) after their projection prologues; see the definition */
+void orb_oracle_search_best_in_window(const orb_oracle_keypoint* kps_un, const uint8_t* desc, int n, const float* uright,
+                                      float min_x, float max_x, float min_y, float max_y, const float* inv_level_sigma2,
+                                      const float* q_uv, const float* q_ur, const float* q_radius, const int32_t* q_level,
+                                      const uint8_t* q_desc, int nq, uint8_t* taken, int th, int32_t* best_idx,
+                                      int32_t* best_dist);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,7 +11,9 @@
 // The harness builds real Frame and MapPoint objects, calls the reference's member functions and copies plain
 // arrays out. Nothing here re-implements the functions under test.
 #include <cstdint>
+#include <cmath>
 #include <cstring>
+#include <set>
 #include <vector>
 
 #include "Frame.h"
@@ -345,6 +347,109 @@ void ref_map_point_distinctive(void* h, int mp, uint8_t* out32) {
   p->ComputeDistinctiveDescriptors();
   cv::Mat d = p->GetDescriptor();
   std::memcpy(out32, d.ptr(0), 32);
+}
+
+// ---- Fuse / SearchByProjection(KeyFrame*, Scw, ...) ------------------------------------------------------------
+// The projection prologue those functions run per map point before their windowed search (R/src/ORBmatcher.cpp
+// :1019-1061 and :401-443): same Mat arithmetic, same MapPoint members (GetNormal, PredictScale, ...); the scalar
+// expressions carry the contractions of the reference's object code (u = fma(x, fx, cx), ur = fma(-bf, invz, u)).
+// Exported so that the test hands identical queries to the oracle and to the CUDA path.
+static bool window_query(KeyFrame* pKF, const cv::Mat& Rcw, const cv::Mat& tcw, const cv::Mat& Ow, MapPoint* pMP, float th,
+                         float* u, float* v, float* ur, float* radius, int* level) {
+  cv::Mat p3Dw = pMP->GetWorldPos();
+  cv::Mat p3Dc = Rcw * p3Dw + tcw;
+  if (p3Dc.at<float>(2) < 0.0f) return false;
+  const float invz = 1 / p3Dc.at<float>(2);
+  const float x = p3Dc.at<float>(0) * invz;
+  const float y = p3Dc.at<float>(1) * invz;
+  *u = __builtin_fmaf(x, pKF->fx, pKF->cx);
+  *v = __builtin_fmaf(y, pKF->fy, pKF->cy);
+  if (!pKF->IsInImage(*u, *v)) return false;
+  *ur = __builtin_fmaf(-pKF->mbf, invz, *u);
+  const float maxDistance = pMP->GetMaxDistanceInvariance();
+  const float minDistance = pMP->GetMinDistanceInvariance();
+  cv::Mat PO = p3Dw - Ow;
+  const float dist3D = cv::norm(PO);
+  if (dist3D < minDistance || dist3D > maxDistance) return false;
+  cv::Mat Pn = pMP->GetNormal();
+  if (PO.dot(Pn) < 0.5 * dist3D) return false;
+  *level = pMP->PredictScale(dist3D, pKF);
+  *radius = th * pKF->mvScaleFactors[*level];
+  return true;
+}
+
+// queries of Fuse(pKF, vpMapPoints, th) (:995-1160); valid[i] = 0 for points the loop skips (:1012-1061)
+void ref_fuse_queries(void* h, void* kfp, const int* mps, int nmp, float th, uint8_t* valid, float* uv, float* ur, float* radius,
+                      int* level, uint8_t* desc) {
+  Front* f = static_cast<Front*>(h);
+  KeyFrame* pKF = static_cast<KeyFrame*>(kfp);
+  cv::Mat Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation(), Ow = pKF->GetCameraCenter();
+  for (int i = 0; i < nmp; i++) {
+    MapPoint* pMP = f->points[mps[i]];
+    valid[i] = 0; uv[2 * i] = uv[2 * i + 1] = ur[i] = radius[i] = 0; level[i] = 0;
+    std::memcpy(desc + (size_t)i * 32, pMP->GetDescriptor().ptr(0), 32);
+    if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+    valid[i] = window_query(pKF, Rcw, tcw, Ow, pMP, th, &uv[2 * i], &uv[2 * i + 1], &ur[i], &radius[i], &level[i]);
+  }
+}
+int ref_fuse(void* h, void* kfp, const int* mps, int nmp, float th) {
+  Front* f = static_cast<Front*>(h);
+  std::vector<MapPoint*> v(nmp);
+  for (int i = 0; i < nmp; i++) v[i] = f->points[mps[i]];
+  ORBmatcher matcher(0.6f, true);
+  return matcher.Fuse(static_cast<KeyFrame*>(kfp), v, th);
+}
+void ref_keyframe_get_map_points(void* h, void* kfp, int* out) {
+  KeyFrame* kf = static_cast<KeyFrame*>(kfp);
+  for (int i = 0; i < kf->N; i++) out[i] = point_index(static_cast<Front*>(h), kf->GetMapPoint((size_t)i));
+}
+void ref_keyframe_inv_level_sigma2(void* kfp, float* out) {
+  KeyFrame& K = *static_cast<KeyFrame*>(kfp);
+  for (size_t i = 0; i < K.mvInvLevelSigma2.size(); i++) out[i] = K.mvInvLevelSigma2[i];
+}
+int ref_map_point_observations(void* h, int mp) { return static_cast<Front*>(h)->points[mp]->Observations(); }
+int ref_map_point_is_bad(void* h, int mp) { return static_cast<Front*>(h)->points[mp]->isBad() ? 1 : 0; }
+
+// SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:370-497). matched: pKF->N entries, map point index or -1,
+// read and updated like the reference's vpMatched.
+static void scw_parts(const float* Scw16, cv::Mat* Scw, cv::Mat* Rcw, cv::Mat* tcw, cv::Mat* Ow) {
+  *Scw = cv::Mat(4, 4, CV_32F);
+  for (int i = 0; i < 16; i++) Scw->at<float>(i / 4, i % 4) = Scw16[i];
+  cv::Mat sRcw = Scw->rowRange(0, 3).colRange(0, 3);
+  const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+  *Rcw = sRcw / scw;
+  *tcw = Scw->rowRange(0, 3).col(3) / scw;
+  *Ow = -Rcw->t() * *tcw;
+}
+void ref_scw_queries(void* h, void* kfp, const float* Scw16, const int* mps, int nmp, const int* matched, int th, uint8_t* valid,
+                     float* uv, float* radius, int* level, uint8_t* desc) {
+  Front* f = static_cast<Front*>(h);
+  KeyFrame* pKF = static_cast<KeyFrame*>(kfp);
+  cv::Mat Scw, Rcw, tcw, Ow;
+  scw_parts(Scw16, &Scw, &Rcw, &tcw, &Ow);
+  std::set<MapPoint*> spAlreadyFound;
+  for (int i = 0; i < pKF->N; i++) if (matched[i] >= 0) spAlreadyFound.insert(f->points[matched[i]]);
+  for (int i = 0; i < nmp; i++) {
+    MapPoint* pMP = f->points[mps[i]];
+    float ur;
+    valid[i] = 0; uv[2 * i] = uv[2 * i + 1] = radius[i] = 0; level[i] = 0;
+    std::memcpy(desc + (size_t)i * 32, pMP->GetDescriptor().ptr(0), 32);
+    if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+    valid[i] = window_query(pKF, Rcw, tcw, Ow, pMP, (float)th, &uv[2 * i], &uv[2 * i + 1], &ur, &radius[i], &level[i]);
+  }
+}
+int ref_search_by_projection_kf_scw(void* h, void* kfp, const float* Scw16, const int* mps, int nmp, int* matched, int th) {
+  Front* f = static_cast<Front*>(h);
+  KeyFrame* pKF = static_cast<KeyFrame*>(kfp);
+  cv::Mat Scw(4, 4, CV_32F);
+  for (int i = 0; i < 16; i++) Scw.at<float>(i / 4, i % 4) = Scw16[i];
+  std::vector<MapPoint*> pts(nmp), vm(pKF->N, static_cast<MapPoint*>(nullptr));
+  for (int i = 0; i < nmp; i++) pts[i] = f->points[mps[i]];
+  for (int i = 0; i < pKF->N; i++) if (matched[i] >= 0) vm[i] = f->points[matched[i]];
+  ORBmatcher matcher(0.75f, true);
+  const int n = matcher.SearchByProjection(pKF, Scw, pts, vm, th);
+  for (int i = 0; i < pKF->N; i++) matched[i] = point_index(f, vm[i]);
+  return n;
 }
 
 }  // extern "C"

@@ -127,4 +127,12 @@ int mirror_search_for_triangulation(orbx_matcher* m, const orbx_keypoint* k1, co
   return n == (int)v.size() ? n : -1000000;
 }
 
+void mirror_search_best_in_window(orbx_matcher* m, const orbx_keypoint* k, const unsigned char* d, int n, const float* uright,
+                                  const float* bounds, const float* invLevelSigma2, const float* qUV, const float* qUR,
+                                  const float* qRadius, const int* qLevel, const unsigned char* qDesc, int nQ,
+                                  unsigned char* taken, int th, int* bestIdx, int* bestDist) {
+  orbx_host::SearchBestInWindow(m, view(k, d, n, bounds, uright), invLevelSigma2, qUV, qUR, qRadius, qLevel, qDesc, nQ, taken, th,
+                                bestIdx, bestDist);
+}
+
 }  // extern "C"

@@ -406,4 +406,39 @@ int SearchForTriangulation(orbx_matcher* m, const BowView& KF1, const BowView& K
   return nmatches;
 }
 
+void SearchBestInWindow(orbx_matcher* m, const FrameView& KF, const float* invLevelSigma2, const float* qUV, const float* qUR,
+                        const float* qRadius, const int* qLevel, const unsigned char* qDesc, int nQ, unsigned char* taken,
+                        int th, int* bestIdx, int* bestDist) {
+  std::vector<float> qxy(qUV, qUV + 2 * (size_t)nQ), qr(qRadius, qRadius + nQ);
+  std::vector<int> qmin((size_t)nQ), qmax((size_t)nQ);
+  for (int i = 0; i < nQ; i++) { qmin[i] = qLevel[i] - 1; qmax[i] = qLevel[i]; }   // the octave test of the loops, done on the device
+  Candidates c;
+  WindowSearch(m, KF, qxy, qr, qmin, qmax, qDesc, nQ, &c);
+  for (int i = 0; i < nQ; i++) {
+    const float u = qUV[2 * i], v = qUV[2 * i + 1];
+    int best = 256, idxBest = -1;
+    for (int k = c.off[i]; k < c.off[i + 1]; k++) {
+      const int idx = c.idx[k];
+      if (taken && taken[idx]) continue;
+      if (invLevelSigma2) {
+        // fused like the reference's object code (-O3, -ffp-contract=fast), spelled out so that any build agrees
+        const orbx_keypoint& kp = KF.keysUn[idx];
+        const float ex = u - kp.x, ey = v - kp.y;
+        const float e2m = fmaf(ex, ex, ey * ey);
+        if (KF.uRight && KF.uRight[idx] >= 0) {
+          const float er = qUR[i] - KF.uRight[idx];
+          const float e2 = fmaf(er, er, e2m);
+          if (e2 * invLevelSigma2[kp.octave] > 7.8) continue;
+        } else {
+          if (e2m * invLevelSigma2[kp.octave] > 5.99) continue;
+        }
+      }
+      if (c.dist[k] < best) { best = c.dist[k]; idxBest = idx; }
+    }
+    bestIdx[i] = idxBest;
+    bestDist[i] = best;
+    if (taken && best <= th) taken[idxBest] = 1;
+  }
+}
+
 }  // namespace orbx_host

@@ -90,6 +90,19 @@ int SearchForTriangulation(orbx_matcher* m, const BowView& KF1, const BowView& K
                            const float* scaleFactors2, const float* levelSigma2_2, bool onlyStereo, bool checkOrientation,
                            std::vector<std::pair<int, int> >* vMatchedPairs);
 
+// ---- windowed best match (Fuse x2, SearchByProjection(KeyFrame*, Scw), SearchBySim3) --------
+// The loop those four functions share after their projection prologues (R/src/ORBmatcher.cpp:1046-1110, :1248-1270,
+// :441-470, :1379-1406 / :1459-1486): candidates = KeyFrame::GetFeaturesInArea(u, v, radius) (R/src/KeyFrame.cpp:702-743,
+// the Frame grid without a level argument) with octave in [level-1, level], best Hamming distance, first minimum wins.
+//   invLevelSigma2 != NULL: Fuse's chi-square gates (:1070-1099) on (u - kpx, v - kpy [, ur - mvuRight]) -- 5.99 / 7.8;
+//   taken != NULL: vpMatched of SearchByProjection(KeyFrame*, Scw, ...) (:453-454): skipped when set, set for the best
+//   keypoint of a query that ends with bestDist <= th (:479-483).
+// bestIdx[i] = keypoint or -1, bestDist[i] = its distance or 256. What the caller does with a hit (Replace /
+// AddObservation / vpReplacePoint / the mutual check of SearchBySim3 :1494-1508) is pointer-graph work and stays there.
+void SearchBestInWindow(orbx_matcher* m, const FrameView& KF, const float* invLevelSigma2, const float* qUV, const float* qUR,
+                        const float* qRadius, const int* qLevel, const unsigned char* qDesc, int nQ, unsigned char* taken,
+                        int th, int* bestIdx, int* bestDist);
+
 }  // namespace orbx_host
 
 #endif

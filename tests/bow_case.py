@@ -154,3 +154,50 @@ def build_observations(rf, n_kf=7, n_points=60):
             kfs[j].add_map_point((p * 11 + j * 37) % frames[j].N, mp)
         points.append(mp)
     return SimpleNamespace(front=front, frames=frames, kfs=kfs, points=points)
+
+
+T_FUSE = np.array([6 * 4.0 / FX, 3 * 4.0 / FY, 0.0], np.float32)   # points at depth 4 move by the image shift (6, 3)
+
+
+def build_fuse(rf, stereo):
+    """Key frame 1 with map points at depth 4 and a target key frame (the shifted view, pose T_FUSE) that owns map points
+    on three of four keypoints, observed only there: the input of Fuse(pKF, vpMapPoints, th) and of
+    SearchByProjection(pKF, Scw, vpPoints, vpMatched, th)."""
+    front = rf.Front(NFEAT, fx=FX, fy=FY, cx=CX, cy=CY, bf=BF)
+    im1, im2 = images(stereo)
+    mk = front.frame_stereo if stereo else front.frame_mono
+    f1, f2 = mk(*im1), mk(*im2)
+    f1.set_pose(pose(np.zeros(3, np.float32)))
+    f2.set_pose(pose(T_FUSE))
+    kf1, kf2 = front.keyframe(f1), front.keyframe(f2)
+    p1, p2 = backproject(f1.keys_un, np.zeros(3, np.float32)), backproject(f2.keys_un, T_FUSE)
+    src = np.array([front.map_point(f1, int(i), p1[i]) for i in range(0, f1.N, 2)], np.int32)
+    for k, i in enumerate(range(0, f1.N, 2)):
+        kf1.add_map_point(int(i), int(src[k]))
+    mp_of2 = np.full(f2.N, -1, np.int32)
+    for i in range(f2.N):
+        if i % 4:
+            mp_of2[i] = front.map_point(f2, int(i), p2[i], n_obs=(3 if i % 8 < 4 else 0))
+            kf2.add_map_point(int(i), int(mp_of2[i]))
+    return SimpleNamespace(front=front, f1=f1, f2=f2, kf1=kf1, kf2=kf2, src=src, mp_of2=mp_of2)
+
+
+def simulate_fuse(state, obs, src, valid, best_idx, best_dist, stereo_slot, th_low=50):
+    """What Fuse does with the search results (R/src/ORBmatcher.cpp:1112-1136), on index arrays: state[idx] = map point
+    owning keypoint idx of the target key frame, obs[mp] = Observations(). Returns nFused."""
+    n = 0
+    for i in np.nonzero(valid)[0]:
+        if best_dist[i] > th_low:
+            continue
+        b, mp = int(best_idx[i]), int(src[i])
+        if state[b] >= 0:
+            if obs[state[b]] > obs[mp]:
+                pass                      # pMP->Replace(pMPinKF): the key frame keeps its point
+            else:                         # pMPinKF->Replace(pMP): its single observation (this slot) moves to pMP
+                obs[mp] += 2 if stereo_slot[b] else 1
+                state[b] = mp
+        else:
+            obs[mp] += 2 if stereo_slot[b] else 1
+            state[b] = mp
+        n += 1
+    return n

@@ -89,6 +89,8 @@ def lib():
                                                           I, I, V]
         L.orb_oracle_distinctive.argtypes = [V, V, I, V, V]
         L.orb_oracle_distinctive.restype = None
+        L.orb_oracle_search_best_in_window.argtypes = [V, V, I, V, F, F, F, F, V, V, V, V, V, V, I, V, I, V, V]
+        L.orb_oracle_search_best_in_window.restype = None
     return _lib
 
 
@@ -410,3 +412,23 @@ def distinctive(desc, obs_off):
     best, med = np.empty(max(npoints, 1), np.int32), np.empty(max(npoints, 1), np.int32)
     lib().orb_oracle_distinctive(_ptr(desc), _ptr(obs_off), npoints, _ptr(best), _ptr(med))
     return best[:npoints], med[:npoints]
+
+
+def search_best_in_window(kps_un, desc, uright, bounds, inv_level_sigma2, q_uv, q_ur, q_radius, q_level, q_desc, taken, th):
+    """Windowed best-match core of Fuse x2 / SearchByProjection(KeyFrame*, Scw) / SearchBySim3. `taken` (uint8 array or
+    None) is updated in place. Returns (best_idx, best_dist)."""
+    kps_un = np.ascontiguousarray(kps_un)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+    ils = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+    q_uv = np.ascontiguousarray(q_uv, np.float32).reshape(-1, 2)
+    nq = len(q_uv)
+    q_ur = np.zeros(nq, np.float32) if q_ur is None else np.ascontiguousarray(q_ur, np.float32)
+    q_radius, q_level = np.ascontiguousarray(q_radius, np.float32), np.ascontiguousarray(q_level, np.int32)
+    q_desc = np.ascontiguousarray(q_desc, np.uint8)
+    assert taken is None or (taken.dtype == np.uint8 and taken.flags.c_contiguous and len(taken) == len(kps_un))
+    bi, bd = np.empty(max(nq, 1), np.int32), np.empty(max(nq, 1), np.int32)
+    lib().orb_oracle_search_best_in_window(_ptr(kps_un), _ptr(desc), len(kps_un), _opt(ur), *[float(b) for b in bounds], _opt(ils),
+                                           _ptr(q_uv), _ptr(q_ur), _ptr(q_radius), _ptr(q_level), _ptr(q_desc), nq,
+                                           _opt(taken), th, _ptr(bi), _ptr(bd))
+    return bi[:nq], bd[:nq]

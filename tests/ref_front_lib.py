@@ -64,6 +64,14 @@ def lib():
         L.ref_keyframe_tables.argtypes = [P, P, P]
         L.ref_map_point_observed_rows.argtypes = [P, C.c_int, P, C.c_int]
         L.ref_map_point_distinctive.argtypes = [P, C.c_int, P]
+        L.ref_fuse_queries.argtypes = [P, P, P, C.c_int, C.c_float] + [P] * 6
+        L.ref_fuse.argtypes = [P, P, P, C.c_int, C.c_float]
+        L.ref_keyframe_get_map_points.argtypes = [P, P, P]
+        L.ref_keyframe_inv_level_sigma2.argtypes = [P, P]
+        L.ref_map_point_observations.argtypes = [P, C.c_int]
+        L.ref_map_point_is_bad.argtypes = [P, C.c_int]
+        L.ref_scw_queries.argtypes = [P, P, P, P, C.c_int, P, C.c_int] + [P] * 5
+        L.ref_search_by_projection_kf_scw.argtypes = [P, P, P, P, C.c_int, P, C.c_int]
         L.ref_set_allocator_mode(1)   # pointer order == creation order: the canonical DistributeOctTree tie-break
         _lib = L
     return _lib
@@ -135,6 +143,16 @@ class KeyFrame:
         sf, ls = np.empty(self.front.nlevels, np.float32), np.empty(self.front.nlevels, np.float32)
         lib().ref_keyframe_tables(self._h, _p(sf), _p(ls))
         return sf, ls
+
+    def inv_level_sigma2(self):
+        out = np.empty(self.front.nlevels, np.float32)
+        lib().ref_keyframe_inv_level_sigma2(self._h, _p(out))
+        return out
+
+    def map_points(self):
+        out = np.empty(max(self.N, 1), np.int32)
+        lib().ref_keyframe_get_map_points(self.front._h, self._h, _p(out))
+        return out[:self.N]
 
 
 class Front:
@@ -234,3 +252,38 @@ class Front:
         out = np.empty(32, np.uint8)
         lib().ref_map_point_distinctive(self._h, mp, _p(out))
         return out
+
+    # ---- Fuse / SearchByProjection(KeyFrame*, Scw, ...) ----
+    def fuse_queries(self, kf, mps, th):
+        mps = np.ascontiguousarray(mps, np.int32)
+        n = len(mps)
+        valid, uv, ur, radius = np.empty(n, np.uint8), np.empty((n, 2), np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+        level, desc = np.empty(n, np.int32), np.empty((n, 32), np.uint8)
+        lib().ref_fuse_queries(self._h, kf._h, _p(mps), n, th, _p(valid), _p(uv), _p(ur), _p(radius), _p(level), _p(desc))
+        return valid.astype(bool), uv, ur, radius, level, desc
+
+    def fuse(self, kf, mps, th):
+        mps = np.ascontiguousarray(mps, np.int32)
+        return lib().ref_fuse(self._h, kf._h, _p(mps), len(mps), th)
+
+    def observations(self, mp):
+        return lib().ref_map_point_observations(self._h, int(mp))
+
+    def is_bad(self, mp):
+        return bool(lib().ref_map_point_is_bad(self._h, int(mp)))
+
+    def scw_queries(self, kf, Scw, mps, matched, th):
+        mps, matched = np.ascontiguousarray(mps, np.int32), np.ascontiguousarray(matched, np.int32)
+        S = np.ascontiguousarray(Scw, np.float32).reshape(16)
+        n = len(mps)
+        valid, uv, radius = np.empty(n, np.uint8), np.empty((n, 2), np.float32), np.empty(n, np.float32)
+        level, desc = np.empty(n, np.int32), np.empty((n, 32), np.uint8)
+        lib().ref_scw_queries(self._h, kf._h, _p(S), _p(mps), n, _p(matched), th, _p(valid), _p(uv), _p(radius), _p(level), _p(desc))
+        return valid.astype(bool), uv, radius, level, desc
+
+    def search_by_projection_kf_scw(self, kf, Scw, mps, matched, th):
+        mps = np.ascontiguousarray(mps, np.int32)
+        out = np.ascontiguousarray(matched, np.int32).copy()
+        S = np.ascontiguousarray(Scw, np.float32).reshape(16)
+        n = lib().ref_search_by_projection_kf_scw(self._h, kf._h, _p(S), _p(mps), len(mps), _p(out), th)
+        return n, out

@@ -24,6 +24,8 @@ def mirror():
     L.mirror_search_by_bow_kf_frame.argtypes = [P, P, P, I, P, P, P, I, P, P, P, I, P, P, P, I, F, I, P]
     L.mirror_search_by_bow_kf_kf.argtypes = [P, P, P, I, P, P, P, I, P, P, P, I, P, P, P, I, P, F, I, P]
     L.mirror_search_for_triangulation.argtypes = [P, P, P, I, P, P, P, I, P, P, P, P, I, P, P, P, I, P, P, P, F, F, P, P, I, I, P]
+    L.mirror_search_best_in_window.argtypes = [P, P, P, I, P, P, P, P, P, P, P, P, I, P, I, P, P]
+    L.mirror_search_best_in_window.restype = None
     return L
 
 
@@ -169,3 +171,66 @@ def test_search_for_triangulation(pkg, oracle, mirror, case, only_stereo, check_
     if c.front is not None:
         rn, rpairs = c.front.search_for_triangulation(c.kf1, kf2, c.F12, bool(only_stereo), 0.6, bool(check_ori))
         assert rn == gn and np.array_equal(rpairs, pairs[:gn])
+
+
+def _best_in_window(mirror, m, f, inv_sigma2, uv, ur, radius, level, desc, taken, th):
+    nq = len(radius)
+    bi, bd = np.empty(max(nq, 1), np.int32), np.empty(max(nq, 1), np.int32)
+    uv, radius, level, desc = (np.ascontiguousarray(a) for a in (uv, radius, level, desc))
+    ur = np.zeros(nq, np.float32) if ur is None else np.ascontiguousarray(ur)
+    mirror.mirror_search_best_in_window(m._h, _p(f.keys_un), _p(f.desc), f.N, _p(f.u_right), _p(f.bounds), _p(inv_sigma2), _p(uv),
+                                        _p(ur), _p(radius), _p(level), _p(desc), nq, None if taken is None else taken.ctypes.data_as(P),
+                                        th, _p(bi), _p(bd))
+    return bi[:nq], bd[:nq]
+
+
+@pytest.mark.parametrize("stereo", [False, True])
+@pytest.mark.parametrize("th", [3.0, 8.0])
+def test_fuse(pkg, oracle, mirror, stereo, th):
+    """Fuse(pKF, vpMapPoints, th) (R/src/ORBmatcher.cpp:995-1160): device candidates + distances, host gates and best
+    match; against the oracle and against the reference's Fuse run on the real key frame."""
+    if not rf.available():
+        pytest.skip("oracle/_ref/libref_front.so not built (the projection prologue comes from the reference objects)")
+    c = bow_case.build_fuse(rf, stereo)
+    m = pkg.ORBmatcher(0.6)
+    valid, uv, ur, radius, level, desc = c.front.fuse_queries(c.kf2, c.src, th)
+    ils = c.kf2.inv_level_sigma2()
+    gi, gd = _best_in_window(mirror, m, c.f2, ils, uv[valid], ur[valid], radius[valid], level[valid], desc[valid], None, 50)
+    ei, ed = oracle.search_best_in_window(c.f2.keys_un, c.f2.desc, c.f2.u_right, c.f2.bounds, ils, uv[valid], ur[valid],
+                                          radius[valid], level[valid], desc[valid], None, 50)
+    assert np.array_equal(gi, ei) and np.array_equal(gd, ed)
+    best_idx, best_dist = np.full(len(c.src), -1, np.int32), np.full(len(c.src), 256, np.int32)
+    best_idx[valid], best_dist[valid] = gi, gd
+    n_points = int(max(c.src.max(), c.mp_of2.max())) + 1
+    obs = np.array([c.front.observations(k) for k in range(n_points)])
+    state = c.mp_of2.copy()
+    gn = bow_case.simulate_fuse(state, obs, c.src, valid, best_idx, best_dist, c.f2.u_right >= 0)
+    rn = c.front.fuse(c.kf2, c.src, th)
+    assert rn == gn and rn > (20 if stereo else 300)
+    assert np.array_equal(c.kf2.map_points(), state)
+
+
+@pytest.mark.parametrize("stereo", [False, True])
+def test_search_by_projection_keyframe_scw(pkg, oracle, mirror, stereo):
+    """SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (R/src/ORBmatcher.cpp:370-497): no gates, vpMatched as the
+    `taken` flags; the same core serves Fuse(pKF, Scw, ...) (:1164-1296) and SearchBySim3 (:1305-1547)."""
+    if not rf.available():
+        pytest.skip("oracle/_ref/libref_front.so not built")
+    c = bow_case.build_fuse(rf, stereo)
+    m = pkg.ORBmatcher(0.75)
+    th = 10
+    Scw = bow_case.pose(bow_case.T_FUSE)
+    Scw[:3, :] *= np.float32(1.25)
+    matched = np.full(c.f2.N, -1, np.int32)
+    matched[5::9] = c.src[np.arange(len(matched[5::9])) % len(c.src)]
+    valid, uv, radius, level, desc = c.front.scw_queries(c.kf2, Scw, c.src, matched, th)
+    tg, te = ((matched >= 0).astype(np.uint8) for _ in range(2))
+    gi, gd = _best_in_window(mirror, m, c.f2, None, uv[valid], None, radius[valid], level[valid], desc[valid], tg, 50)
+    ei, ed = oracle.search_best_in_window(c.f2.keys_un, c.f2.desc, None, c.f2.bounds, None, uv[valid], None, radius[valid],
+                                          level[valid], desc[valid], te, 50)
+    assert np.array_equal(gi, ei) and np.array_equal(gd, ed) and np.array_equal(tg, te)
+    expect = matched.copy()
+    hit = gd <= 50
+    expect[gi[hit]] = c.src[valid][hit]
+    rn, rmatched = c.front.search_by_projection_kf_scw(c.kf2, Scw, c.src, matched, th)
+    assert rn == int(hit.sum()) and rn > 200 and np.array_equal(rmatched, expect)

@@ -95,3 +95,48 @@ def test_compute_distinctive_descriptors_vs_reference():
         d = np.unpackbits(r[:, None, :] ^ r[None, :, :], axis=2).sum(2)
         m = np.sort(d, axis=1)[:, int(0.5 * (len(r) - 1))]
         assert med[k] == m.min() and best[k] == int(np.argmin(m))
+
+
+@pytest.mark.parametrize("stereo", [False, True])
+@pytest.mark.parametrize("th", [3.0, 8.0])
+def test_fuse_vs_reference(stereo, th):
+    """Fuse(pKF, vpMapPoints, th): the oracle's windowed best-match core on the reference's own projection prologue, then
+    the reference's bookkeeping rule on index arrays, must leave the key frame with the same map points as the reference's
+    Fuse run on the real objects."""
+    c = bow_case.build_fuse(rf, stereo)
+    valid, uv, ur, radius, level, desc = c.front.fuse_queries(c.kf2, c.src, th)
+    bi, bd = ol.search_best_in_window(c.f2.keys_un, c.f2.desc, c.f2.u_right, c.f2.bounds, c.kf2.inv_level_sigma2(), uv[valid],
+                                      ur[valid], radius[valid], level[valid], desc[valid], None, 50)
+    best_idx, best_dist = np.full(len(c.src), -1, np.int32), np.full(len(c.src), 256, np.int32)
+    best_idx[valid], best_dist[valid] = bi, bd
+    n_points = int(max(c.src.max(), c.mp_of2.max())) + 1
+    obs = np.array([c.front.observations(k) for k in range(n_points)])
+    state = c.mp_of2.copy()
+    en = bow_case.simulate_fuse(state, obs, c.src, valid, best_idx, best_dist, c.f2.u_right >= 0)
+    rn = c.front.fuse(c.kf2, c.src, th)
+    assert valid.sum() > 500 and rn > (20 if stereo else 300)
+    assert rn == en
+    assert np.array_equal(c.kf2.map_points(), state)
+    replaced = (state != c.mp_of2) & (c.mp_of2 >= 0)
+    assert replaced.any() and ((state == c.mp_of2) & (c.mp_of2 >= 0)).any() and ((c.mp_of2 < 0) & (state >= 0)).any()
+
+
+@pytest.mark.parametrize("stereo", [False, True])
+@pytest.mark.parametrize("th", [4, 10])
+def test_search_by_projection_keyframe_scw_vs_reference(stereo, th):
+    c = bow_case.build_fuse(rf, stereo)
+    Scw = bow_case.pose(bow_case.T_FUSE) * np.float32(1.0)
+    Scw[:3, :] *= np.float32(1.25)    # a similarity: the function divides the scale out again (:378-382)
+    matched = np.full(c.f2.N, -1, np.int32)
+    matched[5::9] = c.src[np.arange(len(matched[5::9])) % len(c.src)]   # keypoints loop closing has matched already
+    valid, uv, radius, level, desc = c.front.scw_queries(c.kf2, Scw, c.src, matched, th)
+    taken = (matched >= 0).astype(np.uint8)
+    bi, bd = ol.search_best_in_window(c.f2.keys_un, c.f2.desc, None, c.f2.bounds, None, uv[valid], None, radius[valid],
+                                      level[valid], desc[valid], taken, 50)
+    expect = matched.copy()
+    hit = bd <= 50
+    expect[bi[hit]] = c.src[valid][hit]
+    rn, rmatched = c.front.search_by_projection_kf_scw(c.kf2, Scw, c.src, matched, th)
+    assert rn == int(hit.sum()) and rn > 200
+    assert np.array_equal(rmatched, expect)
+    assert (~valid).sum() >= (matched >= 0).sum() - 5    # the already-found points were skipped
