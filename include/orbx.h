@@ -99,6 +99,16 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
                        int32_t height, size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap,
                        int32_t* n);
 
+/* Streaming form of orbx_extract_batch for continuous sequences: returns once the chunks are enqueued, so that the
+ * next submission's host->device copies overlap this one's kernels and device->host copies (a synchronous call pays
+ * one chunk of pipeline fill and one of drain). kps / desc / n must be page-locked (orbx_host_alloc) and, like the
+ * frames, stay untouched until orbx_extract_batch_wait(h, *ticket) returns; up to 8 submissions may be in flight,
+ * and they complete in order. Results and error conditions are those of orbx_extract_batch, reported by the wait. */
+int orbx_extract_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width,
+                              int32_t height, size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap,
+                              int32_t* n, int32_t* ticket);
+int orbx_extract_batch_wait(orbx_extractor* h, int32_t ticket);
+
 /* Same, frames and outputs resident in device memory; asynchronous on `stream`.
  * Frame f starts at d_imgs + f*frame_stride. d_n[f] may exceed cap: rows beyond cap are dropped. */
 int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_imgs, int32_t count, int32_t width,

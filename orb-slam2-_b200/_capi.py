@@ -42,6 +42,8 @@ SIGNATURES = {
     "orbx_extractor_set_pipeline": (C.c_int, [_vp, _i32, _i32]),
     "orbx_extract": (C.c_int, [_vp, _vp, _i32, _i32, _sz, _vp, _vp, _i32, C.POINTER(_i32)]),
     "orbx_extract_batch": (C.c_int, [_vp, C.POINTER(_vp), _i32, _i32, _i32, _sz, _vp, _vp, _i32, _vp]),
+    "orbx_extract_batch_submit": (C.c_int, [_vp, C.POINTER(_vp), _i32, _i32, _i32, _sz, _vp, _vp, _i32, _vp, C.POINTER(_i32)]),
+    "orbx_extract_batch_wait": (C.c_int, [_vp, _i32]),
     "orbx_extract_batch_device": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _sz, _sz, _vp, _vp, _i32, _vp, _vp]),
     "orbx_level_size": (C.c_int, [_vp, _i32, C.POINTER(_i32), C.POINTER(_i32)]),
     "orbx_get_level": (C.c_int, [_vp, _i32, _i32, _vp, _sz]),

@@ -302,7 +302,7 @@ bool is_pinned(const void* p, size_t bytes) {
 }
 
 int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int count, int width, int height, size_t stride,
-                 const HostOut& out) {
+                 const HostOut& out, int* nOut = nullptr, int* overflowOut = nullptr) {
   const FrameSetGeom& g = L.geom;
   cudaStream_t s = L.stream;
   uint8_t* l0 = static_cast<uint8_t*>(L.pyrArena.p);  // level-0 slot of the arena (planeOff 0)
@@ -341,8 +341,10 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
   g_trace.mark(2, s);
   HostStage st = stage_of(L);
   const int* dOverflow = static_cast<const int*>(L.counts.p) + 2 * L.batchCap * g.nlevels;
-  ORBX_CUDA_TRY(cudaMemcpyAsync(st.n, dN, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
-  ORBX_CUDA_TRY(cudaMemcpyAsync(st.overflow, dOverflow, sizeof(int), cudaMemcpyDeviceToHost, s));
+  // streaming submissions hand in pinned destinations of their own: the lane's staging may be rewritten by the next
+  // chunk on this lane before anybody has looked at it
+  ORBX_CUDA_TRY(cudaMemcpyAsync(nOut ? nOut : st.n, dN, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(overflowOut ? overflowOut : st.overflow, dOverflow, sizeof(int), cudaMemcpyDeviceToHost, s));
   if (out.direct) {
     // one "row" per frame: the first min(rows, cap) keypoints; entries past n[f] are unspecified
     const size_t take = (size_t)std::min(rows, out.cap);
@@ -452,6 +454,10 @@ void orbx_extractor_destroy(orbx_extractor* h) {
   cudaSetDevice(h->params.device);
   for (Lane& L : h->lane) L.release();
   h->tapArena.release();
+  for (auto& t : h->tickets) {
+    for (cudaEvent_t& e : t.done) if (e) cudaEventDestroy(e);
+    if (t.overflow) cudaFreeHost(t.overflow);
+  }
   delete h;
 }
 
@@ -538,6 +544,76 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
   g_trace.dump();
   if (nchunks > 1) h->haveResult = false;  // introspection only covers single-chunk batches
   if (tooSmall) { set_error("keypoint capacity %d too small (see n[])", cap); return ORBX_ERR_CAPACITY; }
+  return ORBX_OK;
+}
+
+int orbx_extract_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width, int32_t height,
+                              size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n, int32_t* ticket) {
+  if (!h || !imgs || !kps || !desc || !n || !ticket || cap <= 0 || count <= 0) { set_error("null/invalid argument"); return ORBX_ERR_ARG; }
+  if (stride < (size_t)width) { set_error("stride %zu < width %d", stride, width); return ORBX_ERR_ARG; }
+  if (count > h->params.max_batch) {
+    set_error("batch of %d frames exceeds the handle's max_batch %d", count, h->params.max_batch);
+    return ORBX_ERR_ARG;
+  }
+  ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
+  if (!is_pinned(kps, (size_t)count * cap * sizeof(orbx_keypoint)) || !is_pinned(desc, (size_t)count * cap * 32) ||
+      !is_pinned(n, (size_t)count * sizeof(int32_t))) {
+    set_error("streaming submissions need page-locked result arrays (orbx_host_alloc): kps, desc and n");
+    return ORBX_ERR_ARG;
+  }
+  ChunkPlan plan;
+  // without fill and drain to pay per call, larger chunks win: they fill the GPU better (tools/stream_probe.py:
+  // 128 frames x 4 lanes 167.7 k frames/s, 64 x 4 143 k, 256 x 3 167.7 k at 640x480)
+  if (!plan_chunks(count, h->chunkFrames > 0 ? h->chunkFrames : 2 * chunk_frames(width, height), &plan) ||
+      plan.n > orbx_extractor::kTicketChunks) {
+    set_error("batch of %d frames needs more than %d chunks (raise the chunk size)", count, orbx_extractor::kTicketChunks);
+    return ORBX_ERR_ARG;
+  }
+  orbx_extractor::Ticket& t = h->tickets[h->nextTicket % orbx_extractor::kTickets];
+  if (t.open) { set_error("%d submissions in flight: wait for ticket %d first", orbx_extractor::kTickets, t.id); return ORBX_ERR_STATE; }
+  const int nlanes = h->laneCount > 0 ? h->laneCount : lane_count();
+  int rc;
+  for (int i = 0; i < nlanes; i++) {
+    // a change of shape or capacity synchronises the lane before its arenas are rebuilt (ensure_lane)
+    if ((rc = ensure_lane(h, h->lane[i], width, height, plan.largest))) return rc;
+    if ((rc = ensure_lane_staging(h->lane[i]))) return rc;
+  }
+  if (!t.overflow) ORBX_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&t.overflow), orbx_extractor::kTicketChunks * sizeof(int), cudaHostAllocPortable));
+  for (int i = 0; i < nlanes; i++)
+    if (!t.done[i]) ORBX_CUDA_TRY(cudaEventCreateWithFlags(&t.done[i], cudaEventDisableTiming));
+  for (int c = 0; c < plan.n; c++) t.overflow[c] = 0;
+  bool used[kMaxLanes] = {};
+  for (int c = 0; c < plan.n; c++) {
+    const int f0 = plan.first[c], cnt = plan.count[c];
+    const int li = (int)(h->laneRotor++ % (unsigned)nlanes);
+    const HostOut out{kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, true};
+    if ((rc = submit_chunk(h, h->lane[li], imgs + f0, cnt, width, height, stride, out, n + f0, t.overflow + c))) return rc;
+    used[li] = true;
+  }
+  t.lanesUsed = 0;
+  for (int i = 0; i < nlanes; i++)
+    if (used[i]) { ORBX_CUDA_TRY(cudaEventRecord(t.done[i], h->lane[i].stream)); t.lanesUsed |= 1 << i; }
+  t.open = true; t.id = h->nextTicket++; t.chunks = plan.n; t.cap = cap; t.count = count; t.n = n;
+  h->haveResult = false;  // introspection covers synchronous single-chunk calls only
+  *ticket = t.id;
+  return ORBX_OK;
+}
+
+int orbx_extract_batch_wait(orbx_extractor* h, int32_t ticket) {
+  if (!h) { set_error("null handle"); return ORBX_ERR_ARG; }
+  ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
+  orbx_extractor::Ticket& t = h->tickets[((ticket % orbx_extractor::kTickets) + orbx_extractor::kTickets) % orbx_extractor::kTickets];
+  if (!t.open || t.id != ticket) { set_error("ticket %d is not in flight", ticket); return ORBX_ERR_STATE; }
+  for (int i = 0; i < kMaxLanes; i++)
+    if (t.lanesUsed >> i & 1) ORBX_CUDA_TRY(cudaEventSynchronize(t.done[i]));
+  t.open = false;
+  for (int c = 0; c < t.chunks; c++)
+    if (t.overflow[c]) {
+      set_error("FAST candidate list overflowed its capacity (corner density above 1 per 8 pixels)");
+      return ORBX_ERR_CAPACITY;
+    }
+  for (int f = 0; f < t.count; f++)
+    if (t.n[f] > t.cap) { set_error("keypoint capacity %d too small (see n[])", t.cap); return ORBX_ERR_CAPACITY; }
   return ORBX_OK;
 }
 

@@ -80,4 +80,18 @@ struct orbx_extractor {
   long long lastL0FrameStride = 0;
   int lastL0Pitch = 0;
   bool haveResult = false;
+
+  // streaming submissions (orbx_extract_batch_submit / _wait): a ring of tickets, each with one event per lane it
+  // touched, the result ranges to validate at wait time and pinned overflow words the chunks copy into
+  static constexpr int kTickets = 8, kTicketChunks = 64;
+  struct Ticket {
+    bool open = false;
+    int id = 0, lanesUsed = 0, chunks = 0, cap = 0, count = 0;
+    const int* n = nullptr;
+    cudaEvent_t done[orbx::kMaxLanes] = {};
+    int* overflow = nullptr;   // pinned, kTicketChunks words
+  };
+  Ticket tickets[kTickets];
+  int nextTicket = 1;
+  unsigned laneRotor = 0;
 };

@@ -113,6 +113,24 @@ class ORBextractor:
         check(lib().orbx_extract_batch(self._h, C.cast(ptr(ptrs), C.POINTER(C.c_void_p)), cnt, w, h, frames.strides[1],
                                        ptr(kps), ptr(desc), cap, ptr(n)))
 
+    def extract_batch_submit(self, frames, kps, desc, n):
+        """orbx_extract_batch_submit: the streaming form of extract_batch_into. All four arrays must be page-locked
+        (pinned_empty) and stay untouched until extract_batch_wait(ticket). Returns the ticket."""
+        if frames.dtype != np.uint8 or frames.ndim != 3 or frames.strides[2] != 1:
+            raise TypeError("frames must be a (B, H, W) uint8 array with contiguous rows")
+        cnt, h, w = frames.shape
+        cap = kps.shape[1]
+        if kps.dtype != KP_DTYPE or kps.shape[0] < cnt or desc.shape[:2] != kps.shape[:2] or n.shape[0] < cnt or n.dtype != np.int32:
+            raise TypeError("output arrays do not match the batch")
+        ptrs = frames.ctypes.data + frames.strides[0] * np.arange(cnt, dtype=np.int64)
+        ticket = C.c_int32(0)
+        check(lib().orbx_extract_batch_submit(self._h, C.cast(ptr(ptrs), C.POINTER(C.c_void_p)), cnt, w, h, frames.strides[1],
+                                              ptr(kps), ptr(desc), cap, ptr(n), C.byref(ticket)))
+        return ticket.value
+
+    def extract_batch_wait(self, ticket):
+        check(lib().orbx_extract_batch_wait(self._h, ticket))
+
     def extract_batch_device(self, d_imgs_ptr, count, width, height, row_stride, frame_stride, d_kps_ptr,
                              d_desc_ptr, cap, d_n_ptr, stream=0):
         """Device-resident batch (raw device pointers, e.g. torch tensors' data_ptr()); asynchronous."""

@@ -236,6 +236,49 @@ def test_pinned_outputs_take_rows_directly(pkg, cap):
             assert np.array_equal(pd[f, :m], rd[f, :m]), f
 
 
+def test_streaming_submissions_equal_synchronous_batch(pkg):
+    """orbx_extract_batch_submit / _wait: three submissions in flight on the same handle (lanes keep rotating across
+    submissions), waited for out of submission order, must give what the synchronous call gives; pageable result
+    arrays, a stale ticket and a too-small capacity are refused."""
+    B, S = 40, 3
+    frames = [pkg.pinned_empty((B, 240, 320), np.uint8) for _ in range(S)]
+    for s in range(S):
+        for i in range(B):
+            frames[s][i] = pkg.synth.frame(320, 240, 500 + 100 * s + i)
+    ex = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240, max_batch=64)
+    ex.set_pipeline(chunk_frames=8, lanes=3)   # 5 chunks per submission over 3 lanes
+    cap = 700
+    ref = []
+    for s in range(S):
+        rk, rd, rn = np.empty((B, cap), pkg.KP_DTYPE), np.empty((B, cap, 32), np.uint8), np.zeros(B, np.int32)
+        ex.extract_batch_into(frames[s], rk, rd, rn)
+        ref.append((rk, rd, rn))
+    outs = [(pkg.pinned_empty((B, cap), pkg.KP_DTYPE), pkg.pinned_empty((B, cap, 32), np.uint8), pkg.pinned_empty(B, np.int32))
+            for _ in range(S)]
+    for rounds in range(2):   # the second round reuses tickets' ring slots and the lanes' arenas
+        for o in outs:
+            o[2][:] = -1
+        tickets = [ex.extract_batch_submit(frames[s], *outs[s]) for s in range(S)]
+        for s in (2, 0, 1):
+            ex.extract_batch_wait(tickets[s])
+        for s in range(S):
+            rk, rd, rn = ref[s]
+            gk, gd, gn = outs[s]
+            assert np.array_equal(gn, rn)
+            for f in range(B):
+                assert np.array_equal(gk[f, :rn[f]].view(np.uint8), rk[f, :rn[f]].view(np.uint8)), (s, f)
+                assert np.array_equal(gd[f, :rn[f]], rd[f, :rn[f]]), (s, f)
+    with pytest.raises(pkg.OrbxError):
+        ex.extract_batch_wait(tickets[0])          # already collected
+    with pytest.raises(pkg.OrbxError):               # pageable results cannot take asynchronous copies
+        ex.extract_batch_submit(frames[0], np.empty((B, cap), pkg.KP_DTYPE), np.empty((B, cap, 32), np.uint8), np.zeros(B, np.int32))
+    small = (pkg.pinned_empty((B, 300), pkg.KP_DTYPE), pkg.pinned_empty((B, 300, 32), np.uint8), pkg.pinned_empty(B, np.int32))
+    t = ex.extract_batch_submit(frames[0], *small)
+    with pytest.raises(pkg.OrbxError):
+        ex.extract_batch_wait(t)
+    assert np.array_equal(small[2], ref[0][2])       # n is still reported
+
+
 @pytest.mark.parametrize("w,h", [(321, 240), (1241, 376)])
 def test_odd_width_batch_equals_single(pkg, w, h):
     """Tightly packed frames whose width is not a multiple of the arena pitch cross PCIe flat and are re-pitched on the
