@@ -8,7 +8,12 @@
 //    (u inside the disc, else 0 / 1 inside the disc, else 0) kept in shared memory:
 //    m10 += dot(px, u), m01 += v * dot(px, 1). Exact int32, reduced by shuffles;
 //    angle = cv::fastAtan2 (orbx_math.cuh).
-//  * Descriptor on the BLURRED level: lane b produces byte b (16 samples). The pattern sits in
+//  * Descriptor on the BLURRED level: the 39x39 neighbourhood the rotated pattern can reach (|x|,|y| <= 13 =>
+//    radius <= 18.4) is first staged into shared memory with coalesced 8-byte loads -- 5 rows x 6 vectors per
+//    warp instruction, 8 instructions per keypoint -- and the 512 samples are gathered from there. Gathering them
+//    from global memory made the kernel L1-bound (ncu r1_x: l1tex 86 %, every warp-wide byte gather touches up
+//    to 32 sectors); from shared memory a gather costs its bank conflicts only.
+//    Lane b produces byte b (16 samples). The pattern sits in
 //    shared memory as float4 (x0,y0,x1,y1) per (bit, lane) -- conflict-free LDS.128 instead of
 //    the 32-way divergent constant loads of v1. Rotation uses glibc-exact sincosf and the fused forms
 //    the reference's -O3 -march=native build emits: row = fma(x,b,y*a), col = fma(x,a,-(y*b));
@@ -28,6 +33,12 @@ __constant__ int cUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9,
 constexpr int kDescWarps = 8;
 constexpr int kDescKpPerWarp = 4;
 constexpr int kDescKpPerCta = kDescWarps * kDescKpPerWarp;
+constexpr int kPatchR = 19;                      // EDGE_THRESHOLD: reach of the rotated pattern (R/src/ORBextractor.cpp:76)
+constexpr int kPatchRows = 2 * kPatchR + 1;      // 39
+constexpr int kPatchVecs = 6;                    // 8-byte vectors per staged row (39 bytes + up to 7 of misalignment)
+constexpr int kPatchPitch = kPatchVecs * 8;      // 48 bytes
+constexpr int kPatchRowsPerPass = 32 / kPatchVecs;                                        // 5
+constexpr int kPatchPasses = (kPatchRows + kPatchRowsPerPass - 1) / kPatchRowsPerPass;    // 8
 
 __device__ __forceinline__ int round_half_even_small(float t) {  // |t| < 2^22
   return __float_as_int(__fadd_rn(t, 12582912.f)) - 0x4B400000;
@@ -49,6 +60,7 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
   __shared__ uint32_t sWU[32 * 8];       // [row v+15][chunk]: u (s8) inside the disc, else 0
   __shared__ uint32_t sWO[32 * 8];       // [row][chunk]: 1 inside the disc, else 0
   __shared__ int sStart[kMaxLevels + 1]; // first output row of each level in this frame
+  __shared__ uint2 sPatch[kDescWarps][kPatchRows * kPatchVecs];   // per warp: the blurred 39x39 neighbourhood
 
   const int f = blockIdx.y;
   const int nl = g.nlevels;
@@ -97,6 +109,20 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
     const uint32_t k = kept[L.keptOff + (long long)f * L.keptCap + (row - sStart[level])];
     const int x = cand_x(k) + kMinBorder, y = cand_y(k) + kMinBorder;  // level coordinates (:909-910)
 
+    // stage rows y-19 .. y+19, bytes from the 8-byte boundary at or below x-19 (planes are 16-byte pitched)
+    const int bp = L.pitch;
+    const int x0 = (x - kPatchR) & ~7, xo = (x - kPatchR) - x0;
+    const uint8_t* brow = blurArena + L.planeOff + (long long)f * L.planeBytes + (long long)(y - kPatchR) * bp + x0;
+    const int prow = lane / kPatchVecs, pvec = lane - prow * kPatchVecs;
+    const bool pload = lane < kPatchRowsPerPass * kPatchVecs && pvec * 8 < xo + kPatchRows;
+    __syncwarp();  // the previous keypoint's gathers are done
+#pragma unroll
+    for (int i = 0; i < kPatchPasses; i++) {
+      const int r = i * kPatchRowsPerPass + prow;
+      if (pload && r < kPatchRows)
+        sPatch[warp][r * kPatchVecs + pvec] = *reinterpret_cast<const uint2*>(brow + (long long)r * bp + pvec * 8);
+    }
+
     // ---- IC_Angle ----
     const int pitch = pyr.pitch[level];
     const uint8_t* center = pyr.lvl[level] + (long long)f * pyr.frameStride[level] + (long long)y * pitch + x;
@@ -125,8 +151,8 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
     float sn, cs;
     sincosf_glibc(__fmul_rn(angle, factorPI), &sn, &cs);
     const float a = cs, b = sn;
-    const uint8_t* bc = blurArena + L.planeOff + (long long)f * L.planeBytes + (long long)y * L.pitch + x;
-    const int bp = L.pitch;
+    __syncwarp();  // the staged rows are visible
+    const uint8_t* bc = reinterpret_cast<const uint8_t*>(sPatch[warp]) + kPatchR * kPatchPitch + kPatchR + xo;
     int val = 0;
 #pragma unroll
     for (int bit = 0; bit < 8; bit++) {
@@ -135,7 +161,7 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
       const int c0 = round_half_even_small(__fmaf_rn(q.x, a, -__fmul_rn(q.y, b)));
       const int r1 = round_half_even_small(__fmaf_rn(q.z, b, __fmul_rn(q.w, a)));
       const int c1 = round_half_even_small(__fmaf_rn(q.z, a, -__fmul_rn(q.w, b)));
-      const int t0 = bc[r0 * bp + c0], t1 = bc[r1 * bp + c1];
+      const int t0 = bc[r0 * kPatchPitch + c0], t1 = bc[r1 * kPatchPitch + c1];
       val |= (t0 < t1) << bit;
     }
     outDesc[((long long)f * cap + row) * 32 + lane] = (uint8_t)val;
