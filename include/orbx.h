@@ -234,6 +234,32 @@ int orbx_distinctive(orbx_matcher* h, const uint8_t* desc, const int32_t* obs_of
 int orbx_distinctive_device(orbx_matcher* h, const uint8_t* d_desc, const int32_t* d_obs_off, int32_t npoints,
                             int32_t* d_best, int32_t* d_best_median, void* stream);
 
+/* ---- frame epilogue on the device ----
+ * cv::undistortPoints(src, dst, K, distCoef, cv::Mat(), K) as Frame::UndistortKeyPoints (R/src/Frame.cpp:470-504)
+ * and ComputeImageBounds (:506-540) call it: n (x, y) float pairs, K4 = fx fy cx cy, dist = k1 k2 p1 p2 [k3 ...]
+ * (n_dist <= 12, OpenCV order). Bit-exact with OpenCV 4.13 (double arithmetic, five iterations). Host buffers. */
+int orbx_undistort_points(int32_t device, const float* xy, int64_t n, const float* K4, const float* dist, int32_t n_dist,
+                          float* out_xy);
+
+/* A frame whose keypoints, descriptors and 64x48 grid stay on the device between extraction and the windowed
+ * searches (Frame::Frame's epilogue: UndistortKeyPoints, AssignFeaturesToGrid R/src/Frame.cpp:244-260). Lives on the
+ * matcher's device and stream; one frame handle serves one frame at a time and is refilled with orbx_frame_set. */
+typedef struct orbx_frame orbx_frame;
+int orbx_frame_create(orbx_matcher* m, orbx_frame** out);
+void orbx_frame_destroy(orbx_frame* f);
+/* kps / desc: n rows, host (on_device = 0) or device pointers (on_device = 1, e.g. the outputs of
+ * orbx_extract_batch_device). dist[0] == 0 or n_dist == 0: mvKeysUn = mvKeys (:472-476). bounds4 = mnMinX mnMaxX mnMinY
+ * mnMaxY (computed once per camera, :506-540; orbx_undistort_points serves the four corners). Asynchronous. */
+int orbx_frame_set(orbx_frame* f, const orbx_keypoint* kps, const uint8_t* desc, int32_t n, int32_t on_device,
+                   const float* K4, const float* dist, int32_t n_dist, const float* bounds4);
+/* mvKeysUn back on the host (pose optimisation reads it): n rows */
+int orbx_frame_get_keys_un(orbx_frame* f, orbx_keypoint* kps_un);
+/* orbx_match_window against the resident frame: no keypoint / descriptor upload, no grid build, one packed upload of
+ * the queries. Same outputs and error behaviour. */
+int orbx_frame_match_window(orbx_frame* f, const float* q_xy, const float* q_r, const int32_t* q_min_level,
+                            const int32_t* q_max_level, const uint8_t* q_desc, int32_t nq, int32_t* cand_off,
+                            int32_t* cand_idx, int32_t* cand_dist, int32_t cand_cap, int32_t* n_cand);
+
 #ifdef __cplusplus
 }
 #endif

@@ -345,3 +345,38 @@ void sincosf_port(float y, float* sinp, float* cosp) {
 }
 
 }  // namespace orb_oracle
+
+// ---- cv::undistortPoints(src, dst, K, distCoeffs, noArray(), K) -- OpenCV 4.13 imgproc, cvUndistortPointsInternal ----
+// Called by Frame::UndistortKeyPoints (R/src/Frame.cpp:470-504) and ComputeImageBounds (:506-540). Double arithmetic,
+// x = (u - cx) * (1/fx), five iterations (default TermCriteria(COUNT, 5, 0.01): no EPS test), identity tilt and
+// rectification, projection with P = K, one rounding to float. This file is compiled with -ffp-contract=off.
+// PINNED: tests/test_oracle_prims.py against cv2 4.13.0 live and against tests/golden/undistort_cv2.npz.
+namespace cvp {
+void undistort_points(const float* xy, long long n, const float* K4, const float* dist, int ndist, float* out) {
+  const double fx = K4[0], fy = K4[1], cx = K4[2], cy = K4[3];
+  const double ifx = 1. / fx, ify = 1. / fy;
+  double k[12];
+  for (int i = 0; i < 12; i++) k[i] = i < ndist ? (double)dist[i] : 0.0;
+  for (long long i = 0; i < n; i++) {
+    double x = ((double)xy[2 * i] - cx) * ifx, y = ((double)xy[2 * i + 1] - cy) * ify;
+    const double x0 = x, y0 = y;
+    for (int j = 0; j < 5; j++) {
+      const double r2 = x * x + y * y;
+      const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+      if (icdist < 0) { x = x0; y = y0; break; }
+      const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+      const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+      x = (x0 - deltaX) * icdist;
+      y = (y0 - deltaY) * icdist;
+    }
+    const double xx = fx * x + 0.0 * y + cx, yy = 0.0 * x + fy * y + cy, ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+    out[2 * i] = (float)(xx * ww);
+    out[2 * i + 1] = (float)(yy * ww);
+  }
+}
+}  // namespace cvp
+
+extern "C" void orb_oracle_undistort_points(const float* xy, long long n, const float* K4, const float* dist, int ndist,
+                                            float* out) {
+  cvp::undistort_points(xy, n, K4, dist, ndist, out);
+}

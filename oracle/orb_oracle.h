@@ -144,6 +144,9 @@ void orb_oracle_search_best_in_window(const orb_oracle_keypoint* kps_un, const u
                                       const uint8_t* q_desc, int nq, uint8_t* taken, int th, int32_t* best_idx,
                                       int32_t* best_dist);
 
+/* cv::undistortPoints(src, dst, K, dist, noArray(), K) as OpenCV 4.13 computes it (cv_prims.cpp) */
+void orb_oracle_undistort_points(const float* xy, long long n, const float* K4, const float* dist, int ndist, float* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -74,6 +74,12 @@ SIGNATURES = {
     "orbx_match_merge_device": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _f32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "orbx_match_blocks": (C.c_int, [_vp, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i64, C.POINTER(_i64)]),
     "orbx_distinctive": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp]),
+    "orbx_undistort_points": (C.c_int, [_i32, _vp, _i64, _vp, _vp, _i32, _vp]),
+    "orbx_frame_create": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "orbx_frame_destroy": (None, [_vp]),
+    "orbx_frame_set": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _vp]),
+    "orbx_frame_get_keys_un": (C.c_int, [_vp, _vp]),
+    "orbx_frame_match_window": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, C.POINTER(_i32)]),
     "orbx_distinctive_device": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp]),
 }
 

@@ -1,5 +1,6 @@
 // C ABI of liborbx.so, matcher half (include/orbx.h): DescriptorDistance and brute-force top-2.
 #include <algorithm>
+#include <cstring>
 #include <initializer_list>
 #include <new>
 #include <vector>
@@ -26,6 +27,10 @@ void launch_block_distance(const uint8_t* descA, const uint8_t* descB, const int
                            const int* bIdx, const int* entryBlock, const long long* dOff, int nEntries,
                            unsigned short* dist, cudaStream_t s);
 void launch_distinctive(const uint8_t* desc, const int* obsOff, int nPoints, int* best, int* bestMedian, cudaStream_t s);
+void launch_undistort_keys(const orbx_keypoint* in, orbx_keypoint* out, int n, const float* K4, const float* dist, int ndist,
+                           cudaStream_t s);
+void launch_undistort_points(const float* in, float* out, long long n, const float* K4, const float* dist, int ndist,
+                             cudaStream_t s);
 }  // namespace orbx
 
 using namespace orbx;
@@ -504,6 +509,188 @@ int orbx_distinctive(orbx_matcher* h, const uint8_t* desc, const int32_t* obs_of
   ORBX_CUDA_TRY(cudaMemcpyAsync(best, dBest, P * 4, cudaMemcpyDeviceToHost, s));
   ORBX_CUDA_TRY(cudaMemcpyAsync(best_median, dMed, P * 4, cudaMemcpyDeviceToHost, s));
   ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  return ORBX_OK;
+}
+
+// ---- device-resident frames -----------------------------------------------------------------
+}  // extern "C"
+
+struct orbx_frame {
+  orbx_matcher* m = nullptr;
+  int n = 0;
+  bool ready = false;
+  float bounds[4] = {0, 0, 0, 0};
+  DeviceBuf kps, kpsUn, desc, grid, work;   // grid: cellStart | items; work: packed queries | counts | offsets | candidates
+  void* hostQ = nullptr;                    // pinned staging of one call's packed queries
+  size_t hostQBytes = 0;
+};
+
+extern "C" {
+
+int orbx_undistort_points(int32_t device, const float* xy, int64_t n, const float* K4, const float* dist, int32_t n_dist,
+                          float* out_xy) {
+  if (!xy || !out_xy || !K4 || n < 0 || n_dist < 0 || n_dist > 12 || (n_dist > 0 && !dist)) { set_error("bad arguments"); return ORBX_ERR_ARG; }
+  int cnt = 0;
+  cudaError_t e = cudaGetDeviceCount(&cnt);
+  if (e != cudaSuccess || cnt <= 0) { set_error("no usable CUDA device; liborbx has no CPU fallback"); return ORBX_ERR_CUDA; }
+  if (device < 0 || device >= cnt) { set_error("device %d out of range", device); return ORBX_ERR_ARG; }
+  ORBX_CUDA_TRY(cudaSetDevice(device));
+  if (n == 0) return ORBX_OK;
+  float *dIn = nullptr, *dOut = nullptr;
+  ORBX_CUDA_TRY(cudaMalloc(&dIn, (size_t)n * 8));
+  if (cudaMalloc(&dOut, (size_t)n * 8) != cudaSuccess) { cudaFree(dIn); set_error("out of device memory"); return ORBX_ERR_CUDA; }
+  cudaMemcpy(dIn, xy, (size_t)n * 8, cudaMemcpyHostToDevice);
+  launch_undistort_points(dIn, dOut, n, K4, dist, n_dist, nullptr);
+  cudaMemcpy(out_xy, dOut, (size_t)n * 8, cudaMemcpyDeviceToHost);
+  e = cudaGetLastError();
+  cudaFree(dIn); cudaFree(dOut);
+  if (e != cudaSuccess) { set_error("undistort failed: %s", cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
+  return ORBX_OK;
+}
+
+int orbx_frame_create(orbx_matcher* m, orbx_frame** out) {
+  int rc = set_dev(m);
+  if (rc) return rc;
+  if (!out) { set_error("null argument"); return ORBX_ERR_ARG; }
+  orbx_frame* f = new (std::nothrow) orbx_frame();
+  if (!f) { set_error("out of host memory"); return ORBX_ERR_ARG; }
+  f->m = m;
+  *out = f;
+  return ORBX_OK;
+}
+
+void orbx_frame_destroy(orbx_frame* f) {
+  if (!f) return;
+  cudaSetDevice(f->m->device);
+  cudaStreamSynchronize(f->m->stream);
+  f->kps.release(); f->kpsUn.release(); f->desc.release(); f->grid.release(); f->work.release();
+  if (f->hostQ) cudaFreeHost(f->hostQ);
+  delete f;
+}
+
+int orbx_frame_set(orbx_frame* f, const orbx_keypoint* kps, const uint8_t* desc, int32_t n, int32_t on_device,
+                   const float* K4, const float* dist, int32_t n_dist, const float* bounds4) {
+  if (!f) { set_error("null frame"); return ORBX_ERR_ARG; }
+  int rc = set_dev(f->m);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!kps || !desc)) || !bounds4 || n_dist < 0 || n_dist > 12 || (n_dist > 0 && (!dist || !K4))) {
+    set_error("bad arguments");
+    return ORBX_ERR_ARG;
+  }
+  if (!(bounds4[1] > bounds4[0]) || !(bounds4[3] > bounds4[2])) { set_error("empty image bounds"); return ORBX_ERR_ARG; }
+  f->ready = false;
+  const size_t N = (size_t)std::max(n, 1);
+  const int cells = grid_cells();
+  if ((rc = f->kps.ensure(N * sizeof(orbx_keypoint))) || (rc = f->kpsUn.ensure(N * sizeof(orbx_keypoint))) ||
+      (rc = f->desc.ensure(N * 32)) || (rc = f->grid.ensure(carve_size({(size_t)(cells + 1) * 4, N * 4}))))
+    return rc;
+  cudaStream_t s = f->m->stream;
+  const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  orbx_keypoint* dK = static_cast<orbx_keypoint*>(f->kps.p);
+  orbx_keypoint* dKU = static_cast<orbx_keypoint*>(f->kpsUn.p);
+  if (n > 0) {
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dK, kps, (size_t)n * sizeof(orbx_keypoint), kind, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(f->desc.p, desc, (size_t)n * 32, kind, s));
+    // R/src/Frame.cpp:472-476: no distortion => mvKeysUn = mvKeys
+    if (n_dist > 0 && dist[0] != 0.0f) {
+      launch_undistort_keys(dK, dKU, n, K4, dist, n_dist, s);
+      f->m->launches++;
+    } else {
+      ORBX_CUDA_TRY(cudaMemcpyAsync(dKU, dK, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyDeviceToDevice, s));
+    }
+  }
+  Carver c{static_cast<uint8_t*>(f->grid.p)};
+  int* dCell = c.take<int>(cells + 1);
+  int* dItems = c.take<int>(N);
+  launch_grid_build(dKU, n, bounds4[0], bounds4[1], bounds4[2], bounds4[3], dCell, dItems, s);   // AssignFeaturesToGrid :244-260
+  f->m->launches++;
+  ORBX_CUDA_TRY(cudaGetLastError());
+  f->n = n;
+  for (int i = 0; i < 4; i++) f->bounds[i] = bounds4[i];
+  f->ready = true;
+  return ORBX_OK;
+}
+
+int orbx_frame_get_keys_un(orbx_frame* f, orbx_keypoint* kps_un) {
+  if (!f || !f->ready) { set_error("frame holds no keypoints"); return ORBX_ERR_STATE; }
+  int rc = set_dev(f->m);
+  if (rc) return rc;
+  if (f->n > 0) {
+    if (!kps_un) { set_error("null argument"); return ORBX_ERR_ARG; }
+    ORBX_CUDA_TRY(cudaMemcpyAsync(kps_un, f->kpsUn.p, (size_t)f->n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, f->m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(f->m->stream));
+  }
+  return ORBX_OK;
+}
+
+int orbx_frame_match_window(orbx_frame* f, const float* q_xy, const float* q_r, const int32_t* q_min_level,
+                            const int32_t* q_max_level, const uint8_t* q_desc, int32_t nq, int32_t* cand_off,
+                            int32_t* cand_idx, int32_t* cand_dist, int32_t cand_cap, int32_t* n_cand) {
+  if (!f || !f->ready) { set_error("frame holds no keypoints"); return ORBX_ERR_STATE; }
+  orbx_matcher* h = f->m;
+  int rc = set_dev(h);
+  if (rc) return rc;
+  if (nq < 0 || cand_cap < 0 || !cand_off || !n_cand || (nq > 0 && (!q_xy || !q_r || !q_min_level || !q_max_level || !q_desc))) {
+    set_error("bad arguments");
+    return ORBX_ERR_ARG;
+  }
+  *n_cand = 0;
+  cand_off[0] = 0;
+  if (nq == 0) return ORBX_OK;
+  // one packed upload instead of five: xy | r | min | max | desc, each part 256-byte aligned
+  const size_t Q = (size_t)nq;
+  const size_t oXY = 0, oR = oXY + ((Q * 8 + 255) & ~size_t(255)), oMin = oR + ((Q * 4 + 255) & ~size_t(255)),
+               oMax = oMin + ((Q * 4 + 255) & ~size_t(255)), oD = oMax + ((Q * 4 + 255) & ~size_t(255)),
+               qBytes = oD + ((Q * 32 + 255) & ~size_t(255));
+  if (qBytes > f->hostQBytes) {
+    if (f->hostQ) { ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream)); cudaFreeHost(f->hostQ); f->hostQ = nullptr; f->hostQBytes = 0; }
+    ORBX_CUDA_TRY(cudaMallocHost(&f->hostQ, qBytes * 2));
+    f->hostQBytes = qBytes * 2;
+  }
+  uint8_t* hq = static_cast<uint8_t*>(f->hostQ);
+  std::memcpy(hq + oXY, q_xy, Q * 8);
+  std::memcpy(hq + oR, q_r, Q * 4);
+  std::memcpy(hq + oMin, q_min_level, Q * 4);
+  std::memcpy(hq + oMax, q_max_level, Q * 4);
+  std::memcpy(hq + oD, q_desc, Q * 32);
+  if ((rc = f->work.ensure(carve_size({qBytes, Q * 4, (Q + 1) * 4, (size_t)std::max(cand_cap, 1) * 4, (size_t)std::max(cand_cap, 1) * 4}))))
+    return rc;
+  Carver c{static_cast<uint8_t*>(f->work.p)};
+  uint8_t* dQ = c.take<uint8_t>(qBytes);
+  int* dCount = c.take<int>(Q);
+  int* dOff = c.take<int>(Q + 1);
+  int* dCi = c.take<int>(std::max(cand_cap, 1));
+  int* dCd = c.take<int>(std::max(cand_cap, 1));
+  Carver cg{static_cast<uint8_t*>(f->grid.p)};
+  const int* dCell = cg.take<int>(grid_cells() + 1);
+  const int* dItems = cg.take<int>(std::max(f->n, 1));
+  cudaStream_t s = h->stream;
+  const orbx_keypoint* dKU = static_cast<const orbx_keypoint*>(f->kpsUn.p);
+  const uint8_t* dD = static_cast<const uint8_t*>(f->desc.p);
+  const float* b = f->bounds;
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dQ, hq, qBytes, cudaMemcpyHostToDevice, s));
+  auto window = [&](bool fill) {
+    launch_window(fill, dKU, dD, b[0], b[1], b[2], b[3], dCell, dItems, reinterpret_cast<const float*>(dQ + oXY),
+                  reinterpret_cast<const float*>(dQ + oR), reinterpret_cast<const int*>(dQ + oMin),
+                  reinterpret_cast<const int*>(dQ + oMax), dQ + oD, nq, dCount, dOff, dCi, dCd, s);
+  };
+  window(false);
+  launch_scan(dCount, nq, dOff, s);
+  h->launches += 2;
+  ORBX_CUDA_TRY(cudaGetLastError());
+  ORBX_CUDA_TRY(cudaMemcpyAsync(cand_off, dOff, (Q + 1) * 4, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  const int total = cand_off[nq];
+  *n_cand = total;
+  if (total > cand_cap || (total > 0 && (!cand_idx || !cand_dist))) { set_error("candidate capacity %d < %d", cand_cap, total); return ORBX_ERR_CAPACITY; }
+  if (total > 0) {
+    window(true);
+    h->launches++;
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(cand_idx, dCi, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(cand_dist, dCd, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  }
   return ORBX_OK;
 }
 

@@ -134,3 +134,81 @@ class ORBmatcher:
 
     def launch_count(self):
         return int(lib().orbx_matcher_launch_count(self._h))
+
+
+def undistort_points(xy, K4, dist, device=0):
+    """cv::undistortPoints(xy, K, dist, None, K) on the device (R/src/Frame.cpp:491, :523): (n, 2) float32."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    K4 = np.ascontiguousarray(K4, np.float32)
+    dist = np.ascontiguousarray(dist, np.float32)
+    out = np.empty_like(xy)
+    check(lib().orbx_undistort_points(device, ptr(xy), len(xy), ptr(K4), ptr(dist), len(dist), ptr(out)))
+    return out
+
+
+class Frame:
+    """Device-resident mirror of what Frame::Frame leaves for the matchers (R/src/Frame.cpp:187-250): mvKeysUn
+    (UndistortKeyPoints), mDescriptors and the 64x48 grid (AssignFeaturesToGrid), kept in HBM on the matcher's device."""
+
+    def __init__(self, matcher):
+        self.matcher = matcher
+        h = C.c_void_p()
+        check(lib().orbx_frame_create(matcher._h, C.byref(h)))
+        self._h = h
+        self.N = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbx_frame_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def set(self, kps, desc, bounds, K4=None, dist=None):
+        """Host arrays: keypoints (KP_DTYPE) and descriptors of one frame; K4 = (fx, fy, cx, cy) and dist = distortion
+        coefficients (None or dist[0] == 0: no undistortion); bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+        kps = np.ascontiguousarray(kps)
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        b = np.ascontiguousarray(bounds, np.float32)
+        k = np.zeros(4, np.float32) if K4 is None else np.ascontiguousarray(K4, np.float32)
+        d = np.zeros(0, np.float32) if dist is None else np.ascontiguousarray(dist, np.float32)
+        check(lib().orbx_frame_set(self._h, ptr(kps), ptr(desc), len(kps), 0, ptr(k), ptr(d), len(d), ptr(b)))
+        self.N = len(kps)
+        self._dtype = kps.dtype
+
+    def set_device(self, d_kps_ptr, d_desc_ptr, n, bounds, K4=None, dist=None):
+        """The same from device pointers (e.g. one frame's rows of orbx_extract_batch_device's outputs)."""
+        b = np.ascontiguousarray(bounds, np.float32)
+        k = np.zeros(4, np.float32) if K4 is None else np.ascontiguousarray(K4, np.float32)
+        d = np.zeros(0, np.float32) if dist is None else np.ascontiguousarray(dist, np.float32)
+        check(lib().orbx_frame_set(self._h, d_kps_ptr, d_desc_ptr, n, 1, ptr(k), ptr(d), len(d), ptr(b)))
+        self.N = n
+
+    def keys_un(self):
+        from ._capi import KP_DTYPE
+        out = np.empty(max(self.N, 1), KP_DTYPE)
+        check(lib().orbx_frame_get_keys_un(self._h, ptr(out)))
+        return out[:self.N]
+
+    def match_window(self, q_xy, q_r, q_min_level, q_max_level, q_desc):
+        """ORBmatcher.match_window against the resident frame: (cand_off, cand_idx, cand_dist)."""
+        q_xy = np.ascontiguousarray(q_xy, np.float32).reshape(-1, 2)
+        nq = q_xy.shape[0]
+        q_r = np.ascontiguousarray(q_r, np.float32)
+        q_min_level = np.ascontiguousarray(q_min_level, np.int32)
+        q_max_level = np.ascontiguousarray(q_max_level, np.int32)
+        q_desc = np.ascontiguousarray(q_desc, np.uint8).reshape(-1, 32)
+        if not (len(q_r) == len(q_min_level) == len(q_max_level) == len(q_desc) == nq):
+            raise ValueError("query arrays disagree in length")
+        off = np.zeros(nq + 1, np.int32)
+        cap = max(64, 32 * nq)
+        while True:
+            idx, dist = np.empty(cap, np.int32), np.empty(cap, np.int32)
+            n = C.c_int32(0)
+            rc = lib().orbx_frame_match_window(self._h, ptr(q_xy), ptr(q_r), ptr(q_min_level), ptr(q_max_level), ptr(q_desc), nq,
+                                               ptr(off), ptr(idx), ptr(dist), cap, C.byref(n))
+            if rc == -3 and n.value > cap:
+                cap = n.value
+                continue
+            check(rc)
+            return off, idx[:n.value].copy(), dist[:n.value].copy()

@@ -91,6 +91,8 @@ def lib():
         L.orb_oracle_distinctive.restype = None
         L.orb_oracle_search_best_in_window.argtypes = [V, V, I, V, F, F, F, F, V, V, V, V, V, V, I, V, I, V, V]
         L.orb_oracle_search_best_in_window.restype = None
+        L.orb_oracle_undistort_points.argtypes = [V, C.c_longlong, V, V, I, V]
+        L.orb_oracle_undistort_points.restype = None
     return _lib
 
 
@@ -432,3 +434,13 @@ def search_best_in_window(kps_un, desc, uright, bounds, inv_level_sigma2, q_uv, 
                                            _ptr(q_uv), _ptr(q_ur), _ptr(q_radius), _ptr(q_level), _ptr(q_desc), nq,
                                            _opt(taken), th, _ptr(bi), _ptr(bd))
     return bi[:nq], bd[:nq]
+
+
+def undistort_points(xy, K4, dist):
+    """cv::undistortPoints(xy, K, dist, None, K): (n, 2) float32 in and out."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    K4 = np.ascontiguousarray(K4, np.float32)
+    dist = np.ascontiguousarray(dist, np.float32)
+    out = np.empty_like(xy)
+    lib().orb_oracle_undistort_points(_ptr(xy), len(xy), _ptr(K4), _ptr(dist), len(dist), _ptr(out))
+    return out

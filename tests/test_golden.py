@@ -24,6 +24,14 @@ def test_primitives_match_cv2_golden(oracle):
     assert np.array_equal(got.view(np.uint32), d["atan2_deg"].view(np.uint32))
 
 
+def test_undistort_points_match_cv2_golden(oracle):
+    d = np.load(G / "undistort_cv2.npz")
+    assert str(d["cv2_version"]).startswith("4.13")
+    for cam in ("tum1", "tum2", "euroc", "strong"):
+        got = oracle.undistort_points(d[cam + "_in"], d[cam + "_K4"], d[cam + "_dist"])
+        assert np.array_equal(got.view(np.uint32), d[cam + "_out"].view(np.uint32)), cam
+
+
 def test_extractor_regression_hashes(oracle, pkg):
     e = np.load(G / "extract_oracle.npz")
     keys = sorted(k[:-4] for k in e.files if k.endswith("_sha"))

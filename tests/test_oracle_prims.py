@@ -58,3 +58,19 @@ def test_sincosf_port_equals_libm_on_orb_domain(oracle):
     for start in range(0, hi, hi // 16):
         bad, first = oracle.sincosf_sweep(start, min(hi, start + (1 << 21)))
         assert bad == 0, hex(first)
+
+
+def test_undistort_points_vs_cv2(oracle):
+    """cv::undistortPoints(src, dst, K, dist, noArray(), K) as Frame::UndistortKeyPoints / ComputeImageBounds call it
+    (R/src/Frame.cpp:491, :523): every coordinate bit-identical, 4 and 5 coefficients, weak and strong lenses."""
+    rng = np.random.default_rng(11)
+    cams = [([517.306408, 516.469215, 318.643040, 255.313989], [0.262383, -0.953104, -0.005358, 0.002628, 1.163314]),
+            ([458.654, 457.296, 367.215, 248.375], [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05]),
+            ([300.0, 300.0, 320.0, 240.0], [-0.9, 0.1, 0.01, -0.02, 0.0])]
+    for K4, dist in cams:
+        K4, dist = np.array(K4, np.float32), np.array(dist, np.float32)
+        pts = np.stack([rng.uniform(-50, 810, 50000), rng.uniform(-50, 570, 50000)], 1).astype(np.float32)
+        K = np.array([[K4[0], 0, K4[2]], [0, K4[1], K4[3]], [0, 0, 1]], np.float32)
+        exp = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, dist.reshape(-1, 1), None, K).reshape(-1, 2)
+        got = oracle.undistort_points(pts, K4, dist)
+        assert np.array_equal(got.view(np.uint32), exp.view(np.uint32))
