@@ -260,6 +260,21 @@ int orbx_frame_match_window(orbx_frame* f, const float* q_xy, const float* q_r, 
                             const int32_t* q_max_level, const uint8_t* q_desc, int32_t nq, int32_t* cand_off,
                             int32_t* cand_idx, int32_t* cand_dist, int32_t cand_cap, int32_t* n_cand);
 
+/* ---- vocabulary descent ----
+ * The tree of a DBoW2::TemplatedVocabulary<cv::Mat, FORB> resident on the device: node 0 is the root, parent[i] < i,
+ * the children of a node keep their id order (the order loadFromTextFile appends them in,
+ * R/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1362-1436), desc = nnodes x 32 bytes, depth_L = m_L. */
+typedef struct orbx_vocabulary orbx_vocabulary;
+int orbx_vocabulary_create(orbx_matcher* m, int32_t nnodes, const int32_t* parent, const uint8_t* desc, int32_t depth_L,
+                           orbx_vocabulary** out);
+void orbx_vocabulary_destroy(orbx_vocabulary* v);
+/* transform(feature, word_id, weight, nid, levelsup) (:1242-1296) for n descriptors: leaf_node[i] = the node the
+ * descent ends in (its word id and weight are the caller's m_nodes[leaf].word_id / .weight), level_node[i] = the node
+ * passed at level depth_L - levelsup (0 when that level is <= 0; -1 when the leaf lies above it, where the reference
+ * leaves *nid unset). Host buffers, synchronous. BowVector / FeatureVector assembly: host/orbx_bow.h. */
+int orbx_vocabulary_descend(orbx_vocabulary* v, const uint8_t* desc, int32_t n, int32_t levelsup, int32_t* leaf_node,
+                            int32_t* level_node);
+
 #ifdef __cplusplus
 }
 #endif

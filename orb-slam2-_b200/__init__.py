@@ -7,7 +7,7 @@ tests and bench.py. Nothing here computes on the CPU and nothing here imports or
 from ._capi import KP_DTYPE, LIB_PATH, OrbxError, SIGNATURES, lib, pinned_empty  # noqa: F401
 from .extractor import (ORBextractor, blur7_u8, distribute, fast_atan2, resize_u8, sincosf,  # noqa: F401
                         sincosf_sweep)
-from .matcher import Frame, ORBmatcher, undistort_points  # noqa: F401
+from .matcher import Frame, ORBmatcher, Vocabulary, undistort_points  # noqa: F401
 from . import sharding, synth  # noqa: F401
 
 

@@ -80,6 +80,9 @@ SIGNATURES = {
     "orbx_frame_set": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _vp]),
     "orbx_frame_get_keys_un": (C.c_int, [_vp, _vp]),
     "orbx_frame_match_window": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, C.POINTER(_i32)]),
+    "orbx_vocabulary_create": (C.c_int, [_vp, _i32, _vp, _vp, _i32, C.POINTER(_vp)]),
+    "orbx_vocabulary_destroy": (None, [_vp]),
+    "orbx_vocabulary_descend": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _vp]),
     "orbx_distinctive_device": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp]),
 }
 

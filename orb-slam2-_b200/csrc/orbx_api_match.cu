@@ -27,6 +27,8 @@ void launch_block_distance(const uint8_t* descA, const uint8_t* descB, const int
                            const int* bIdx, const int* entryBlock, const long long* dOff, int nEntries,
                            unsigned short* dist, cudaStream_t s);
 void launch_distinctive(const uint8_t* desc, const int* obsOff, int nPoints, int* best, int* bestMedian, cudaStream_t s);
+void launch_voc_descend(const uint8_t* feat, int n, const uint8_t* nodeDesc, const int* childOff, const int* childIdx,
+                        int nidLevel, int* leafNode, int* levelNode, cudaStream_t s);
 void launch_undistort_keys(const orbx_keypoint* in, orbx_keypoint* out, int n, const float* K4, const float* dist, int ndist,
                            cudaStream_t s);
 void launch_undistort_points(const float* in, float* out, long long n, const float* K4, const float* dist, int ndist,
@@ -691,6 +693,89 @@ int orbx_frame_match_window(orbx_frame* f, const float* q_xy, const float* q_r, 
     ORBX_CUDA_TRY(cudaMemcpyAsync(cand_dist, dCd, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA_TRY(cudaStreamSynchronize(s));
   }
+  return ORBX_OK;
+}
+
+// ---- vocabulary -----------------------------------------------------------------------------
+}  // extern "C"
+
+struct orbx_vocabulary {
+  orbx_matcher* m = nullptr;
+  int nnodes = 0, depth = 0;
+  DeviceBuf tree;   // node descriptors | child offsets | child ids
+  DeviceBuf work;   // features | leaf node | level node
+  size_t oOff = 0, oIdx = 0;
+};
+
+extern "C" {
+
+int orbx_vocabulary_create(orbx_matcher* m, int32_t nnodes, const int32_t* parent, const uint8_t* desc, int32_t depth_L,
+                           orbx_vocabulary** out) {
+  int rc = set_dev(m);
+  if (rc) return rc;
+  if (!out || nnodes < 1 || !parent || !desc || depth_L < 1) { set_error("bad arguments"); return ORBX_ERR_ARG; }
+  *out = nullptr;
+  // children in id order, like loadFromTextFile appends them (TemplatedVocabulary.h:1409)
+  std::vector<int> off((size_t)nnodes + 1, 0), idx((size_t)std::max(nnodes - 1, 1));
+  for (int i = 1; i < nnodes; i++) {
+    if (parent[i] < 0 || parent[i] >= i) { set_error("parent[%d] = %d: parents must precede their children", i, parent[i]); return ORBX_ERR_ARG; }
+    off[parent[i] + 1]++;
+  }
+  for (int i = 0; i < nnodes; i++) {
+    if (off[i + 1] > 256) { set_error("node %d has %d children (supported: 256)", i, off[i + 1]); return ORBX_ERR_ARG; }
+    off[i + 1] += off[i];
+  }
+  std::vector<int> fill(off.begin(), off.end() - 1);
+  for (int i = 1; i < nnodes; i++) idx[fill[parent[i]]++] = i;
+  orbx_vocabulary* v = new (std::nothrow) orbx_vocabulary();
+  if (!v) { set_error("out of host memory"); return ORBX_ERR_ARG; }
+  v->m = m; v->nnodes = nnodes; v->depth = depth_L;
+  const size_t N = (size_t)nnodes;
+  v->oOff = (N * 32 + 255) & ~size_t(255);
+  v->oIdx = v->oOff + (((N + 1) * 4 + 255) & ~size_t(255));
+  if ((rc = v->tree.ensure(v->oIdx + idx.size() * 4 + 256))) { delete v; return rc; }
+  uint8_t* base = static_cast<uint8_t*>(v->tree.p);
+  cudaStream_t s = m->stream;
+  cudaError_t e = cudaMemcpyAsync(base, desc, N * 32, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(base + v->oOff, off.data(), (N + 1) * 4, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(base + v->oIdx, idx.data(), idx.size() * 4, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);   // off / idx are locals
+  if (e != cudaSuccess) { set_error("vocabulary upload failed: %s", cudaGetErrorString(e)); v->tree.release(); delete v; return ORBX_ERR_CUDA; }
+  *out = v;
+  return ORBX_OK;
+}
+
+void orbx_vocabulary_destroy(orbx_vocabulary* v) {
+  if (!v) return;
+  cudaSetDevice(v->m->device);
+  cudaStreamSynchronize(v->m->stream);
+  v->tree.release(); v->work.release();
+  delete v;
+}
+
+int orbx_vocabulary_descend(orbx_vocabulary* v, const uint8_t* desc, int32_t n, int32_t levelsup, int32_t* leaf_node,
+                            int32_t* level_node) {
+  if (!v) { set_error("null vocabulary"); return ORBX_ERR_ARG; }
+  int rc = set_dev(v->m);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!desc || !leaf_node || !level_node))) { set_error("bad arguments"); return ORBX_ERR_ARG; }
+  if (n == 0) return ORBX_OK;
+  const size_t N = (size_t)n;
+  if ((rc = v->work.ensure(carve_size({N * 32, N * 4, N * 4})))) return rc;
+  Carver c{static_cast<uint8_t*>(v->work.p)};
+  uint8_t* dF = c.take<uint8_t>(N * 32);
+  int* dLeaf = c.take<int>(N);
+  int* dLevel = c.take<int>(N);
+  cudaStream_t s = v->m->stream;
+  const uint8_t* base = static_cast<const uint8_t*>(v->tree.p);
+  ORBX_CUDA_TRY(cudaMemcpyAsync(dF, desc, N * 32, cudaMemcpyHostToDevice, s));
+  launch_voc_descend(dF, n, base, reinterpret_cast<const int*>(base + v->oOff), reinterpret_cast<const int*>(base + v->oIdx),
+                     v->depth - levelsup, dLeaf, dLevel, s);
+  v->m->launches++;
+  ORBX_CUDA_TRY(cudaGetLastError());
+  ORBX_CUDA_TRY(cudaMemcpyAsync(leaf_node, dLeaf, N * 4, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(level_node, dLevel, N * 4, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(s));
   return ORBX_OK;
 }
 

@@ -116,3 +116,51 @@ void launch_distinctive(const uint8_t* desc, const int* obsOff, int nPoints, int
 }
 
 }  // namespace orbx
+
+// ---- vocabulary descent ---------------------------------------------------------------------
+// DBoW2::TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup)
+// (R/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1242-1296), what Frame::ComputeBoW / KeyFrame::ComputeBoW run once
+// per descriptor (R/src/Frame.cpp:262-274, R/src/KeyFrame.cpp:66-75): from the root, move to the child with the
+// least FORB::distance (first minimum wins, :1268-1278) until a leaf; remember the node passed at level L - levelsup.
+// One warp per descriptor: its row in registers, lane j scores child j (k <= 20 in the text format), the arg-min is
+// a warp reduction of (distance << 8 | child position). The tree (32 bytes per node, ~35 MB for ORBvoc's 1.08 M
+// nodes) stays resident in HBM / L2; a descent reads L x k rows.
+namespace orbx {
+
+__global__ void __launch_bounds__(kBlockWarps * 32)
+voc_descend_kernel(const uint4* __restrict__ feat, int n, const uint4* __restrict__ nodeDesc,
+                   const int* __restrict__ childOff, const int* __restrict__ childIdx, int nidLevel,
+                   int* __restrict__ leafNode, int* __restrict__ levelNode) {
+  const int lane = threadIdx.x & 31;
+  const int f = blockIdx.x * kBlockWarps + (threadIdx.x >> 5);
+  if (f >= n) return;
+  const uint4 a0 = feat[2 * f], a1 = feat[2 * f + 1];
+  int node = 0, level = 0;
+  int nid = nidLevel <= 0 ? 0 : -1;   // -1: a leaf above the requested level (the reference leaves *nid unset there)
+  for (;;) {
+    const int c0 = childOff[node], nc = childOff[node + 1] - c0;
+    if (nc == 0) break;
+    ++level;
+    unsigned best = 0xFFFFFFFFu;
+    for (int j = lane; j < nc; j += 32) {
+      const int c = childIdx[c0 + j];
+      const unsigned d = (unsigned)hamming_rows(a0, a1, nodeDesc[2 * c], nodeDesc[2 * c + 1]);
+      best = min(best, (d << 8) | (unsigned)j);   // nc <= 256 children per node
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    node = childIdx[c0 + (int)(best & 0xFFu)];
+    if (level == nidLevel) nid = node;
+  }
+  if (lane == 0) { leafNode[f] = node; levelNode[f] = nid; }
+}
+
+void launch_voc_descend(const uint8_t* feat, int n, const uint8_t* nodeDesc, const int* childOff, const int* childIdx,
+                        int nidLevel, int* leafNode, int* levelNode, cudaStream_t s) {
+  if (n <= 0) return;
+  voc_descend_kernel<<<(n + kBlockWarps - 1) / kBlockWarps, kBlockWarps * 32, 0, s>>>(
+      reinterpret_cast<const uint4*>(feat), n, reinterpret_cast<const uint4*>(nodeDesc), childOff, childIdx, nidLevel,
+      leafNode, levelNode);
+}
+
+}  // namespace orbx

@@ -136,3 +136,37 @@ void mirror_search_best_in_window(orbx_matcher* m, const orbx_keypoint* k, const
 }
 
 }  // extern "C"
+
+// ---- vocabulary transform (host/orbx_bow.h) -------------------------------------------------------
+#include "orbx_bow.h"
+
+extern "C" {
+
+void* mirror_voc_load(orbx_matcher* m, const char* path) {
+  orbx_host::Vocabulary* v = new orbx_host::Vocabulary();
+  if (!v->loadFromTextFile(m, path)) { delete v; return 0; }
+  return v;
+}
+void mirror_voc_destroy(void* h) { delete static_cast<orbx_host::Vocabulary*>(h); }
+int mirror_voc_words(void* h) { return static_cast<orbx_host::Vocabulary*>(h)->words; }
+
+// flattened like ref_voc_transform (oracle/ref_shim/ref_voc_capi.cpp)
+int mirror_voc_transform(void* h, const unsigned char* desc, int n, int levelsup, unsigned* words, double* values,
+                         unsigned* nodes, int* off, unsigned* idx, int* nNodes, int* nIdx) {
+  std::map<unsigned, double> v;
+  std::map<unsigned, std::vector<unsigned> > fv;
+  static_cast<orbx_host::Vocabulary*>(h)->transform(desc, n, &v, &fv, levelsup);
+  int k = 0;
+  for (std::map<unsigned, double>::const_iterator it = v.begin(); it != v.end(); ++it, ++k) { words[k] = it->first; values[k] = it->second; }
+  int a = 0, b = 0;
+  off[0] = 0;
+  for (std::map<unsigned, std::vector<unsigned> >::const_iterator it = fv.begin(); it != fv.end(); ++it, ++a) {
+    nodes[a] = it->first;
+    for (size_t j = 0; j < it->second.size(); j++) idx[b++] = it->second[j];
+    off[a + 1] = b;
+  }
+  *nNodes = a; *nIdx = b;
+  return k;
+}
+
+}  // extern "C"

@@ -212,3 +212,33 @@ class Frame:
                 continue
             check(rc)
             return off, idx[:n.value].copy(), dist[:n.value].copy()
+
+
+class Vocabulary:
+    """The tree of a DBoW2 vocabulary resident on the device (orbx_vocabulary_*): parent[i] < i per node (node 0 =
+    root), node descriptors (nodes, 32) uint8, depth L."""
+
+    def __init__(self, matcher, parent, desc, depth):
+        self.matcher = matcher
+        parent = np.ascontiguousarray(parent, np.int32)
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        if len(parent) != len(desc):
+            raise ValueError("parent and desc disagree in length")
+        h = C.c_void_p()
+        check(lib().orbx_vocabulary_create(matcher._h, len(parent), ptr(parent), ptr(desc), depth, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbx_vocabulary_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def descend(self, desc, levelsup):
+        """Per descriptor: (leaf node, node at level L - levelsup) of TemplatedVocabulary::transform's descent."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        leaf, level = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
+        check(lib().orbx_vocabulary_descend(self._h, ptr(desc), n, levelsup, ptr(leaf), ptr(level)))
+        return leaf[:n], level[:n]

@@ -93,6 +93,14 @@ def lib():
         L.orb_oracle_search_best_in_window.restype = None
         L.orb_oracle_undistort_points.argtypes = [V, C.c_longlong, V, V, I, V]
         L.orb_oracle_undistort_points.restype = None
+        L.orb_oracle_voc_load.restype = V
+        L.orb_oracle_voc_load.argtypes = [C.c_char_p]
+        L.orb_oracle_voc_destroy.argtypes = [V]
+        L.orb_oracle_voc_nodes.argtypes = [V]
+        L.orb_oracle_voc_words.argtypes = [V]
+        L.orb_oracle_voc_export.argtypes = [V] * 6
+        L.orb_oracle_voc_export.restype = None
+        L.orb_oracle_voc_transform.argtypes = [V, V, I, I] + [V] * 7
     return _lib
 
 
@@ -444,3 +452,30 @@ def undistort_points(xy, K4, dist):
     out = np.empty_like(xy)
     lib().orb_oracle_undistort_points(_ptr(xy), len(xy), _ptr(K4), _ptr(dist), len(dist), _ptr(out))
     return out
+
+
+class Vocabulary:
+    """Restatement of the vendored DBoW2 vocabulary: loadFromTextFile + transform (oracle/bow_oracle.cpp)."""
+
+    def __init__(self, path):
+        self._h = lib().orb_oracle_voc_load(str(path).encode())
+        assert self._h, "not a vocabulary text file"
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orb_oracle_voc_destroy(self._h)
+            self._h = None
+
+    def words(self):
+        return lib().orb_oracle_voc_words(self._h)
+
+    def export(self):
+        n = lib().orb_oracle_voc_nodes(self._h)
+        parent, desc = np.empty(n, np.int32), np.empty((n, 32), np.uint8)
+        weight, word, klsw = np.empty(n, np.float64), np.empty(n, np.int32), np.empty(4, np.int32)
+        lib().orb_oracle_voc_export(self._h, _ptr(parent), _ptr(desc), _ptr(weight), _ptr(word), _ptr(klsw))
+        return parent, desc, weight, word, klsw
+
+    def transform(self, desc, levelsup):
+        import ref_voc_lib
+        return ref_voc_lib.flat_transform(lib().orb_oracle_voc_transform, self._h, desc, levelsup)
