@@ -233,6 +233,79 @@ def run_reference(args):
     return 0
 
 
+def run_matcher_rows(pkg, local):
+    """SURVEY 8f rows (key-frame searches, distinctive descriptors, frame epilogue, vocabulary descent): ms per call
+    through the product's host-buffer entry points next to the oracle port on ONE host thread, same inputs. These
+    are per-frame latencies of small problems (10^3 keypoints), reported for completeness; rank 0, N = 1 only."""
+    import oracle_lib as ol
+    import tempfile
+    sys.path.insert(0, str(ROOT / "tests"))
+    import voc_case
+
+    def ms(fn, reps):
+        fn()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        return (time.perf_counter() - t0) / reps * 1e3
+
+    rng = np.random.default_rng(5)
+    w, h = 640, 480
+    ex = pkg.ORBextractor(2000, 1.2, 8, 20, 7, max_width=w, max_height=h, device=local)
+    m = pkg.ORBmatcher(0.6, device=local)
+    img = pkg.synth.frame(w, h, 70)
+    k1, d1 = ex(img)
+    k2, d2 = ex(np.roll(img, (3, 6), (0, 1)))
+    rows = {}
+    # node-restricted distance blocks of SearchByBoW / SearchForTriangulation (128 synthetic nodes)
+    node = lambda d: ((d[:, 0] >> 4).astype(np.int32) << 3) | (d[:, 5] >> 5).astype(np.int32)
+    blocks = ol.common_blocks(ol.featvec(node(d1)), ol.featvec(node(d2)))
+    pairs = int(np.sum(np.diff(blocks[0]).astype(np.int64) * np.diff(blocks[2])))
+    rows["bow_blocks"] = {"what": f"orbx_match_blocks, {len(k1)} x {len(k2)} features in {len(blocks[0]) - 1} shared nodes, {pairs} pairs",
+                          "gpu_ms": ms(lambda: m.match_blocks(d1, d2, *blocks), 50),
+                          "cpu_ms": ms(lambda: ol.block_distances(d1, d2, *blocks), 20)}
+    # distinctive descriptors of 2000 map points with 2-12 observations
+    sizes = rng.integers(2, 13, 2000).astype(np.int32)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    obs = pkg.synth.descriptors(int(off[-1]), 4)
+    rows["distinctive"] = {"what": f"orbx_distinctive, 2000 map points, {int(off[-1])} observations",
+                           "gpu_ms": ms(lambda: m.distinctive(obs, off), 50), "cpu_ms": ms(lambda: ol.distinctive(obs, off), 10)}
+    # frame epilogue + windowed search on the resident frame (SearchByProjection's size)
+    K4 = np.array([517.3, 516.5, 318.6, 255.3], np.float32)
+    D = np.array([0.2624, -0.9531, -0.0054, 0.0026, 1.1633], np.float32)
+    xy = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    rows["undistort"] = {"what": f"orbx_undistort_points, {len(xy)} keypoints, 5 coefficients",
+                         "gpu_ms": ms(lambda: pkg.undistort_points(xy, K4, D, device=local), 50),
+                         "cpu_ms": ms(lambda: ol.undistort_points(xy, K4, D), 50)}
+    fr = pkg.Frame(m)
+    b = np.array([0, w, 0, h], np.float32)
+    fr.set(k2, d2, b)
+    nq = 1000
+    i = rng.integers(0, len(k1), nq)
+    q = (xy[i], np.full(nq, 15, np.float32), np.maximum(k1["octave"][i] - 1, 0).astype(np.int32),
+         (k1["octave"][i] + 1).astype(np.int32), d1[i].copy())
+    grid = ol.Grid(k2, b)
+
+    def cpu_window():
+        for j in range(nq):
+            c = grid.query(q[0][j, 0], q[0][j, 1], q[1][j], int(q[2][j]), int(q[3][j]))
+            np.unpackbits(d2[c] ^ q[4][j], axis=1).sum(1)
+    rows["window_search"] = {"what": f"orbx_frame_match_window, {nq} queries on a resident {len(k2)}-keypoint frame, radius 15",
+                             "gpu_ms": ms(lambda: fr.match_window(*q), 50), "cpu_ms": ms(cpu_window, 2),
+                             "cpu_note": "oracle grid query per point + numpy popcount (Python loop)"}
+    # vocabulary descent: k = 10, L = 5 (about 10^4 words), levelsup 3
+    with tempfile.TemporaryDirectory() as td:
+        path = Path(td) / "voc.txt"
+        voc_case.write(path, 10, 5, 0, 0, seed=3, min_leaf_level=4)
+        ov = ol.Vocabulary(path)
+        parent, ndesc, weight, word, klsw = ov.export()
+        gv = pkg.Vocabulary(m, parent, ndesc, int(klsw[1]))
+        rows["vocabulary"] = {"what": f"orbx_vocabulary_descend, {len(d1)} descriptors, {len(parent)} nodes (k 10, L 5)",
+                              "gpu_ms": ms(lambda: gv.descend(d1, 3), 50), "cpu_ms": ms(lambda: ov.transform(d1, 3), 10),
+                              "cpu_note": "oracle transform incl. BowVector / FeatureVector assembly"}
+    return rows
+
+
 HAM_NQ, HAM_NDB = 10_000, 10_000_000   # BASELINE.json config 5
 
 
@@ -497,6 +570,8 @@ def _run_gpu(args, torch):
                "sample": f"12 s of the same {W}x{H} frames on {cores} threads ({n} frames), one extractor per thread",
                "single_thread_ms_per_frame": med_ms}
 
+    matcher_rows = run_matcher_rows(pkg, local) if (world == 1 and not args.skip_cpu and not args.skip_hamming) else None
+
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
@@ -505,7 +580,7 @@ def _run_gpu(args, torch):
                        "keypoints_per_frame": nkp / B, "parallelism": f"frame sharding x{world}, no collective"},
             "clocks": clocks, "e2e": e2e_obj, "gpu_launches": launches + (3 * args.steps if stereo else 0), "roofline": roof,
             "stages": stages, "stereo": stereo_obj,
-            "cpu_baseline": cpu, "hamming": hamming}
+            "cpu_baseline": cpu, "hamming": hamming, "matcher_rows": matcher_rows}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

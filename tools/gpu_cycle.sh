@@ -27,8 +27,14 @@ MCMD="python tools/match_probe.py"
 timeout 300 $MCMD > $OUT/match_probe.log 2>&1
 echo "match probe exit $?"; tail -5 $OUT/match_probe.log
 timeout 600 ncu --set full --clock-control none --import-source on \
-  -k regex:'bf2_kernel|bf2_reduce|window_kernel|grid_build|stereo_match|stereo_median|merge_kernel' --launch-count 12 \
+  -k regex:'bf2_kernel|window_kernel|grid_build|stereo_match|stereo_median|merge_kernel|block_distance|distinctive_kernel|undistort_keys|voc_descend' --launch-count 40 \
   -o $OUT/match_full -f $MCMD > $OUT/ncu_match.log 2>&1
 echo "ncu match exit $?"
 ncu -i $OUT/match_full.ncu-rep --page raw --csv > $OUT/match_full_raw.csv 2>/dev/null
+# the key-frame / frame-epilogue / vocabulary kernels come last in the probe: a capture of their own
+timeout 600 ncu --set full --clock-control none --import-source on \
+  -k regex:'block_distance|distinctive_kernel|undistort_keys|voc_descend|stereo_' --launch-count 14 \
+  -o $OUT/rows_full -f $MCMD > $OUT/ncu_rows.log 2>&1
+echo "ncu rows exit $?"
+ncu -i $OUT/rows_full.ncu-rep --page raw --csv > $OUT/rows_full_raw.csv 2>/dev/null
 ls -la $OUT

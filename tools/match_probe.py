@@ -65,6 +65,39 @@ def main():
     u, z, n = timed("stereo_match 1241x376 2000 kps", lambda: m.stereo_match(exl, exr, kl, dl, kr, dr, mbf, mb))
     print("  stereo matches:", n, "of", len(kl))
 
+    # node-restricted blocks, distinctive descriptors, frame epilogue, vocabulary descent
+    node = lambda d: ((d[:, 0] >> 4).astype(np.int64) << 3) | (d[:, 5] >> 5).astype(np.int64)
+
+    def featvec(n):
+        order = np.argsort(n, kind="stable")
+        ids, counts = np.unique(n, return_counts=True)
+        return ids, np.concatenate([[0], np.cumsum(counts)]).astype(np.int32), order.astype(np.int32)
+    (ia, oa, xa), (ib, ob, xb) = featvec(node(d1)), featvec(node(d2))
+    common, pa, pb = np.intersect1d(ia, ib, return_indices=True)
+    a_idx = np.concatenate([xa[oa[i]:oa[i + 1]] for i in pa]).astype(np.int32)
+    b_idx = np.concatenate([xb[ob[i]:ob[i + 1]] for i in pb]).astype(np.int32)
+    a_off = np.concatenate([[0], np.cumsum([oa[i + 1] - oa[i] for i in pa])]).astype(np.int32)
+    b_off = np.concatenate([[0], np.cumsum([ob[i + 1] - ob[i] for i in pb])]).astype(np.int32)
+    off, dist = timed("match_blocks 2000 x 2000 features, 128 nodes", lambda: m.match_blocks(d1, d2, a_off, a_idx, b_off, b_idx), reps=20)
+    print("  pairs:", len(dist))
+    sizes = rng.integers(2, 13, 2000).astype(np.int32)
+    ooff = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    obs = pkg.synth.descriptors(int(ooff[-1]), 4)
+    timed("distinctive 2000 map points x 2-12 observations", lambda: m.distinctive(obs, ooff), reps=20)
+    K4 = np.array([517.3, 516.5, 318.6, 255.3], np.float32)
+    D = np.array([0.2624, -0.9531, -0.0054, 0.0026, 1.1633], np.float32)
+    fr = pkg.Frame(m)
+    b4 = np.array(bounds, np.float32)
+    timed("frame_set 2000 keypoints, undistort + grid", lambda: fr.set(k2, d2, b4, K4, D), reps=20)
+    fr.set(k2, d2, b4)
+    timed("frame_match_window r=15 level+-1 (resident frame)",
+          lambda: fr.match_window(qxy, r, np.maximum(lv - 1, 0), lv + 1, d1), reps=20)
+    kk, LL = 10, 4
+    counts = [kk ** l for l in range(LL + 1)]
+    parent = np.concatenate([[0]] + [np.repeat(np.arange(sum(counts[:l - 1]), sum(counts[:l])), kk) for l in range(1, LL + 1)]).astype(np.int32)
+    voc = pkg.Vocabulary(m, parent, pkg.synth.descriptors(len(parent), 9), LL)
+    timed(f"vocabulary_descend 2000 descriptors, {len(parent)} nodes", lambda: voc.descend(d1, 2), reps=20)
+
 
 if __name__ == "__main__":
     main()
