@@ -452,4 +452,49 @@ int ref_search_by_projection_kf_scw(void* h, void* kfp, const float* Scw16, cons
   return n;
 }
 
+// SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (:1723-1851), Tracking::Relocalization's second pass
+int ref_search_by_projection_frame_kf(void* h, void* cur, void* kfp, const int* found, int nfound, float th, int orbDist,
+                                      float nnratio, int checkOri) {
+  Front* f = static_cast<Front*>(h);
+  std::set<MapPoint*> sFound;
+  for (int i = 0; i < nfound; i++) sFound.insert(f->points[found[i]]);
+  ORBmatcher matcher(nnratio, checkOri != 0);
+  return matcher.SearchByProjection(*static_cast<Frame*>(cur), static_cast<KeyFrame*>(kfp), sFound, th, orbDist);
+}
+
+// Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1164-1290); replace[i] = index of the key frame's point that point i
+// is to replace, or -1
+int ref_fuse_scw(void* h, void* kfp, const float* Scw16, const int* mps, int nmp, float th, int* replace) {
+  Front* f = static_cast<Front*>(h);
+  cv::Mat Scw(4, 4, CV_32F);
+  for (int i = 0; i < 16; i++) Scw.at<float>(i / 4, i % 4) = Scw16[i];
+  std::vector<MapPoint*> pts(nmp), rep(nmp, static_cast<MapPoint*>(nullptr));
+  for (int i = 0; i < nmp; i++) pts[i] = f->points[mps[i]];
+  ORBmatcher matcher(0.8f, true);
+  const int n = matcher.Fuse(static_cast<KeyFrame*>(kfp), Scw, pts, th, rep);
+  for (int i = 0; i < nmp; i++) replace[i] = point_index(f, rep[i]);
+  return n;
+}
+
+// SearchBySim3 (:1305-1560); matches12: pKF1->N entries, map point index or -1, read and updated like vpMatches12
+int ref_search_by_sim3(void* h, void* kf1, void* kf2, int* matches12, float s12, const float* R12, const float* t12, float th) {
+  Front* f = static_cast<Front*>(h);
+  KeyFrame *pKF1 = static_cast<KeyFrame*>(kf1), *pKF2 = static_cast<KeyFrame*>(kf2);
+  cv::Mat R(3, 3, CV_32F), t(3, 1, CV_32F);
+  for (int i = 0; i < 9; i++) R.at<float>(i / 3, i % 3) = R12[i];
+  for (int i = 0; i < 3; i++) t.at<float>(i) = t12[i];
+  std::vector<MapPoint*> vm(pKF1->N, static_cast<MapPoint*>(nullptr));
+  for (int i = 0; i < pKF1->N; i++) if (matches12[i] >= 0) vm[i] = f->points[matches12[i]];
+  ORBmatcher matcher(0.75f, true);
+  const int n = matcher.SearchBySim3(pKF1, pKF2, vm, s12, R, t, th);
+  for (int i = 0; i < pKF1->N; i++) matches12[i] = point_index(f, vm[i]);
+  return n;
+}
+
+// Hamming distance through whichever ORBmatcher this library carries (static member, :1901-1917)
+int ref_descriptor_distance(const uint8_t* a, const uint8_t* b) {
+  cv::Mat ma(1, 32, CV_8UC1, const_cast<uint8_t*>(a), 32), mb(1, 32, CV_8UC1, const_cast<uint8_t*>(b), 32);
+  return ORBmatcher::DescriptorDistance(ma, mb);
+}
+
 }  // extern "C"

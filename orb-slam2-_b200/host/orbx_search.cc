@@ -171,7 +171,7 @@ int SearchByProjection(orbx_matcher* m, const FrameView& F, unsigned char* hasMa
 int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* hasMapPoint, const float* qUV,
                        const float* qRadius, const int* qMinLevel, const int* qMaxLevel, const float* qUR,
                        const float* qAngle, const unsigned char* qDesc, int nQ, int thDist, bool checkOrientation,
-                       int* curMatch, const unsigned char* qHasObs) {
+                       int* curMatch, const unsigned char* qHasObs, std::vector<int>* cleared) {
   std::vector<float> qxy(qUV, qUV + 2 * (size_t)nQ), qr(qRadius, qRadius + nQ);
   std::vector<int> qmin(qMinLevel, qMinLevel + nQ), qmax(qMaxLevel, qMaxLevel + nQ);
   Candidates c;
@@ -208,6 +208,7 @@ int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* has
         for (size_t j = 0; j < rotHist[i].size(); j++) {
           curMatch[rotHist[i][j]] = -1;
           hasMapPoint[rotHist[i][j]] = 0;  // mvpMapPoints[...] = NULL (:1711)
+          if (cleared) cleared->push_back(rotHist[i][j]);
           nmatches--;
         }
   }

@@ -48,10 +48,12 @@ int SearchByProjection(orbx_matcher* m, const FrameView& F, unsigned char* hasMa
 // R/src/ORBmatcher.cpp:1564-1718 (last frame -> current frame) and :1723-1851 (keyframe -> frame) after
 // their projection prologues: per query (u,v), radius, level window, ur = u - mbf*invzc, the source
 // keypoint's angle and descriptor. curMatch[i2] = query index or -1. Returns nmatches.
+// cleared (optional): the keypoints whose mvpMapPoints entry the rotation check resets to NULL (:1704-1714), which a
+// caller holding pointers cannot tell from untouched entries by curMatch alone.
 int SearchByProjection(orbx_matcher* m, const FrameView& Cur, unsigned char* hasMapPoint, const float* qUV,
                        const float* qRadius, const int* qMinLevel, const int* qMaxLevel, const float* qUR,
                        const float* qAngle, const unsigned char* qDesc, int nQ, int thDist, bool checkOrientation,
-                       int* curMatch, const unsigned char* qHasObs = nullptr);
+                       int* curMatch, const unsigned char* qHasObs = nullptr, std::vector<int>* cleared = nullptr);
 
 // ---- bag-of-words restricted searches ---------------------------------------------------
 // A DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) flattened in map order: node ids ascending,

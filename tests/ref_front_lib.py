@@ -72,6 +72,10 @@ def lib():
         L.ref_map_point_is_bad.argtypes = [P, C.c_int]
         L.ref_scw_queries.argtypes = [P, P, P, P, C.c_int, P, C.c_int] + [P] * 5
         L.ref_search_by_projection_kf_scw.argtypes = [P, P, P, P, C.c_int, P, C.c_int]
+        L.ref_search_by_projection_frame_kf.argtypes = [P, P, P, P, C.c_int, C.c_float, C.c_int, C.c_float, C.c_int]
+        L.ref_fuse_scw.argtypes = [P, P, P, P, C.c_int, C.c_float, P]
+        L.ref_search_by_sim3.argtypes = [P, P, P, P, C.c_float, P, P, C.c_float]
+        L.ref_descriptor_distance.argtypes = [P, P]
         L.ref_set_allocator_mode(1)   # pointer order == creation order: the canonical DistributeOctTree tie-break
         _lib = L
     return _lib
@@ -79,6 +83,25 @@ def lib():
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(P)
+
+
+DROPIN_PATH = ROOT / "oracle" / "_ref" / "libdropin_front.so"
+
+
+def variant(path, name="ref_front_lib_dropin"):
+    """A second instance of this module bound to another build of the same harness: oracle/_ref/libdropin_front.so =
+    the reference's Frame / KeyFrame / MapPoint objects with R/src/ORBmatcher.cpp replaced by the product's
+    orb-slam2-_b200/host/ORBmatcher.cc over liborbx.so (needs a GPU)."""
+    import importlib.util
+    import sys
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, __file__)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    mod.LIB_PATH = Path(path)
+    return mod
 
 
 class Frame:
@@ -287,3 +310,26 @@ class Front:
         S = np.ascontiguousarray(Scw, np.float32).reshape(16)
         n = lib().ref_search_by_projection_kf_scw(self._h, kf._h, _p(S), _p(mps), len(mps), _p(out), th)
         return n, out
+
+    # ---- the remaining ORBmatcher members (relocalization, loop closing) ----
+    def search_by_projection_frame_kf(self, cur, kf, found, th, orb_dist, nnratio=0.9, check_ori=True):
+        found = np.ascontiguousarray(found, np.int32)
+        return lib().ref_search_by_projection_frame_kf(self._h, cur._h, kf._h, _p(found), len(found), th, orb_dist, nnratio,
+                                                       int(check_ori))
+
+    def fuse_scw(self, kf, Scw, mps, th):
+        mps = np.ascontiguousarray(mps, np.int32)
+        S = np.ascontiguousarray(Scw, np.float32).reshape(16)
+        rep = np.empty(max(len(mps), 1), np.int32)
+        n = lib().ref_fuse_scw(self._h, kf._h, _p(S), _p(mps), len(mps), th, _p(rep))
+        return n, rep[:len(mps)]
+
+    def search_by_sim3(self, kf1, kf2, matches12, s12, R12, t12, th):
+        out = np.ascontiguousarray(matches12, np.int32).copy()
+        R, t = np.ascontiguousarray(R12, np.float32).reshape(9), np.ascontiguousarray(t12, np.float32).reshape(3)
+        n = lib().ref_search_by_sim3(self._h, kf1._h, kf2._h, _p(out), s12, _p(R), _p(t), th)
+        return n, out
+
+    def descriptor_distance(self, a, b):
+        a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
+        return lib().ref_descriptor_distance(_p(a), _p(b))
