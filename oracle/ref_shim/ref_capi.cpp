@@ -25,17 +25,40 @@
 namespace {
 std::atomic<int> g_mode{0};
 char* g_arena = nullptr;
-std::atomic<size_t> g_off{0};
-constexpr size_t kArenaBytes = size_t(8) << 30;  // virtual reservation, touched on demand
+size_t g_arenaBytes = 0;
+size_t g_off = 0;                                // bump pointer, under g_lock
+constexpr size_t kChunk = size_t(2) << 20;       // physical memory goes back to the system chunk by chunk
+constexpr size_t kHeader = 64;                   // block size, kept in front of the payload (blocks are 64-byte aligned)
+int* g_live = nullptr;                           // live blocks per chunk
+std::atomic_flag g_lock = ATOMIC_FLAG_INIT;
 
+struct Lock {
+  Lock() { while (g_lock.test_and_set(std::memory_order_acquire)) {} }
+  ~Lock() { g_lock.clear(std::memory_order_release); }
+};
+
+// Addresses only ever grow (pointer order == creation order for the lifetime of the process); a chunk whose blocks
+// have all been freed and that the bump pointer has left behind is handed back with MADV_DONTNEED, so a long test
+// session keeps the canonical order without keeping the memory.
 void* arena_alloc(size_t n) {
   if (!g_arena) return nullptr;
-  const size_t need = (n + 63) & ~size_t(63);
-  const size_t off = g_off.fetch_add(need);
-  if (off + need > kArenaBytes) return nullptr;
-  return g_arena + off;
+  const size_t need = ((n + 63) & ~size_t(63)) + kHeader;
+  Lock lock;
+  if (g_off + need > g_arenaBytes) return nullptr;
+  const size_t off = g_off;
+  g_off += need;
+  for (size_t c = off / kChunk; c <= (off + need - 1) / kChunk; c++) g_live[c]++;
+  *reinterpret_cast<size_t*>(g_arena + off) = need;
+  return g_arena + off + kHeader;
 }
-inline bool in_arena(void* p) { return g_arena && (char*)p >= g_arena && (char*)p < g_arena + kArenaBytes; }
+inline bool in_arena(void* p) { return g_arena && (char*)p >= g_arena && (char*)p < g_arena + g_arenaBytes; }
+void arena_free(void* p) {
+  Lock lock;
+  const size_t off = (size_t)((char*)p - g_arena) - kHeader;
+  const size_t need = *reinterpret_cast<size_t*>(g_arena + off);
+  for (size_t c = off / kChunk; c <= (off + need - 1) / kChunk; c++)
+    if (--g_live[c] == 0 && (c + 1) * kChunk <= g_off) madvise(g_arena + c * kChunk, kChunk, MADV_DONTNEED);
+}
 }  // namespace
 
 void* operator new(size_t n) {
@@ -46,7 +69,11 @@ void* operator new(size_t n) {
   throw std::bad_alloc();
 }
 void* operator new[](size_t n) { return operator new(n); }
-void operator delete(void* p) noexcept { if (p && !in_arena(p)) std::free(p); }
+void operator delete(void* p) noexcept {
+  if (!p) return;
+  if (in_arena(p)) arena_free(p);
+  else std::free(p);
+}
 void operator delete[](void* p) noexcept { operator delete(p); }
 void operator delete(void* p, size_t) noexcept { operator delete(p); }
 void operator delete[](void* p, size_t) noexcept { operator delete(p); }
@@ -58,15 +85,24 @@ extern "C" {
 // 0 = system allocator (heap-address-dependent ties, as the reference ships); 1 = monotonic arena
 int ref_set_allocator_mode(int mode) {
   if (mode == 1 && !g_arena) {
-    void* p = mmap(nullptr, kArenaBytes, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
-    if (p == MAP_FAILED) return -1;
-    g_arena = static_cast<char*>(p);
+    // virtual reservation, touched on demand; smaller if the system refuses the large one
+    for (size_t bytes = size_t(256) << 30; bytes >= (size_t(8) << 30); bytes >>= 1) {
+      void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
+      if (p == MAP_FAILED) continue;
+      void* live = mmap(nullptr, (bytes / kChunk) * sizeof(int), PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+      if (live == MAP_FAILED) { munmap(p, bytes); continue; }
+      g_live = static_cast<int*>(live);
+      g_arenaBytes = bytes;
+      g_arena = static_cast<char*>(p);
+      break;
+    }
+    if (!g_arena) return -1;
   }
   g_mode.store(mode);
   return 0;
 }
 // bytes handed out by the arena so far
-uint64_t ref_arena_used(void) { return g_off.load(); }
+uint64_t ref_arena_used(void) { Lock lock; return g_off; }
 
 void* ref_extractor_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh) {
   return new ORB_SLAM2::ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);

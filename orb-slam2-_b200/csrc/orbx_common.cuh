@@ -1,6 +1,7 @@
 // Shared declarations for the liborbx.so translation units (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <mutex>
 #include <stdint.h>
 
 #include "../../include/orbx.h"
@@ -15,6 +16,27 @@ namespace orbx {
 // an early griddepcontrol.launch_dependents made the waiting CTAs of k+1 crowd out k's tail (512 frames: 3.58 ->
 // 4.27 ms) and is not used.
 #ifdef __CUDACC__
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the (kernel, device) pair and is shared by every host thread
+// and every handle of the process: two extractors of different sizes on two threads (the stereo Frame constructor
+// runs one per eye) must never lower it under each other's launches. Raise it monotonically under a lock; `state`
+// is one zero-initialised static per kernel.
+struct SmemLimit {
+  std::mutex mu;
+  size_t bytes[64] = {};
+};
+inline cudaError_t raise_dynamic_smem(const void* kernel, size_t bytes, SmemLimit* state) {
+  if (bytes <= 48 * 1024) return cudaSuccess;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  dev &= 63;
+  std::lock_guard<std::mutex> lock(state->mu);
+  if (bytes <= state->bytes[dev]) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e == cudaSuccess) state->bytes[dev] = bytes;
+  return e;
+}
+
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 template <typename... KArgs, typename... Args>

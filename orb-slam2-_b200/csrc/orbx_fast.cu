@@ -423,10 +423,9 @@ int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* can
   int words = 0;
   for (int l = 0; l < hGeom.nlevels; l++) words = max(words, fast_cell_words(hGeom.lv[l].wCell, hGeom.lv[l].hCell));
   const size_t smem = (size_t)words * 4 * kFastWarps;
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-  }
+  static SmemLimit limit;
+  cudaError_t e = raise_dynamic_smem(reinterpret_cast<const void*>(fast_cells_kernel), smem, &limit);
+  if (e != cudaSuccess) return (int)e;
   dim3 grid((hGeom.totalCells + kFastWarps - 1) / kFastWarps, nframes);
   launch_pdl(fast_cells_kernel, grid, dim3(kFastThreads), smem, s, pyr, hGeom, cand, candCount, overflow, words);
   return 0;

@@ -333,12 +333,9 @@ int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const ui
   int cap = 0;
   for (int l = 0; l < hGeom.nlevels; l++) cap = max(cap, hGeom.lv[l].keptCap);
   const size_t smem = octree_smem_bytes(cap);
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    configured = smem;
-  }
+  static SmemLimit limit;
+  cudaError_t e = raise_dynamic_smem(reinterpret_cast<const void*>(octree_kernel), smem, &limit);
+  if (e != cudaSuccess) return (int)e;
   dim3 grid(hGeom.nlevels, nframes);
   launch_pdl(octree_kernel, grid, dim3(nframes >= kOctBatchFrames ? kOctThreadsBatch : kOctThreads), smem, s, dGeom, cand, candCount, nodeScratch, kept, keptCount, cap);
   return 0;
@@ -352,7 +349,8 @@ int launch_octree_single(const uint32_t* cand, int n, int width, int height, int
   t.n = n; t.width = width; t.height = height; t.N = nfeat; t.cap = keptCap;
   t.wCell = wCell; t.hCell = hCell; t.nCols = nCols;
   const size_t smem = octree_smem_bytes(keptCap);
-  cudaError_t e = cudaFuncSetAttribute(octree_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static SmemLimit limit;
+  cudaError_t e = raise_dynamic_smem(reinterpret_cast<const void*>(octree_single_kernel), smem, &limit);
   if (e != cudaSuccess) return (int)e;
   octree_single_kernel<<<1, kOctThreads, smem, s>>>(t);
   return 0;

@@ -264,10 +264,9 @@ int stereo_items_per_keypoint(float maxScale) { return 2 * (int)ceilf(2.0f * max
 int launch_stereo(const StereoLevels& lv, const StereoArrays& a, int pairs, int maxNL, float mbf, float mb, cudaStream_t s) {
   if (pairs <= 0) return 0;
   const size_t smem = (size_t)lv.rows0 * sizeof(int);
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(stereo_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-  }
+  static SmemLimit limit;
+  cudaError_t e = raise_dynamic_smem(reinterpret_cast<const void*>(stereo_rows_kernel), smem, &limit);
+  if (e != cudaSuccess) return (int)e;
   stereo_rows_kernel<<<pairs, 1024, smem, s>>>(lv, a);
   if (maxNL > 0) stereo_match_kernel<<<dim3((maxNL + 7) / 8, pairs), 256, 0, s>>>(lv, a, mbf, mb);
   stereo_median_kernel<<<pairs, 1024, 0, s>>>(lv, a);

@@ -85,15 +85,18 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(P)
 
 
+# the reference's objects with the product's ORBmatcher.cc (matcher) / ORBmatcher.cc and ORBextractor.cc (front)
+DROPIN_MATCHER_PATH = ROOT / "oracle" / "_ref" / "libdropin_matcher.so"
 DROPIN_PATH = ROOT / "oracle" / "_ref" / "libdropin_front.so"
 
 
-def variant(path, name="ref_front_lib_dropin"):
+def variant(path, name=None):
     """A second instance of this module bound to another build of the same harness: oracle/_ref/libdropin_front.so =
     the reference's Frame / KeyFrame / MapPoint objects with R/src/ORBmatcher.cpp replaced by the product's
     orb-slam2-_b200/host/ORBmatcher.cc over liborbx.so (needs a GPU)."""
     import importlib.util
     import sys
+    name = name or "ref_front_lib_" + Path(path).stem
     if name in sys.modules:
         return sys.modules[name]
     spec = importlib.util.spec_from_file_location(name, __file__)

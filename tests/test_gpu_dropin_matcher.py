@@ -18,13 +18,24 @@ import ref_front_lib as rf
 synth = importlib.import_module("orb-slam2-_b200.synth")
 
 pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(not (rf.available() and rf.DROPIN_PATH.exists()), reason="oracle/_ref libraries not built")]
+              pytest.mark.skipif(not (rf.available() and rf.DROPIN_PATH.exists() and rf.DROPIN_MATCHER_PATH.exists()),
+                                 reason="oracle/_ref libraries not built")]
 
 FX, BASELINE = 435.2, 0.11
+# "matcher": only R/src/ORBmatcher.cpp replaced; "front": R/src/ORBextractor.cpp replaced as well, so the frames the
+# searches run on were extracted (and stereo-matched from the product's pyramids) on the device
+PATHS = {"matcher": rf.DROPIN_MATCHER_PATH, "front": rf.DROPIN_PATH}
+_current = {"path": rf.DROPIN_MATCHER_PATH}
+
+
+@pytest.fixture(autouse=True, scope="module", params=["matcher", "front"])
+def dropin_variant(request):
+    _current["path"] = PATHS[request.param]
+    return request.param
 
 
 def libs():
-    return rf, rf.variant(rf.DROPIN_PATH)
+    return rf, rf.variant(_current["path"])
 
 
 def same(a, b):
@@ -52,8 +63,11 @@ def test_the_two_libraries_differ_in_the_matcher_only():
         out = subprocess.run(["nm", "-D", flag, str(path)], capture_output=True, text=True).stdout
         return {l.split()[-1] for l in out.splitlines() if l.strip()}
     assert not any(s.startswith("orbx_") for s in syms(rf.LIB_PATH, "-u"))
+    need = syms(rf.DROPIN_MATCHER_PATH, "-u")
+    assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks"} <= need and "orbx_extract" not in need
     need = syms(rf.DROPIN_PATH, "-u")
-    assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks"} <= need
+    assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks", "orbx_extract"} <= need
+    assert not any("ExtractorNode" in s for s in syms(rf.DROPIN_PATH, "--defined-only"))   # no reference extractor inside
 
 
 def test_descriptor_distance_and_stereo_frames():
@@ -181,7 +195,7 @@ def test_search_by_projection_last_frame(kind, th, check_ori):
 
 
 @pytest.fixture(scope="module", params=["mono", "stereo"])
-def bow_pair(request):
+def bow_pair(request, dropin_variant):
     return [bow_case.build(m, stereo=request.param == "stereo") for m in libs()], request.param
 
 

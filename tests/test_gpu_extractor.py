@@ -337,3 +337,29 @@ def test_edge_inputs(pkg, oracle):
         ex(pkg.synth.frame(160, 120, 3))
     k, d = ex(pkg.synth.frame(640, 480, 3))                       # the handle stays usable after the refusal
     assert len(k) > 400
+
+
+@pytest.mark.gpu
+def test_extractors_of_different_sizes_on_two_threads(pkg):
+    """The stereo Frame constructor runs one extractor per eye on two threads (R/src/Frame.cpp:86-89). The opt-in
+    shared-memory limit of a kernel is a property of the process, not of the thread or the handle: a small extractor on
+    a second thread must not lower it under a large extractor on the first."""
+    import threading
+    img = pkg.synth.frame(752, 480, 21)
+    big = pkg.ORBextractor(3000, 1.2, 8, 20, 7, max_width=752, max_height=480)
+    k0, d0 = big(img)
+    out = {}
+
+    def worker():
+        small = pkg.ORBextractor(300, 1.2, 4, 20, 7, max_width=752, max_height=480)
+        out["small"] = small(img)
+        small.close()
+
+    for _ in range(2):
+        t = threading.Thread(target=worker)
+        t.start()
+        t.join()
+        k1, d1 = big(img)
+        assert np.array_equal(k0.view(np.uint8), k1.view(np.uint8)) and np.array_equal(d0, d1)
+    assert len(out["small"][0]) > 100
+    big.close()
