@@ -309,3 +309,47 @@ def test_search_by_projection_relocalization(stereo, th, orb_dist, check_ori):
         out.append((n, cur.map_points()))
     assert out[0][0] > 150
     same(out[0], out[1])
+
+
+def test_three_threads_use_the_matcher_at_once():
+    """Tracking, LocalMapping and LoopClosing construct ORBmatcher objects on their own threads and search concurrently
+    (SURVEY.md 8b). The drop-in keeps one device handle per host thread; results must not depend on what the other
+    threads are doing."""
+    import threading
+    ref, drop = libs()
+    rounds = 3
+
+    def jobs(m):
+        a = [T for T in (_frame_pair(m, "mono") for _ in range(rounds))]
+        b = [bow_case.build_fuse(m, False) for _ in range(rounds)]
+        c = [bow_case.build(m, stereo=False) for _ in range(rounds)]
+        return [
+            [lambda s=s: (s[0].search_by_projection_frame(s[2], s[1], 15.0, True, 0.9, True), s[2].map_points()) for s in a],
+            [lambda s=s: (s.front.fuse(s.kf2, s.src, 3.0), s.kf2.map_points()) for s in b],
+            [lambda s=s: (s.front.search_by_bow_kf_kf(s.kf1, s.kf2, 0.75, True),
+                          s.front.search_for_triangulation(s.kf1, s.kf2, s.F12, False, 0.6, True)) for s in c],
+        ]
+
+    expect = [[fn() for fn in lane] for lane in jobs(ref)]
+    lanes = jobs(drop)
+    got = [[None] * rounds for _ in lanes]
+    errors = []
+    start = threading.Barrier(len(lanes))
+
+    def run(k):
+        try:
+            start.wait()
+            for r, fn in enumerate(lanes[k]):
+                got[k][r] = fn()
+        except BaseException as e:   # noqa: BLE001 - reported by the main thread
+            errors.append(e)
+
+    threads = [threading.Thread(target=run, args=(k,)) for k in range(len(lanes))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for k in range(len(lanes)):
+        for r in range(rounds):
+            same(expect[k][r], got[k][r])
