@@ -52,6 +52,24 @@ bool plan_chunks(int total, int chunk, ChunkPlan* p) {
   return true;
 }
 
+// The blocking call pays the H2D of its first chunk before any kernel runs and the kernels + D2H of its last chunk
+// after the last copy: ramp the chunk size up at the head and down at the tail (chunk/4, chunk/2, chunk ... chunk,
+// chunk/2, chunk/4) so that both exposed pieces are a quarter chunk. Small chunks use the GPU less well, but they
+// run next to full-sized ones on the other lanes.
+bool plan_chunks_tapered(int total, int chunk, ChunkPlan* p) {
+  const int q = chunk / 4, hq = chunk / 2;
+  if (q < 8 || total < 3 * chunk) return plan_chunks(total, chunk, p);
+  const int body = total - 2 * (q + hq);
+  if (2 + (body + chunk - 1) / chunk + 2 > ChunkTrace_kMaxChunks) return false;
+  int f0 = 0;
+  p->add(f0, q); f0 += q;
+  p->add(f0, hq); f0 += hq;
+  for (int left = body; left > 0; left -= chunk) { const int c = std::min(chunk, left); p->add(f0, c); f0 += c; }
+  p->add(f0, hq); f0 += hq;
+  p->add(f0, q);
+  return true;
+}
+
 // ORBX_TRACE=1: per-chunk device timeline of orbx_extract_batch (H2D / kernels / D2H begin-end and the host time of
 // the submit), printed to stderr after the call. A debugging aid for the host-buffer pipeline; off by default.
 struct ChunkTrace {
@@ -512,7 +530,7 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
   }
   ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
   ChunkPlan plan;
-  if (!plan_chunks(count, h->chunkFrames > 0 ? h->chunkFrames : chunk_frames(width, height), &plan)) { set_error("batch of %d frames needs more than %d chunks (raise ORBX_CHUNK)", count, ChunkTrace_kMaxChunks); return ORBX_ERR_ARG; }
+  if (!plan_chunks_tapered(count, h->chunkFrames > 0 ? h->chunkFrames : chunk_frames(width, height), &plan)) { set_error("batch of %d frames needs more than %d chunks (raise ORBX_CHUNK)", count, ChunkTrace_kMaxChunks); return ORBX_ERR_ARG; }
   const int nchunks = plan.n;
   const int nlanes = std::min(nchunks, h->laneCount > 0 ? h->laneCount : lane_count());
   int rc;

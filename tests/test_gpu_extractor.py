@@ -363,3 +363,26 @@ def test_extractors_of_different_sizes_on_two_threads(pkg):
         assert np.array_equal(k0.view(np.uint8), k1.view(np.uint8)) and np.array_equal(d0, d1)
     assert len(out["small"][0]) > 100
     big.close()
+
+
+@pytest.mark.gpu
+def test_tapered_chunks_equal_single(pkg):
+    """Batches of three chunks or more are cut with a ramp (chunk/4, chunk/2, chunk ..., chunk/2, chunk/4: less exposed
+    fill and drain per blocking call); every frame must still get the result of a single-frame call."""
+    B = 150
+    frames = np.stack([pkg.synth.frame(320, 240, 500 + i) for i in range(B)])
+    ex = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240, max_batch=256)
+    ex.set_pipeline(chunk_frames=32, lanes=4)   # 8 16 32 32 32 6 16 8
+    cap = 700
+    kps = pkg.pinned_empty((B, cap), pkg.KP_DTYPE)
+    desc = pkg.pinned_empty((B, cap, 32), np.uint8)
+    n = np.zeros(B, np.int32)
+    single = pkg.ORBextractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240)
+    for _ in range(2):   # the second call reuses lanes that last held a chunk of another size
+        kps[:] = 0
+        ex.extract_batch_into(frames, kps, desc, n)
+        for f in list(range(0, B, 7)) + [7, 8, 23, 24, 55, 56, 119, 120, 125, 126, 141, 142, 149]:
+            sk, sd = single(frames[f])
+            assert n[f] == len(sk)
+            assert np.array_equal(kps[f, :n[f]].view(np.uint8), sk.view(np.uint8)), f
+            assert np.array_equal(desc[f, :n[f]], sd), f
