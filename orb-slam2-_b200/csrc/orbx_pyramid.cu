@@ -73,6 +73,14 @@ __device__ __forceinline__ void resize_hrow4(uint32_t w0, uint32_t w1, uint32_t 
 #endif
 constexpr int kResizeRows = ORBX_RESIZE_ROWS;    // destination rows per thread (source rows are reused between them)
 constexpr int kResizeBands = ORBX_RESIZE_BANDS;  // threadIdx.y
+#ifndef ORBX_RESIZE_ROWS_SMALL
+#define ORBX_RESIZE_ROWS_SMALL 2
+#endif
+constexpr int kResizeRowsSmall = ORBX_RESIZE_ROWS_SMALL;
+#ifndef ORBX_RESIZE_FILL
+#define ORBX_RESIZE_FILL 1536
+#endif
+constexpr long long kResizeFillThreads = 148LL * ORBX_RESIZE_FILL;  // fewer threads than this at kResizeRows cannot fill the GPU
 
 // Requires non-negative weights (build_resize_groups checks both axes; always true when shrinking): then
 // (c * (h >> 4)) >> 16 == umulhi(c << 16, h >> 4), two IMAD.HI per pixel instead of multiply + shift twice, and
@@ -82,13 +90,18 @@ constexpr int kResizeBands = ORBX_RESIZE_BANDS;  // threadIdx.y
 #ifndef ORBX_RESIZE_MINB
 #define ORBX_RESIZE_MINB 12
 #endif
+// ROWS = destination rows per thread. A thread loads its source rows one after the other (each use waits for its
+// load), so a launch that cannot fill the GPU anyway -- one frame, or the small levels of a small batch -- is bound by
+// that chain: kResizeRowsSmall rows per thread make four times the threads with a quarter of the chain, at the
+// price of re-interpolating more shared source rows (1.5 instead of 1.33 per destination row).
+template <int ROWS>
 __global__ void __launch_bounds__(32 * kResizeBands, ORBX_RESIZE_MINB)
 resize4_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int srcPitch, int sh,
                uint8_t* __restrict__ dst, long long dstFrameStride, int dstPitch, int dw, int dh,
                const ResizeGroup* __restrict__ xg, const ResizeTap* __restrict__ yt) {
   pdl_wait();
   const int gx = blockIdx.x * 32 + threadIdx.x;  // group of 4 destination pixels
-  const int dy0 = (blockIdx.y * kResizeBands + threadIdx.y) * kResizeRows;
+  const int dy0 = (blockIdx.y * kResizeBands + threadIdx.y) * ROWS;
   if (4 * gx >= dw || dy0 >= dh) return;
   const uint8_t* S = src + (long long)blockIdx.z * srcFrameStride;
   uint8_t* D = dst + (long long)blockIdx.z * dstFrameStride + 4 * gx + (long long)dy0 * dstPitch;
@@ -123,7 +136,7 @@ resize4_kernel(const uint8_t* __restrict__ src, long long srcFrameStride, int sr
   // across the warp, so the reuse branches do not diverge)
   int ia = -1, ib = -1;
   uint32_t ha[4] = {0, 0, 0, 0}, hb[4] = {0, 0, 0, 0};
-  const int dyEnd = min(dy0 + kResizeRows, dh);
+  const int dyEnd = min(dy0 + ROWS, dh);
   uint2 tyNext = *reinterpret_cast<const uint2*>(&yt[dy0]);
   for (int dy = dy0; dy < dyEnd; dy++) {
     const uint2 ty = tyNext;  // (p0 | p1 << 16, c0 | c1 << 16), all >= 0
@@ -164,10 +177,18 @@ void launch_resize(const uint8_t* src, long long srcFrameStride, int srcPitch, i
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)srcPitch | (uintptr_t)srcFrameStride |
                          reinterpret_cast<uintptr_t>(dst) | (uintptr_t)dstPitch | (uintptr_t)dstFrameStride) & 3) == 0;
   if (t.xg && aligned) {
-    const int rowsPerCta = kResizeRows * kResizeBands;
-    dim3 grid(((dw + 3) / 4 + 31) / 32, (dh + rowsPerCta - 1) / rowsPerCta, nframes);
-    launch_pdl(resize4_kernel, grid, dim3(32, kResizeBands), 0, s, src, srcFrameStride, srcPitch, sh, dst, dstFrameStride,
-               dstPitch, dw, dh, t.xg, t.yt);
+    const long long threadsAtFull = (long long)((dw + 3) / 4) * ((dh + kResizeRows - 1) / kResizeRows) * nframes;
+    if (threadsAtFull >= kResizeFillThreads) {
+      const int rowsPerCta = kResizeRows * kResizeBands;
+      dim3 grid(((dw + 3) / 4 + 31) / 32, (dh + rowsPerCta - 1) / rowsPerCta, nframes);
+      launch_pdl(resize4_kernel<kResizeRows>, grid, dim3(32, kResizeBands), 0, s, src, srcFrameStride, srcPitch, sh, dst,
+                 dstFrameStride, dstPitch, dw, dh, t.xg, t.yt);
+    } else {
+      const int rowsPerCta = kResizeRowsSmall * kResizeBands;
+      dim3 grid(((dw + 3) / 4 + 31) / 32, (dh + rowsPerCta - 1) / rowsPerCta, nframes);
+      launch_pdl(resize4_kernel<kResizeRowsSmall>, grid, dim3(32, kResizeBands), 0, s, src, srcFrameStride, srcPitch, sh, dst,
+                 dstFrameStride, dstPitch, dw, dh, t.xg, t.yt);
+    }
   } else {
     dim3 grid((dw + 31) / 32, (dh + 7) / 8, nframes);
     launch_pdl(resize_kernel, grid, dim3(32, 8), 0, s, src, srcFrameStride, srcPitch, dst, dstFrameStride, dstPitch, dw, dh,

@@ -386,3 +386,19 @@ def test_tapered_chunks_equal_single(pkg):
             assert n[f] == len(sk)
             assert np.array_equal(kps[f, :n[f]].view(np.uint8), sk.view(np.uint8)), f
             assert np.array_equal(desc[f, :n[f]], sd), f
+
+
+@pytest.mark.gpu
+def test_resize_row_variants_agree(pkg):
+    """The pyramid kernel runs with 8 destination rows per thread when a launch fills the GPU and with 2 when it cannot
+    (one frame, or the small levels of a small batch): a 48-frame batch (8 rows on the large levels) must give every
+    frame the result of a single-frame call (2 rows everywhere)."""
+    B = 48
+    frames = np.stack([pkg.synth.frame(640, 480, 900 + i) for i in range(B)])
+    ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480, max_batch=B)
+    ex.set_pipeline(chunk_frames=B, lanes=1)
+    res = ex.extract_batch(list(frames))
+    single = pkg.ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    for f in range(0, B, 5):
+        sk, sd = single(frames[f])
+        assert np.array_equal(res[f][0].view(np.uint8), sk.view(np.uint8)) and np.array_equal(res[f][1], sd), f
