@@ -38,16 +38,22 @@ static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint must 
 
 // One matcher handle (stream + device scratch) per host thread: ORBmatcher objects are stack locals used from the
 // Tracking, LocalMapping and LoopClosing threads at the same time (threading).
+struct ThreadHandle {
+  orbx_matcher* h;
+  ThreadHandle() : h(nullptr) {}
+  ~ThreadHandle() { if (h) orbx_matcher_destroy(h); }   // a thread that ends gives its stream and scratch back
+};
+
 orbx_matcher* Handle() {
-  static thread_local orbx_matcher* h = nullptr;
-  if (!h) {
+  static thread_local ThreadHandle t;
+  if (!t.h) {
     const char* dev = std::getenv("ORBX_DEVICE");
-    if (orbx_matcher_create(dev ? std::atoi(dev) : 0, &h) != ORBX_OK) {
+    if (orbx_matcher_create(dev ? std::atoi(dev) : 0, &t.h) != ORBX_OK) {
       std::fprintf(stderr, "ORBmatcher: %s\n", orbx_last_error());
       std::abort();   // no CPU fallback
     }
   }
-  return h;
+  return t.h;
 }
 
 const orbx_keypoint* Keys(const std::vector<cv::KeyPoint>& v) {
