@@ -25,6 +25,7 @@
 
 #include "orbx.h"
 #include "orbx_search.h"
+#include "orbx_thread.h"
 
 namespace ORB_SLAM2 {
 
@@ -36,25 +37,7 @@ namespace {
 
 static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint must be the 28-byte record of include/orbx.h");
 
-// One matcher handle (stream + device scratch) per host thread: ORBmatcher objects are stack locals used from the
-// Tracking, LocalMapping and LoopClosing threads at the same time (threading).
-struct ThreadHandle {
-  orbx_matcher* h;
-  ThreadHandle() : h(nullptr) {}
-  ~ThreadHandle() { if (h) orbx_matcher_destroy(h); }   // a thread that ends gives its stream and scratch back
-};
-
-orbx_matcher* Handle() {
-  static thread_local ThreadHandle t;
-  if (!t.h) {
-    const char* dev = std::getenv("ORBX_DEVICE");
-    if (orbx_matcher_create(dev ? std::atoi(dev) : 0, &t.h) != ORBX_OK) {
-      std::fprintf(stderr, "ORBmatcher: %s\n", orbx_last_error());
-      std::abort();   // no CPU fallback
-    }
-  }
-  return t.h;
-}
+orbx_matcher* Handle() { return orbx_host::ThreadMatcher(); }   // one device handle per host thread (orbx_thread.h)
 
 const orbx_keypoint* Keys(const std::vector<cv::KeyPoint>& v) {
   return v.empty() ? nullptr : reinterpret_cast<const orbx_keypoint*>(&v[0]);

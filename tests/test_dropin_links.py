@@ -22,7 +22,7 @@ def test_symbols():
     need = _syms(rf.DROPIN_MATCHER_PATH, "-u")
     assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks"} <= need and "orbx_extract" not in need
     need = _syms(rf.DROPIN_PATH, "-u")
-    assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks", "orbx_extract"} <= need
+    assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks", "orbx_extract", "orbx_stereo_match"} <= need
     assert not any("ExtractorNode" in s for s in _syms(rf.DROPIN_PATH, "--defined-only"))
 
 

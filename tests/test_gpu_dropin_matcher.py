@@ -22,8 +22,9 @@ pytestmark = [pytest.mark.gpu,
                                  reason="oracle/_ref libraries not built")]
 
 FX, BASELINE = 435.2, 0.11
-# "matcher": only R/src/ORBmatcher.cpp replaced; "front": R/src/ORBextractor.cpp replaced as well, so the frames the
-# searches run on were extracted (and stereo-matched from the product's pyramids) on the device
+# "matcher": only R/src/ORBmatcher.cpp replaced; "front": R/src/ORBextractor.cpp and Frame::ComputeStereoMatches replaced
+# as well (host/ORBextractor.cc, host/FrameStereo.cc), so the frames the searches run on were extracted and
+# stereo-matched on the device
 PATHS = {"matcher": rf.DROPIN_MATCHER_PATH, "front": rf.DROPIN_PATH}
 _current = {"path": rf.DROPIN_MATCHER_PATH}
 
@@ -66,7 +67,7 @@ def test_the_two_libraries_differ_in_the_matcher_only():
     need = syms(rf.DROPIN_MATCHER_PATH, "-u")
     assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks"} <= need and "orbx_extract" not in need
     need = syms(rf.DROPIN_PATH, "-u")
-    assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks", "orbx_extract"} <= need
+    assert {"orbx_matcher_create", "orbx_match_window", "orbx_match_blocks", "orbx_extract", "orbx_stereo_match"} <= need
     assert not any("ExtractorNode" in s for s in syms(rf.DROPIN_PATH, "--defined-only"))   # no reference extractor inside
 
 
@@ -353,3 +354,16 @@ def test_three_threads_use_the_matcher_at_once():
     for k in range(len(lanes)):
         for r in range(rounds):
             same(expect[k][r], got[k][r])
+
+
+@pytest.mark.parametrize("w,h,nf,seed", [(752, 480, 1200, 5), (1241, 376, 2000, 6), (640, 480, 1000, 7)])
+def test_stereo_frame_constructor(w, h, nf, seed, dropin_variant):
+    """Frame::Frame(imLeft, imRight, ...) (R/src/Frame.cpp:67-128): in the "front" library both extractions and
+    Frame::ComputeStereoMatches (host/FrameStereo.cc -> orbx_stereo_match on the device pyramids) are the product's."""
+    left, right = synth.stereo_pair(w, h, seed)
+    out = []
+    for m in libs():
+        F = m.Front(nf, fx=FX, fy=FX, cx=w / 2, cy=h / 2, bf=FX * BASELINE).frame_stereo(left, right)
+        out.append((F.keys, F.keys_un, F.desc, F.keys_right, F.desc_right, F.u_right, F.depth))
+    assert (out[0][5] >= 0).sum() > 100
+    same(out[0], out[1])
