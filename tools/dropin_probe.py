@@ -81,9 +81,42 @@ CASES = [
 ]
 
 
+def frame_rows():
+    """Frame::Frame itself (R/src/Frame.cpp:67-128, :187-250) in libref_front.so and in libdropin_front.so, where
+    ORBextractor.cpp and Frame::ComputeStereoMatches are the product's: extraction of the image(s) (the reference runs
+    the two eyes on two threads), stereo matching, undistortion, grid assignment."""
+    full = rf.variant(rf.DROPIN_PATH)
+    out = {}
+    for name, (w, h, nf, stereo) in {"Frame::Frame mono 640x480/1000": (640, 480, 1000, False),
+                                     "Frame::Frame stereo 752x480/1200": (752, 480, 1200, True),
+                                     "Frame::Frame stereo 1241x376/2000": (1241, 376, 2000, True)}.items():
+        if stereo:
+            left, right = T.synth.stereo_pair(w, h, 5)
+        else:
+            left = right = T.synth.frame(w, h, 5)
+        ms = {"reference": [], "dropin": []}
+        n = {}
+        for label, m in (("reference", rf), ("dropin", full)):
+            front = m.Front(nf, fx=435.2, fy=435.2, cx=w / 2, cy=h / 2, bf=47.9)
+            for rep in range(REPS + 1):
+                t0 = time.perf_counter()
+                hnd = (m.lib().ref_frame_stereo(front._h, rf._p(left), rf._p(right), w, h, left.strides[0]) if stereo
+                       else m.lib().ref_frame_mono(front._h, rf._p(left), w, h, left.strides[0]))
+                t = (time.perf_counter() - t0) * 1e3
+                F = m.Frame(front, hnd)
+                if rep:
+                    ms[label].append(t)
+                n[label] = (F.N, int((F.u_right >= 0).sum()))
+                del F
+        assert n["reference"] == n["dropin"], (name, n)
+        out[name] = {"keypoints": n["reference"][0], "stereo_matches": n["reference"][1],
+                     "reference_ms": round(float(np.median(ms["reference"])), 3), "dropin_ms": round(float(np.median(ms["dropin"])), 3)}
+    return out
+
+
 def main():
     drop = rf.variant(rf.DROPIN_MATCHER_PATH)
-    rows = {}
+    rows = frame_rows()
     for name, make in CASES:
         if name == "SearchByProjection(F,MapPoints)":
             continue   # its scenario builder runs the search itself; covered by the tests, not timed here
