@@ -121,6 +121,14 @@ int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_imgs, int32_t 
  * device->host copy of level `level` of frame `frame` of the last batch. */
 int orbx_level_size(const orbx_extractor* h, int32_t level, int32_t* width, int32_t* height);
 int orbx_get_level(orbx_extractor* h, int32_t frame, int32_t level, uint8_t* dst, size_t dst_stride);
+/* Levels 1 .. nlevels-1 of frame `frame` of the last batch in one go (what the C++ ORBextractor mirror fills
+ * mvImagePyramid from after every operator() call): level l lands at dst + offsets[l] with row pitch pitches[l] (the
+ * device planes as they lie, padding included; offsets[0] / pitches[0] are not written: level 0 is the caller's
+ * image). The copies are queued back to back and waited for once; with page-locked dst (orbx_host_alloc) they are
+ * DMA transfers with no staging. *bytes = size dst must have; dst == NULL only reports offsets, pitches and *bytes.
+ * offsets / pitches: ORBX_MAX_LEVELS entries. */
+int orbx_get_pyramid(orbx_extractor* h, int32_t frame, uint8_t* dst, size_t dst_bytes, size_t* offsets,
+                     int32_t* pitches, size_t* bytes);
 
 /* Introspection for the parity tests (not used by the C++ mirror classes). */
 int orbx_get_blurred_level(orbx_extractor* h, int32_t frame, int32_t level, uint8_t* dst, size_t dst_stride);

@@ -47,6 +47,7 @@ SIGNATURES = {
     "orbx_extract_batch_device": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _sz, _sz, _vp, _vp, _i32, _vp, _vp]),
     "orbx_level_size": (C.c_int, [_vp, _i32, C.POINTER(_i32), C.POINTER(_i32)]),
     "orbx_get_level": (C.c_int, [_vp, _i32, _i32, _vp, _sz]),
+    "orbx_get_pyramid": (C.c_int, [_vp, _i32, _vp, _sz, _vp, _vp, _vp]),
     "orbx_get_blurred_level": (C.c_int, [_vp, _i32, _i32, _vp, _sz]),
     "orbx_get_level_candidates": (C.c_int, [_vp, _i32, _i32, _vp, _i32, C.POINTER(_i32)]),
     "orbx_launch_count": (_i64, [_vp]),

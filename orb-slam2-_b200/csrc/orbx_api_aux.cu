@@ -71,6 +71,33 @@ int orbx_get_level(orbx_extractor* h, int32_t frame, int32_t level, uint8_t* dst
   return copy_plane_out(h, src, L.pitch, L.w, L.h, dst, dst_stride);
 }
 
+int orbx_get_pyramid(orbx_extractor* h, int32_t frame, uint8_t* dst, size_t dst_bytes, size_t* offsets, int32_t* pitches,
+                     size_t* bytes) {
+  int rc = check_result(h, frame, 0);
+  if (rc) return rc;
+  if (!offsets || !pitches || !bytes) { set_error("null argument"); return ORBX_ERR_ARG; }
+  const FrameSetGeom& g = h->lane[0].geom;
+  size_t total = 0;
+  for (int l = 1; l < g.nlevels; l++) {
+    offsets[l] = total;
+    pitches[l] = g.lv[l].pitch;
+    total += (size_t)g.lv[l].pitch * g.lv[l].h;
+  }
+  *bytes = total;
+  if (!dst) return ORBX_OK;
+  if (dst_bytes < total) { set_error("pyramid needs %zu bytes, dst has %zu", total, dst_bytes); return ORBX_ERR_CAPACITY; }
+  ORBX_CUDA_TRY(cudaSetDevice(h->params.device));
+  cudaStream_t s = h->lane[0].stream;
+  const uint8_t* arena = static_cast<const uint8_t*>(h->lane[0].pyrArena.p);
+  for (int l = 1; l < g.nlevels; l++) {
+    const LevelGeom& L = g.lv[l];
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dst + offsets[l], arena + L.planeOff + (long long)frame * L.planeBytes,
+                                  (size_t)L.pitch * L.h, cudaMemcpyDeviceToHost, s));
+  }
+  ORBX_CUDA_TRY(cudaStreamSynchronize(s));
+  return ORBX_OK;
+}
+
 int orbx_get_blurred_level(orbx_extractor* h, int32_t frame, int32_t level, uint8_t* dst, size_t dst_stride) {
   int rc = check_result(h, frame, level);
   if (rc) return rc;

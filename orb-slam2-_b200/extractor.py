@@ -150,6 +150,21 @@ class ORBextractor:
         check(fn(self._h, frame, level, ptr(out), w))
         return out
 
+    def image_pyramid(self, frame=0):
+        """Levels 1 .. nlevels-1 of `frame` of the last batch in one batch of copies (orbx_get_pyramid): a list of
+        (h, w) views into one buffer, row stride = the device pitch. Entry 0 is None (level 0 is the caller's image)."""
+        off = (C.c_size_t * 16)()
+        pitch = (C.c_int32 * 16)()
+        nbytes = C.c_size_t()
+        check(lib().orbx_get_pyramid(self._h, frame, None, 0, off, pitch, C.byref(nbytes)))
+        buf = np.empty(max(nbytes.value, 1), np.uint8)
+        check(lib().orbx_get_pyramid(self._h, frame, ptr(buf), buf.size, off, pitch, C.byref(nbytes)))
+        out = [None]
+        for l in range(1, self.nlevels):
+            w, h = self.level_size(l)
+            out.append(np.lib.stride_tricks.as_strided(buf[off[l]:], shape=(h, w), strides=(pitch[l], 1), writeable=False))
+        return out
+
     @property
     def mvImagePyramid(self):
         return [self.image_pyramid_level(l) for l in range(self.nlevels)]

@@ -25,10 +25,14 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels,
                            int _iniThFAST, int _minThFAST):
     nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels),
     iniThFAST(_iniThFAST), minThFAST(_minThFAST), mpHandle(NULL), mnDevice(0), mnMaxWidth(0), mnMaxHeight(0),
-    mbPyramidReadback(true)
+    mbPyramidReadback(true), mpPyramidHost(NULL), mnPyramidBytes(0)
 {
     if(const char* dev = std::getenv("ORBX_DEVICE"))
         mnDevice = std::atoi(dev);
+    // ORBX_PYRAMID_READBACK=0: leave mvImagePyramid[1..] empty (nothing reads it once Frame::ComputeStereoMatches is
+    // host/FrameStereo.cc, which works on the device pyramids); SetPyramidReadback() overrides
+    if(const char* rb = std::getenv("ORBX_PYRAMID_READBACK"))
+        mbPyramidReadback = std::atoi(rb) != 0;
 
     // The tables only depend on the ctor arguments; a 64x64 probe handle computes them with the library's
     // arithmetic (the reference's own types and operation order, R/src/ORBextractor.cpp:435-500).
@@ -58,6 +62,8 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels,
 ORBextractor::~ORBextractor()
 {
     orbx_extractor_destroy(mpHandle);
+    if(mpPyramidHost)
+        orbx_host_free(mpPyramidHost);
 }
 
 void ORBextractor::SetDevice(int device)
@@ -132,18 +138,36 @@ void ORBextractor::operator()( cv::InputArray _image, cv::InputArray _mask, std:
     keys.resize(n);
     _keypoints.swap(keys);             // clear + fill (:1153-1186)
 
-    // mvImagePyramid: level 0 aliases the caller's image (:1223); the others are copied back on demand
+    // mvImagePyramid: level 0 aliases the caller's image (:1223). The other levels come back in one batch of DMA
+    // copies into a page-locked buffer this extractor owns, and the cv::Mat headers alias that buffer (row step = the
+    // device pitch): like the reference's, they are valid until the next operator() call on this extractor.
     mvImagePyramid[0] = image;
-    if(mbPyramidReadback)
+    if(mbPyramidReadback && nlevels > 1)
     {
+        size_t offsets[ORBX_MAX_LEVELS], bytes = 0;
+        int pitches[ORBX_MAX_LEVELS];
+        if(orbx_get_pyramid(mpHandle, 0, NULL, 0, offsets, pitches, &bytes) != ORBX_OK)
+            Fail("orbx_get_pyramid");
+        if(bytes > mnPyramidBytes)
+        {
+            if(mpPyramidHost)
+                orbx_host_free(mpPyramidHost);
+            mpPyramidHost = NULL;
+            mnPyramidBytes = 0;
+            void* p = NULL;
+            if(orbx_host_alloc(mnDevice, bytes, &p) != ORBX_OK)
+                Fail("orbx_host_alloc");
+            mpPyramidHost = static_cast<unsigned char*>(p);
+            mnPyramidBytes = bytes;
+        }
+        if(orbx_get_pyramid(mpHandle, 0, mpPyramidHost, mnPyramidBytes, offsets, pitches, &bytes) != ORBX_OK)
+            Fail("orbx_get_pyramid");
         for(int level=1; level<nlevels; ++level)
         {
             int w = 0, h = 0;
             if(orbx_level_size(mpHandle, level, &w, &h) != ORBX_OK)
                 Fail("orbx_level_size");
-            mvImagePyramid[level].create(h, w, CV_8UC1);
-            if(orbx_get_level(mpHandle, 0, level, mvImagePyramid[level].data, (size_t)mvImagePyramid[level].step) != ORBX_OK)
-                Fail("orbx_get_level");
+            mvImagePyramid[level] = cv::Mat(h, w, CV_8UC1, mpPyramidHost + offsets[level], (size_t)pitches[level]);
         }
     }
 }

@@ -57,8 +57,10 @@ public:
     }
 
     // Host copies of the pyramid levels of the last image (level 0 aliases the caller's image, like
-    // R/src/ORBextractor.cpp:1223). Frame::ComputeStereoMatches reads them; monocular / RGB-D callers
-    // never do and can switch the read-back off to save the device->host copy.
+    // R/src/ORBextractor.cpp:1223; the others alias a page-locked buffer of this extractor and are valid until
+    // its next operator() call). Only the reference's own Frame::ComputeStereoMatches reads them: monocular /
+    // RGB-D callers, and stereo callers that link host/FrameStereo.cc, switch the read-back off
+    // (SetPyramidReadback(false) or ORBX_PYRAMID_READBACK=0) and save the device->host copy.
     std::vector<cv::Mat> mvImagePyramid;
     void SetPyramidReadback(bool on) { mbPyramidReadback = on; }
 
@@ -92,6 +94,8 @@ protected:
     orbx_extractor* mpHandle;
     int mnDevice, mnMaxWidth, mnMaxHeight;
     bool mbPyramidReadback;
+    unsigned char* mpPyramidHost;   // page-locked backing store of mvImagePyramid[1..]
+    size_t mnPyramidBytes;
 
 private:
     ORBextractor(const ORBextractor&);             // owns a device handle: not copyable

@@ -402,3 +402,23 @@ def test_resize_row_variants_agree(pkg):
     for f in range(0, B, 5):
         sk, sd = single(frames[f])
         assert np.array_equal(res[f][0].view(np.uint8), sk.view(np.uint8)) and np.array_equal(res[f][1], sd), f
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h", [(640, 480), (1241, 376)])
+def test_pyramid_in_one_go_equals_per_level_copies(pkg, w, h):
+    """orbx_get_pyramid (what the C++ ORBextractor fills mvImagePyramid from) against orbx_get_level, for a single frame
+    and for a frame in the middle of a batch."""
+    imgs = [pkg.synth.frame(w, h, 300 + i) for i in range(3)]
+    ex = pkg.ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=4)
+    ex(imgs[0])
+    pyr = ex.image_pyramid()
+    assert pyr[0] is None
+    for l in range(1, 8):
+        assert np.array_equal(pyr[l], ex.image_pyramid_level(l)), l
+    ex.extract_batch(imgs)
+    pyr = ex.image_pyramid(frame=1)
+    for l in range(1, 8):
+        assert np.array_equal(pyr[l], ex.image_pyramid_level(l, frame=1)), l
+    with pytest.raises(Exception):
+        ex.image_pyramid(frame=3)
