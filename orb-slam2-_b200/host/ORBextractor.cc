@@ -25,7 +25,8 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels,
                            int _iniThFAST, int _minThFAST):
     nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels),
     iniThFAST(_iniThFAST), minThFAST(_minThFAST), mpHandle(NULL), mnDevice(0), mnMaxWidth(0), mnMaxHeight(0),
-    mbPyramidReadback(true), mpPyramidHost(NULL), mnPyramidBytes(0)
+    mbPyramidReadback(true), mpPyramidHost(NULL), mnPyramidBytes(0),
+    mpOutKeys(NULL), mpOutDesc(NULL), mnOutCap(0)
 {
     if(const char* dev = std::getenv("ORBX_DEVICE"))
         mnDevice = std::atoi(dev);
@@ -64,6 +65,10 @@ ORBextractor::~ORBextractor()
     orbx_extractor_destroy(mpHandle);
     if(mpPyramidHost)
         orbx_host_free(mpPyramidHost);
+    if(mpOutKeys)
+        orbx_host_free(mpOutKeys);
+    if(mpOutDesc)
+        orbx_host_free(mpOutDesc);
 }
 
 void ORBextractor::SetDevice(int device)
@@ -91,6 +96,22 @@ void ORBextractor::EnsureHandle(int width, int height)
     mnMaxHeight = p.max_height;
 }
 
+void ORBextractor::EnsureOutputs(int cap)
+{
+    if(cap <= mnOutCap)
+        return;
+    if(mpOutKeys) orbx_host_free(mpOutKeys);
+    if(mpOutDesc) orbx_host_free(mpOutDesc);
+    mpOutKeys = NULL; mpOutDesc = NULL; mnOutCap = 0;
+    void *k = NULL, *d = NULL;
+    if(orbx_host_alloc(mnDevice, (size_t)cap * sizeof(orbx_keypoint), &k) != ORBX_OK ||
+       orbx_host_alloc(mnDevice, (size_t)cap * 32, &d) != ORBX_OK)
+        Fail("orbx_host_alloc");
+    mpOutKeys = k;
+    mpOutDesc = static_cast<unsigned char*>(d);
+    mnOutCap = cap;
+}
+
 void ORBextractor::operator()( cv::InputArray _image, cv::InputArray _mask, std::vector<cv::KeyPoint>& _keypoints,
                       cv::OutputArray _descriptors)
 {
@@ -107,20 +128,20 @@ void ORBextractor::operator()( cv::InputArray _image, cv::InputArray _mask, std:
 
     EnsureHandle(image.cols, image.rows);
 
-    // Upper bound on the keypoints of one image: every level's quota plus the octree's overshoot
+    // Results land in page-locked arrays this extractor owns (the library then copies device rows straight into
+    // them, no staging), sized for the upper bound on the keypoints of one image: every level's quota plus the
+    // octree's overshoot.
     int cap = nfeatures + 64 * nlevels + 512;
     int n = 0;
-    std::vector<cv::KeyPoint> keys(cap);
-    std::vector<unsigned char> desc((size_t)cap * 32);
-    int rc = orbx_extract(mpHandle, image.data, image.cols, image.rows, (size_t)image.step,
-                          reinterpret_cast<orbx_keypoint*>(&keys[0]), &desc[0], cap, &n);
-    if(rc == ORBX_ERR_CAPACITY && n > cap)
+    int rc = ORBX_OK;
+    for(int attempt=0; attempt<2; attempt++)
     {
-        cap = n;
-        keys.resize(cap);
-        desc.resize((size_t)cap * 32);
+        EnsureOutputs(cap);
         rc = orbx_extract(mpHandle, image.data, image.cols, image.rows, (size_t)image.step,
-                          reinterpret_cast<orbx_keypoint*>(&keys[0]), &desc[0], cap, &n);
+                          static_cast<orbx_keypoint*>(mpOutKeys), mpOutDesc, mnOutCap, &n);
+        if(rc != ORBX_ERR_CAPACITY || n <= mnOutCap)
+            break;
+        cap = n;
     }
     if(rc != ORBX_OK)
         Fail("orbx_extract");
@@ -131,12 +152,15 @@ void ORBextractor::operator()( cv::InputArray _image, cv::InputArray _mask, std:
     {
         _descriptors.create(n, 32, CV_8U);
         cv::Mat descriptors = _descriptors.getMat();
-        for(int i=0; i<n; i++)
-            std::memcpy(descriptors.ptr(i), &desc[(size_t)i*32], 32);
+        if(descriptors.isContinuous())
+            std::memcpy(descriptors.ptr(0), mpOutDesc, (size_t)n * 32);
+        else
+            for(int i=0; i<n; i++)
+                std::memcpy(descriptors.ptr(i), mpOutDesc + (size_t)i*32, 32);
     }
 
-    keys.resize(n);
-    _keypoints.swap(keys);             // clear + fill (:1153-1186)
+    const cv::KeyPoint* first = static_cast<const cv::KeyPoint*>(mpOutKeys);
+    _keypoints.assign(first, first + n);   // clear + fill (:1153-1186)
 
     // mvImagePyramid: level 0 aliases the caller's image (:1223). The other levels come back in one batch of DMA
     // copies into a page-locked buffer this extractor owns, and the cv::Mat headers alias that buffer (row step = the

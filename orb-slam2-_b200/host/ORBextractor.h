@@ -75,6 +75,7 @@ public:
 protected:
 
     void EnsureHandle(int width, int height);
+    void EnsureOutputs(int cap);
 
     int nfeatures;
     double scaleFactor;
@@ -96,6 +97,9 @@ protected:
     bool mbPyramidReadback;
     unsigned char* mpPyramidHost;   // page-locked backing store of mvImagePyramid[1..]
     size_t mnPyramidBytes;
+    void* mpOutKeys;                // page-locked result rows of the last call (orbx_keypoint == cv::KeyPoint, 28 bytes)
+    unsigned char* mpOutDesc;
+    int mnOutCap;
 
 private:
     ORBextractor(const ORBextractor&);             // owns a device handle: not copyable
