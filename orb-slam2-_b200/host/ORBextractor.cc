@@ -23,8 +23,8 @@ static void Fail(const char* what)
 
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels,
                            int _iniThFAST, int _minThFAST):
-    nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels),
-    iniThFAST(_iniThFAST), minThFAST(_minThFAST), mpHandle(NULL), mnDevice(0), mnMaxWidth(0), mnMaxHeight(0),
+    nfeatures(_nfeatures), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST),
+    scaleFactor(_scaleFactor), mpHandle(NULL), mnDevice(0), mnMaxWidth(0), mnMaxHeight(0),
     mbPyramidReadback(true), mpPyramidHost(NULL), mnPyramidBytes(0),
     mpOutKeys(NULL), mpOutDesc(NULL), mnOutCap(0)
 {
