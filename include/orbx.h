@@ -185,6 +185,22 @@ int orbx_match_merge_device(orbx_matcher* h, const int32_t* d_idx, const int32_t
                             int32_t nshards, int32_t nq, float ratio, int32_t th, int32_t* d_out_idx,
                             int32_t* d_out_d1, int32_t* d_out_d2, uint8_t* d_accepted, void* stream);
 
+/* Allocation-free brute-force top-2 + ratio test. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). Same results as orbx_match_bf2_device followed by orbx_match_merge_device (idx / d1 / d2 /
+ * accepted of orbx_match_bf2), all pointers device memory on `device`, asynchronous on `stream` (a cudaStream_t;
+ * NULL = the default stream). No handle: the per-chunk partial results live in ONE file-scope device array of
+ * 12 MiB that every GPU loading the library holds until the process exits; the call itself performs no cudaMalloc,
+ * cudaFree or other allocation. Limits: nq <= ORBX_NOALLOC_MAX_QUERIES, and (database chunks) x nq <= 2^20 partial
+ * triples -- beyond them the call fails with ORBX_ERR_ARG and a message (use orbx_match_bf2_device). All calls on a
+ * device share that array: calls that overlap on the GPU (different streams, or graphs replayed concurrently) race
+ * and must be serialised by the caller. Nothing in the array needs clearing between calls (every slot a call reads
+ * it has written first). The first call per device resolves the array's address (cudaGetSymbolAddress): make it
+ * outside stream capture. d_accepted may be NULL. */
+#define ORBX_NOALLOC_MAX_QUERIES 16384
+int orbx_match_bf2_noalloc(int32_t device, const uint8_t* d_q, int32_t nq, const uint8_t* d_db, int64_t ndb, float ratio,
+                           int32_t th, int32_t* d_idx, int32_t* d_d1, int32_t* d_d2, uint8_t* d_accepted, void* stream);
+
 /* Windowed search on the Frame grid: the data-parallel half of SearchForInitialization / SearchByProjection
  * (R/src/ORBmatcher.cpp:499-617, :63-163, :1564-1718). The target frame is (kps_un, desc, n) with the image
  * bounds mnMinX..mnMaxY that define its 64x48 grid (R/src/Frame.cpp:168-169, :244-260). For query i the

@@ -66,6 +66,7 @@ SIGNATURES = {
     "orbx_descriptor_distance": (C.c_int, [_vp, _vp, _vp, _vp, _i64]),
     "orbx_match_bf2": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _f32, _i32, _vp, _vp, _vp, _vp]),
     "orbx_match_bf2_device": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "orbx_match_bf2_noalloc": (C.c_int, [_i32, _vp, _i32, _vp, _i64, _f32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "orbx_match_window": (C.c_int, [_vp, _vp, _vp, _i32, _f32, _f32, _f32, _f32, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp,
                                     _i32, C.POINTER(_i32)]),
     "orbx_stereo_match": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _i32, _f32, _f32, _vp, _vp,

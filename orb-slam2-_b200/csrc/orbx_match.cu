@@ -190,3 +190,84 @@ void launch_distance(const uint8_t* a, const uint8_t* b, int* d, long long n, cu
 }
 
 }  // namespace orbx
+
+// ---- allocation-free brute-force top-2 (include/orbx.h: orbx_match_bf2_noalloc) -----------------------
+// The per-chunk partial results of bf2_kernel live in a file-scope device array instead of the matcher's
+// grow-only cudaMalloc'd buffer, for callers that may not allocate (CUDA graph capture, serving loops).
+// In host code `g_bf2_scratch` is only the host-side stand-in of the symbol, never a device address: the
+// address the kernels get comes from cudaGetSymbolAddress, looked up once per device with that device current.
+// Every GPU that loads the library holds the array (12 MiB) until the process exits.
+namespace orbx {
+
+constexpr int kNoAllocMaxQueries = ORBX_NOALLOC_MAX_QUERIES;
+constexpr long long kNoAllocTriples = 1LL << 20;  // chunks * nq <= this; 3 ints per triple = 12 MiB
+static __device__ __align__(256) int g_bf2_scratch[3 * kNoAllocTriples];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noallocMutex;
+int* g_noallocPtr[kNoAllocMaxDevices] = {};
+int g_noallocSms[kNoAllocMaxDevices] = {};
+
+// device must be current. No allocation: cudaGetSymbolAddress only resolves the module's symbol.
+int noalloc_setup(int device, int** ptr, int* sms) {
+  std::lock_guard<std::mutex> lock(g_noallocMutex);
+  if (!g_noallocPtr[device]) {
+    int* p = nullptr;
+    ORBX_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_bf2_scratch));
+    int n = 0;
+    ORBX_CUDA_TRY(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device));
+    g_noallocSms[device] = n;
+    g_noallocPtr[device] = p;
+  }
+  *ptr = g_noallocPtr[device];
+  *sms = g_noallocSms[device];
+  return ORBX_OK;
+}
+}  // namespace
+}  // namespace orbx
+
+extern "C" int orbx_match_bf2_noalloc(int32_t device, const uint8_t* d_q, int32_t nq, const uint8_t* d_db, int64_t ndb,
+                                      float ratio, int32_t th, int32_t* d_idx, int32_t* d_d1, int32_t* d_d2,
+                                      uint8_t* d_accepted, void* stream) {
+  using namespace orbx;
+  if (!d_q || !d_db || !d_idx || !d_d1 || !d_d2 || nq <= 0 || ndb <= 0) { set_error("bad arguments"); return ORBX_ERR_ARG; }
+  if (device < 0 || device >= kNoAllocMaxDevices) { set_error("device %d out of range", device); return ORBX_ERR_ARG; }
+  if (nq > kNoAllocMaxQueries) {
+    set_error("orbx_match_bf2_noalloc: %d queries exceed the static scratch limit of %d (use orbx_match_bf2_device)", nq,
+              kNoAllocMaxQueries);
+    return ORBX_ERR_ARG;
+  }
+  if (ndb > 0x7fffffffLL) { set_error("database index exceeds int32"); return ORBX_ERR_ARG; }
+  ORBX_CUDA_TRY(cudaSetDevice(device));
+  int* scratch = nullptr;
+  int sms = 0;
+  int rc = noalloc_setup(device, &scratch, &sms);
+  if (rc) return rc;
+  // same chunk plan as orbx_match_bf2_device, then fewer / longer chunks when the partials would not fit
+  int rowsPerChunk = 0;
+  int chunks = bf2_plan_chunks(nq, ndb, sms, &rowsPerChunk);
+  const long long maxChunks = kNoAllocTriples / nq;  // >= 64 for nq <= kNoAllocMaxQueries
+  if (chunks > maxChunks) {
+    long long rpc = (ndb + maxChunks - 1) / maxChunks;
+    rpc = (rpc + kBfTileRows - 1) / kBfTileRows * kBfTileRows;
+    if (rpc > (1LL << 23)) {
+      set_error("orbx_match_bf2_noalloc: %lld rows x %d queries exceed the static scratch (%lld partial triples)",
+                (long long)ndb, nq, kNoAllocTriples);
+      return ORBX_ERR_ARG;
+    }
+    rowsPerChunk = (int)rpc;
+    chunks = (int)((ndb + rpc - 1) / rpc);
+  }
+  const size_t per = (size_t)chunks * nq;
+  int* pIdx = scratch;
+  int* pD1 = pIdx + per;
+  int* pD2 = pD1 + per;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // bf2_kernel writes every (chunk, query) slot it is launched for and merge_kernel reads only those: nothing in
+  // the shared array has to start at zero, stale contents of earlier calls are never read.
+  launch_bf2(d_q, nq, d_db, ndb, rowsPerChunk, chunks, 0, pIdx, pD1, pD2, s);
+  launch_merge(pIdx, pD1, pD2, chunks, nq, ratio, th, d_idx, d_d1, d_d2, d_accepted, s);
+  ORBX_CUDA_TRY(cudaGetLastError());
+  return ORBX_OK;
+}
