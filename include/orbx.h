@@ -109,8 +109,22 @@ int orbx_extract_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int
                               int32_t* n, int32_t* ticket);
 int orbx_extract_batch_wait(orbx_extractor* h, int32_t ticket);
 
+/* Stereo sequences, streaming (BASELINE.json config 3; the per-frame work of the stereo constructor
+ * R/src/Frame.cpp:68-129: two extractions :86-89, then ComputeStereoMatches :101). imgs are L R L R ... (count even);
+ * kps / desc / n as in orbx_extract_batch_submit. Every chunk of the submission also runs the row matcher of
+ * orbx_stereo_match on its pairs, against the pyramids the chunk has just built: u_right / depth are [count/2][cap]
+ * (row i of pair p belongs to keypoint i of frame 2p; -1 where unmatched; rows >= n[2p] unspecified), n_matched is
+ * [count/2]; all three page-locked. Wait with orbx_extract_batch_wait. Remember that the reference runs
+ * ComputeStereoMatches with mb == 0 (see orbx_stereo_match). */
+int orbx_stereo_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width, int32_t height,
+                             size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n, float mbf, float mb,
+                             float* u_right, float* depth, int32_t* n_matched, int32_t* ticket);
+
 /* Same, frames and outputs resident in device memory; asynchronous on `stream`.
- * Frame f starts at d_imgs + f*frame_stride. d_n[f] may exceed cap: rows beyond cap are dropped. */
+ * Frame f starts at d_imgs + f*frame_stride. d_n[f] may exceed cap: rows beyond cap are dropped.
+ * d_n[f] == -1: the FAST candidate list of frame f overflowed its capacity (corner density above 1 per 8 pixels on
+ * some level; which candidates were dropped depends on atomics) -- the frame's rows are meaningless. The host-buffer
+ * entry points report the same condition as ORBX_ERR_CAPACITY. */
 int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_imgs, int32_t count, int32_t width,
                               int32_t height, size_t row_stride, size_t frame_stride,
                               orbx_keypoint* d_kps, uint8_t* d_desc, int32_t cap, int32_t* d_n,
@@ -298,6 +312,54 @@ void orbx_vocabulary_destroy(orbx_vocabulary* v);
  * leaves *nid unset). Host buffers, synchronous. BowVector / FeatureVector assembly: host/orbx_bow.h. */
 int orbx_vocabulary_descend(orbx_vocabulary* v, const uint8_t* desc, int32_t n, int32_t levelsup, int32_t* leaf_node,
                             int32_t* level_node);
+
+/* ---- multi-GPU ----
+ * The path shards two ways over the GPUs of one box: extraction by frames (contiguous, pair-aligned blocks of a
+ * sequence per GPU -- a stereo pair stays on one GPU like the two extraction threads of R/src/Frame.cpp:86-89 -- no
+ * collective) and brute-force Hamming by database rows (queries replicated, per-GPU top-2, ONE ncclAllGather of
+ * 12 bytes per query and rank, merge with the sequential rule of R/src/ORBmatcher.cpp:282-291 + ratio test on every
+ * rank). A group is either every rank of ONE process (orbx_shard_group_create: the calls below run one host thread
+ * per device) or ONE rank of a multi-process job (orbx_shard_group_create_rank; rank 0 obtains the id with
+ * orbx_shard_unique_id and the launcher broadcasts it). NCCL is bound at run time (libnccl.so.2); a single-rank
+ * group never touches it. */
+#define ORBX_SHARD_ID_BYTES 128
+typedef struct orbx_shard_group orbx_shard_group;
+int orbx_shard_unique_id(uint8_t* id /* ORBX_SHARD_ID_BYTES */);
+int orbx_shard_group_create(const int32_t* devices, int32_t ndev, orbx_shard_group** out);
+int orbx_shard_group_create_rank(int32_t device, int32_t rank, int32_t nranks, const uint8_t* id, orbx_shard_group** out);
+void orbx_shard_group_destroy(orbx_shard_group* g);
+/* any output may be NULL; nccl_version = ncclGetVersion() of the library bound, 0 when NCCL was never needed */
+int orbx_shard_group_info(const orbx_shard_group* g, int32_t* nranks, int32_t* nlocal, int32_t* first_rank,
+                          int32_t* nccl_version);
+int64_t orbx_shard_launch_count(const orbx_shard_group* g);
+/* rank's block [lo, hi) of `total` units cut into nranks contiguous blocks of whole groups (group = 2: stereo pairs) */
+int orbx_shard_block_range(int64_t total, int32_t rank, int32_t nranks, int32_t group, int64_t* lo, int64_t* hi);
+
+/* The database of config 5: ndb rows of 32 bytes on the host; every local rank uploads its own row range
+ * (orbx_shard_block_range(ndb, rank, nranks, 1)). Synchronous. */
+int orbx_shard_set_database(orbx_shard_group* g, const uint8_t* db, int64_t ndb);
+/* ... or adopts rows [row_lo, row_hi) that already lie in its device memory (not copied, not owned) */
+int orbx_shard_set_database_device(orbx_shard_group* g, int32_t local_index, const uint8_t* d_rows, int64_t row_lo,
+                                   int64_t row_hi, int64_t ndb);
+/* orbx_match_bf2 over the sharded database: host queries in, host results out (global row indices), identical on
+ * every rank and to orbx_match_bf2 on the whole database. Synchronous; in a multi-process job every rank calls it. */
+int orbx_shard_match_bf2(orbx_shard_group* g, const uint8_t* q, int32_t nq, float ratio, int32_t th, int32_t* idx,
+                         int32_t* d1, int32_t* d2, uint8_t* accepted);
+/* One rank's part, device-resident and asynchronous on `stream` (NULL: the rank's own): top-2 on its shard,
+ * ncclAllGather, merge + ratio test. For one-rank-per-process groups (every rank calls it once per step). */
+int orbx_shard_match_bf2_device(orbx_shard_group* g, int32_t local_index, const uint8_t* d_q, int32_t nq, float ratio,
+                                int32_t th, int32_t* d_idx, int32_t* d_d1, int32_t* d_d2, uint8_t* d_accepted, void* stream);
+
+/* A sequence of `count` same-sized frames (imgs[f], page-locked or pageable; results page-locked, count x cap rows as
+ * in orbx_extract_batch_submit) extracted by the group: rank r streams block orbx_shard_block_range(count, r, nranks,
+ * group) through its own extractor (created from *params with .device replaced; steps of params->max_batch frames,
+ * two in flight) and the results land in sequence order. group = 2 with u_right / depth / n_matched non-NULL: a
+ * stereo sequence L R L R ... (orbx_stereo_batch_submit; outputs [count/2][cap], [count/2]). In a multi-process job
+ * every process fills only its own block. Synchronous. */
+int orbx_shard_extract_sequence(orbx_shard_group* g, const orbx_params* params, const uint8_t* const* imgs, int64_t count,
+                                int32_t group, int32_t width, int32_t height, size_t stride, orbx_keypoint* kps,
+                                uint8_t* desc, int32_t cap, int32_t* n, float mbf, float mb, float* u_right, float* depth,
+                                int32_t* n_matched);
 
 #ifdef __cplusplus
 }

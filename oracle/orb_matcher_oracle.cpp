@@ -386,7 +386,7 @@ extern "C" int orb_oracle_stereo_matches(const orb_oracle_keypoint* kps_l, const
       float bestuR = scale_factors[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
       float disparity = (uL - bestuR);
       if (disparity >= minD && disparity < maxD) {
-        if (disparity <= 0) { disparity = 0.01f; bestuR = uL - 0.01f; }
+        if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }  // :742-743: double expression, narrowed once
         depth[iL] = mbf / disparity;
         u_right[iL] = bestuR;
         vDistIdx.push_back(std::make_pair(bestSad, iL));

@@ -43,6 +43,8 @@ SIGNATURES = {
     "orbx_extract": (C.c_int, [_vp, _vp, _i32, _i32, _sz, _vp, _vp, _i32, C.POINTER(_i32)]),
     "orbx_extract_batch": (C.c_int, [_vp, C.POINTER(_vp), _i32, _i32, _i32, _sz, _vp, _vp, _i32, _vp]),
     "orbx_extract_batch_submit": (C.c_int, [_vp, C.POINTER(_vp), _i32, _i32, _i32, _sz, _vp, _vp, _i32, _vp, C.POINTER(_i32)]),
+    "orbx_stereo_batch_submit": (C.c_int, [_vp, C.POINTER(_vp), _i32, _i32, _i32, _sz, _vp, _vp, _i32, _vp, _f32, _f32, _vp, _vp, _vp,
+                                           C.POINTER(_i32)]),
     "orbx_extract_batch_wait": (C.c_int, [_vp, _i32]),
     "orbx_extract_batch_device": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _sz, _sz, _vp, _vp, _i32, _vp, _vp]),
     "orbx_level_size": (C.c_int, [_vp, _i32, C.POINTER(_i32), C.POINTER(_i32)]),
@@ -85,6 +87,19 @@ SIGNATURES = {
     "orbx_vocabulary_create": (C.c_int, [_vp, _i32, _vp, _vp, _i32, C.POINTER(_vp)]),
     "orbx_vocabulary_destroy": (None, [_vp]),
     "orbx_vocabulary_descend": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _vp]),
+    "orbx_shard_unique_id": (C.c_int, [_vp]),
+    "orbx_shard_group_create": (C.c_int, [_vp, _i32, C.POINTER(_vp)]),
+    "orbx_shard_group_create_rank": (C.c_int, [_i32, _i32, _i32, _vp, C.POINTER(_vp)]),
+    "orbx_shard_group_destroy": (None, [_vp]),
+    "orbx_shard_group_info": (C.c_int, [_vp, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i32)]),
+    "orbx_shard_launch_count": (_i64, [_vp]),
+    "orbx_shard_block_range": (C.c_int, [_i64, _i32, _i32, _i32, C.POINTER(_i64), C.POINTER(_i64)]),
+    "orbx_shard_set_database": (C.c_int, [_vp, _vp, _i64]),
+    "orbx_shard_set_database_device": (C.c_int, [_vp, _i32, _vp, _i64, _i64, _i64]),
+    "orbx_shard_match_bf2": (C.c_int, [_vp, _vp, _i32, _f32, _i32, _vp, _vp, _vp, _vp]),
+    "orbx_shard_match_bf2_device": (C.c_int, [_vp, _i32, _vp, _i32, _f32, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "orbx_shard_extract_sequence": (C.c_int, [_vp, C.POINTER(Params), C.POINTER(_vp), _i64, _i32, _i32, _i32, _sz, _vp, _vp, _i32,
+                                              _vp, _f32, _f32, _vp, _vp, _vp]),
     "orbx_distinctive_device": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp]),
 }
 

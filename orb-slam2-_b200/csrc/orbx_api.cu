@@ -13,6 +13,7 @@
 #include <new>
 
 #include "orbx_host.h"
+#include "orbx_stereo.cuh"
 
 using namespace orbx;
 
@@ -271,7 +272,7 @@ int run_pipeline(orbx_extractor* h, Lane& L, const uint8_t* dL0, int l0Pitch, lo
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[4], s));
   launch_describe(pyr, static_cast<const uint8_t*>(L.blurArena.p), g, static_cast<const uint32_t*>(L.keptArena.p),
-                  keptCount, dKps, dDesc, cap, dN, count, s);
+                  keptCount, candCount, dKps, dDesc, cap, dN, count, s);
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[5], s));
   ORBX_CUDA_TRY(cudaGetLastError());
@@ -319,8 +320,76 @@ bool is_pinned(const void* p, size_t bytes) {
   return a0.type == cudaMemoryTypeHost && a1.type == cudaMemoryTypeHost;
 }
 
+// Stereo sequences (orbx_stereo_batch_submit): the chunk's frames are L R L R ...; after the extraction the lane runs
+// Frame::ComputeStereoMatches for its count/2 pairs against its own pyramid arena and copies the rows out.
+struct StereoOut {
+  float mbf, mb;
+  float* uRight;   // host, [pairs][cap]
+  float* depth;
+  int* nMatched;   // host, [pairs]
+  int cap;
+};
+
+int run_chunk_stereo(orbx_extractor* h, Lane& L, const uint8_t* l0, int count, const orbx_keypoint* dK, const uint8_t* dD,
+                     const int* dN, const StereoOut& so) {
+  const FrameSetGeom& g = L.geom;
+  const int nlv = g.nlevels, rows = g.keptPerFrame, pairs = count / 2;
+  if (rows > 65535) { set_error("more than 65535 keypoint rows per frame"); return ORBX_ERR_ARG; }
+  StereoLevels lv;
+  for (int l = 0; l < kMaxLevels; l++) {
+    lv.left[l] = lv.right[l] = nullptr;
+    lv.strideL[l] = lv.strideR[l] = 0;
+    lv.pitchL[l] = lv.pitchR[l] = lv.width[l] = 0;
+    lv.scale[l] = lv.invScale[l] = 1.f;
+  }
+  const uint8_t* arena = static_cast<const uint8_t*>(L.pyrArena.p);
+  for (int l = 0; l < nlv; l++) {
+    const LevelGeom& G = g.lv[l];
+    lv.left[l] = lv.right[l] = l == 0 ? l0 : arena + G.planeOff;
+    lv.strideL[l] = lv.strideR[l] = G.planeBytes;
+    lv.pitchL[l] = lv.pitchR[l] = G.pitch;
+    lv.width[l] = G.w;
+    lv.scale[l] = h->tables.scale[l];
+    lv.invScale[l] = h->tables.invScale[l];
+  }
+  lv.rows0 = g.lv[0].h;
+  lv.pyrLeft0 = lv.arrLeft0 = 0;
+  lv.pyrRight0 = lv.arrRight0 = 1;
+  lv.pyrStep = lv.arrStep = 2;
+  lv.cap = rows;
+  lv.fixedNL = lv.fixedNR = 0;
+  const size_t P = (size_t)std::max(L.batchCap / 2, 1);
+  const size_t itemCap = (size_t)rows * (size_t)stereo_items_per_keypoint(h->tables.scale[nlv - 1]);
+  auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
+  const size_t bUR = al(P * rows * 4), bSad = al(P * rows * 4), bN = al(P * 4), bRow = al(P * ((size_t)lv.rows0 + 1) * 4),
+               bItems = al(P * itemCap * 4);
+  int rc;
+  if ((rc = L.stereoBuf.ensure(2 * bUR + bSad + bN + bRow + bItems))) return rc;
+  uint8_t* base = static_cast<uint8_t*>(L.stereoBuf.p);
+  StereoArrays a;
+  a.kpL = a.kpR = dK;
+  a.descL = a.descR = reinterpret_cast<const uint4*>(dD);
+  a.nL = a.nR = dN;
+  a.uRight = reinterpret_cast<float*>(base);
+  a.depth = reinterpret_cast<float*>(base + bUR);
+  a.sad = reinterpret_cast<int*>(base + 2 * bUR);
+  a.nKept = reinterpret_cast<int*>(base + 2 * bUR + bSad);
+  a.rowStart = reinterpret_cast<int*>(base + 2 * bUR + bSad + bN);
+  a.rowItems = reinterpret_cast<int*>(base + 2 * bUR + bSad + bN + bRow);
+  a.itemCap = (int)itemCap;
+  cudaStream_t s = L.stream;
+  const int le = launch_stereo(lv, a, pairs, rows, so.mbf, so.mb, s);
+  if (le) { set_error("stereo kernel configuration failed: %s", cudaGetErrorString((cudaError_t)le)); return ORBX_ERR_CUDA; }
+  h->launches += 3;
+  const size_t take = (size_t)std::min(rows, so.cap) * 4;
+  ORBX_CUDA_TRY(cudaMemcpy2DAsync(so.uRight, (size_t)so.cap * 4, a.uRight, (size_t)rows * 4, take, pairs, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpy2DAsync(so.depth, (size_t)so.cap * 4, a.depth, (size_t)rows * 4, take, pairs, cudaMemcpyDeviceToHost, s));
+  ORBX_CUDA_TRY(cudaMemcpyAsync(so.nMatched, a.nKept, (size_t)pairs * 4, cudaMemcpyDeviceToHost, s));
+  return ORBX_OK;
+}
+
 int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int count, int width, int height, size_t stride,
-                 const HostOut& out, int* nOut = nullptr, int* overflowOut = nullptr) {
+                 const HostOut& out, int* nOut = nullptr, int* overflowOut = nullptr, const StereoOut* stereo = nullptr) {
   const FrameSetGeom& g = L.geom;
   cudaStream_t s = L.stream;
   uint8_t* l0 = static_cast<uint8_t*>(L.pyrArena.p);  // level-0 slot of the arena (planeOff 0)
@@ -374,10 +443,17 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
     ORBX_CUDA_TRY(cudaMemcpyAsync(st.kps, dK, (size_t)count * rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
     ORBX_CUDA_TRY(cudaMemcpyAsync(st.desc, dD, (size_t)count * rows * 32, cudaMemcpyDeviceToHost, s));
   }
+  if (stereo && (rc = run_chunk_stereo(h, L, l0, count, dK, dD, dN, *stereo))) return rc;
   g_trace.mark(3, s);
   if (g_trace.on) g_trace.n++;
   ORBX_CUDA_TRY(cudaEventRecord(L.done, s));
   return ORBX_OK;
+}
+
+// An error after the first chunk was enqueued: the other lanes' asynchronous copies into the caller's arrays must
+// have landed before the call returns (the caller may free or reuse them).
+void drain_lanes(orbx_extractor* h) {
+  for (Lane& L : h->lane) if (L.stream) cudaStreamSynchronize(L.stream);
 }
 
 // wait for a submitted chunk and scatter its rows into the caller's arrays
@@ -399,6 +475,7 @@ int collect_chunk(orbx_extractor* h, Lane& L, int count, const HostOut& out, int
   for (int f = 0; f < count; f++) {
     const int nf = st.n[f];
     n[f] = nf;
+    if (nf < 0) { set_error("FAST candidate list of frame %d overflowed its capacity", f); return ORBX_ERR_CAPACITY; }
     if (nf > cap) { *tooSmall = true; continue; }
     if (out.direct) continue;
     std::memcpy(kps + (size_t)f * cap, st.kps + (size_t)f * rows, (size_t)nf * sizeof(orbx_keypoint));
@@ -412,7 +489,7 @@ int collect_chunk(orbx_extractor* h, Lane& L, int count, const HostOut& out, int
 void orbx::Lane::release() {
   if (stream) cudaStreamSynchronize(stream);
   dGeom.release(); pyrArena.release(); blurArena.release(); candArena.release(); nodeArena.release();
-  keptArena.release(); counts.release(); outKps.release(); outDesc.release(); outN.release();
+  keptArena.release(); counts.release(); outKps.release(); outDesc.release(); outN.release(); stereoBuf.release();
   if (hostStage) cudaFreeHost(hostStage);
   hostStage = nullptr; hostStageBytes = 0;
   for (int i = 0; i < 8; i++) if (ev[i]) { cudaEventDestroy(ev[i]); ev[i] = nullptr; }
@@ -548,15 +625,15 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
       const int f0 = plan.first[c], cnt = plan.count[c];
       if (c >= nlanes) {  // the lane's staging still holds chunk c-nlanes: scatter it before reusing the lane
         const int g0 = plan.first[c - nlanes], gc = plan.count[c - nlanes];
-        if ((rc = collect_chunk(h, h->lane[c % nlanes], gc, out_at(g0), n + g0, &tooSmall))) return rc;
+        if ((rc = collect_chunk(h, h->lane[c % nlanes], gc, out_at(g0), n + g0, &tooSmall))) { drain_lanes(h); return rc; }
         if (g_trace.on && collected < ChunkTrace::kMax) g_trace.hostDone[collected++] = g_trace.now();
       }
-      if ((rc = submit_chunk(h, h->lane[c % nlanes], imgs + f0, cnt, width, height, stride, out_at(f0)))) return rc;
+      if ((rc = submit_chunk(h, h->lane[c % nlanes], imgs + f0, cnt, width, height, stride, out_at(f0)))) { drain_lanes(h); return rc; }
     }
   }
   for (int c = std::max(nchunks - nlanes, 0); c < nchunks; c++) {
     const int f0 = plan.first[c], cnt = plan.count[c];
-    if ((rc = collect_chunk(h, h->lane[c % nlanes], cnt, out_at(f0), n + f0, &tooSmall))) return rc;
+    if ((rc = collect_chunk(h, h->lane[c % nlanes], cnt, out_at(f0), n + f0, &tooSmall))) { drain_lanes(h); return rc; }
     if (g_trace.on && collected < ChunkTrace::kMax) g_trace.hostDone[collected++] = g_trace.now();
   }
   g_trace.dump();
@@ -565,8 +642,13 @@ int orbx_extract_batch(orbx_extractor* h, const uint8_t* const* imgs, int32_t co
   return ORBX_OK;
 }
 
-int orbx_extract_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width, int32_t height,
-                              size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n, int32_t* ticket) {
+}  // extern "C"
+
+namespace {
+// Common body of the streaming submissions. stereo != nullptr: the frames are L R L R ... and every chunk also runs
+// the stereo matcher on its pairs (stereo->uRight / depth / nMatched are the arrays of the whole submission).
+int submit_stream(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width, int32_t height, size_t stride,
+                  orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n, const StereoOut* stereo, int32_t* ticket) {
   if (!h || !imgs || !kps || !desc || !n || !ticket || cap <= 0 || count <= 0) { set_error("null/invalid argument"); return ORBX_ERR_ARG; }
   if (stride < (size_t)width) { set_error("stride %zu < width %d", stride, width); return ORBX_ERR_ARG; }
   if (count > h->params.max_batch) {
@@ -579,11 +661,20 @@ int orbx_extract_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int
     set_error("streaming submissions need page-locked result arrays (orbx_host_alloc): kps, desc and n");
     return ORBX_ERR_ARG;
   }
+  if (stereo) {
+    const size_t pairs = (size_t)count / 2;
+    if ((count & 1) || !stereo->uRight || !stereo->depth || !stereo->nMatched) { set_error("stereo submissions take an even number of frames (L R L R ...) and three result arrays"); return ORBX_ERR_ARG; }
+    if (!is_pinned(stereo->uRight, pairs * cap * 4) || !is_pinned(stereo->depth, pairs * cap * 4) || !is_pinned(stereo->nMatched, pairs * 4)) {
+      set_error("streaming submissions need page-locked result arrays (orbx_host_alloc): u_right, depth and n_matched");
+      return ORBX_ERR_ARG;
+    }
+  }
   ChunkPlan plan;
   // without fill and drain to pay per call, larger chunks win: they fill the GPU better (tools/stream_probe.py:
   // 128 frames x 4 lanes 167.7 k frames/s, 64 x 4 143 k, 256 x 3 167.7 k at 640x480)
-  if (!plan_chunks(count, h->chunkFrames > 0 ? h->chunkFrames : 2 * chunk_frames(width, height), &plan) ||
-      plan.n > orbx_extractor::kTicketChunks) {
+  int chunk = h->chunkFrames > 0 ? h->chunkFrames : 2 * chunk_frames(width, height);
+  if (stereo) chunk = std::max(2, chunk & ~1);  // a pair never straddles two chunks
+  if (!plan_chunks(count, chunk, &plan) || plan.n > orbx_extractor::kTicketChunks) {
     set_error("batch of %d frames needs more than %d chunks (raise the chunk size)", count, orbx_extractor::kTicketChunks);
     return ORBX_ERR_ARG;
   }
@@ -601,12 +692,25 @@ int orbx_extract_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int
     if (!t.done[i]) ORBX_CUDA_TRY(cudaEventCreateWithFlags(&t.done[i], cudaEventDisableTiming));
   for (int c = 0; c < plan.n; c++) t.overflow[c] = 0;
   bool used[kMaxLanes] = {};
+  rc = ORBX_OK;
+  int enqueued = 0;
   for (int c = 0; c < plan.n; c++) {
     const int f0 = plan.first[c], cnt = plan.count[c];
     const int li = (int)(h->laneRotor++ % (unsigned)nlanes);
     const HostOut out{kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, true};
-    if ((rc = submit_chunk(h, h->lane[li], imgs + f0, cnt, width, height, stride, out, n + f0, t.overflow + c))) return rc;
+    StereoOut so;
+    if (stereo) {
+      so = *stereo;
+      so.uRight += (size_t)(f0 / 2) * cap; so.depth += (size_t)(f0 / 2) * cap; so.nMatched += f0 / 2; so.cap = cap;
+    }
+    if ((rc = submit_chunk(h, h->lane[li], imgs + f0, cnt, width, height, stride, out, n + f0, t.overflow + c, stereo ? &so : nullptr))) break;
     used[li] = true;
+    enqueued++;
+  }
+  if (rc) {
+    // nothing of a failed submission stays in flight: the caller gets no ticket to wait on
+    drain_lanes(h);
+    return rc;
   }
   t.lanesUsed = 0;
   for (int i = 0; i < nlanes; i++)
@@ -615,6 +719,21 @@ int orbx_extract_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int
   h->haveResult = false;  // introspection covers synchronous single-chunk calls only
   *ticket = t.id;
   return ORBX_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int orbx_extract_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width, int32_t height,
+                              size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n, int32_t* ticket) {
+  return submit_stream(h, imgs, count, width, height, stride, kps, desc, cap, n, nullptr, ticket);
+}
+
+int orbx_stereo_batch_submit(orbx_extractor* h, const uint8_t* const* imgs, int32_t count, int32_t width, int32_t height,
+                             size_t stride, orbx_keypoint* kps, uint8_t* desc, int32_t cap, int32_t* n, float mbf, float mb,
+                             float* u_right, float* depth, int32_t* n_matched, int32_t* ticket) {
+  const StereoOut so{mbf, mb, u_right, depth, n_matched, cap};
+  return submit_stream(h, imgs, count, width, height, stride, kps, desc, cap, n, &so, ticket);
 }
 
 int orbx_extract_batch_wait(orbx_extractor* h, int32_t ticket) {

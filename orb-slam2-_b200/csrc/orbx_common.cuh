@@ -147,8 +147,8 @@ int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const ui
 void launch_blur(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint8_t* blurArena, int nframes, cudaStream_t s);
 
 void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const FrameSetGeom& hGeom,
-                     const uint32_t* kept, const int* keptCount, orbx_keypoint* outKps, uint8_t* outDesc, int cap,
-                     int* outN, int nframes, cudaStream_t s);
+                     const uint32_t* kept, const int* keptCount, const int* candCount, orbx_keypoint* outKps,
+                     uint8_t* outDesc, int cap, int* outN, int nframes, cudaStream_t s);
 
 // stand-alone octree on one candidate set (orbx_distribute); returns 0 or a cudaError_t
 int launch_octree_single(const uint32_t* cand, int n, int width, int height, int nfeat, int wCell, int hCell,

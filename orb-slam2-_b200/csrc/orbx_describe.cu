@@ -53,8 +53,8 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
 __global__ void __launch_bounds__(kDescWarps * 32)
 describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restrict__ blurArena,
                 const __grid_constant__ FrameSetGeom g, const uint32_t* __restrict__ kept,
-                const int* __restrict__ keptCount, orbx_keypoint* __restrict__ outKps,
-                uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN) {
+                const int* __restrict__ keptCount, const int* __restrict__ candCount,
+                orbx_keypoint* __restrict__ outKps, uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN) {
   pdl_wait();
   __shared__ float4 sPat[8 * 32];        // [bit][lane] = (x0, y0, x1, y1) of pattern pair lane*8+bit
   __shared__ uint32_t sWU[32 * 8];       // [row v+15][chunk]: u (s8) inside the disc, else 0
@@ -87,12 +87,17 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
     sWO[tid] = wo;
     if (tid == 0) {
       int total = 0;
+      // a level whose FAST candidates did not fit candCap (the dropped subset depends on atomics) or whose octree
+      // list hit its guard makes the frame's result meaningless: n[f] = -1 tells the device-resident caller
+      bool truncated = false;
       for (int l = 0; l < nl; l++) {
         sStart[l] = total;
-        total += max(0, min(keptCount[f * nl + l], g.lv[l].keptCap));
+        const int kc = keptCount[f * nl + l];
+        truncated = truncated || kc < 0 || candCount[f * nl + l] > g.lv[l].candCap;
+        total += max(0, min(kc, g.lv[l].keptCap));
       }
       sStart[nl] = total;
-      if (blockIdx.x == 0) outN[f] = total;
+      if (blockIdx.x == 0) outN[f] = truncated ? -1 : total;
     }
   }
   __syncthreads();
@@ -184,11 +189,11 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
 }
 
 void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const FrameSetGeom& hGeom,
-                     const uint32_t* kept, const int* keptCount, orbx_keypoint* outKps, uint8_t* outDesc, int cap,
-                     int* outN, int nframes, cudaStream_t s) {
+                     const uint32_t* kept, const int* keptCount, const int* candCount, orbx_keypoint* outKps,
+                     uint8_t* outDesc, int cap, int* outN, int nframes, cudaStream_t s) {
   const int maxKp = hGeom.keptPerFrame;
   dim3 grid((maxKp + kDescKpPerCta - 1) / kDescKpPerCta, nframes);
-  launch_pdl(describe_kernel, grid, dim3(kDescWarps * 32), 0, s, pyr, blurArena, hGeom, kept, keptCount, outKps, outDesc, cap, outN);
+  launch_pdl(describe_kernel, grid, dim3(kDescWarps * 32), 0, s, pyr, blurArena, hGeom, kept, keptCount, candCount, outKps, outDesc, cap, outN);
 }
 
 // ---- array versions of the float helpers, for the unit parity tests ----------------------------

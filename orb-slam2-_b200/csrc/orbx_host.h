@@ -53,6 +53,7 @@ struct Lane {
   DeviceBuf dGeom;                    // FrameSetGeom on device (octree kernel)
   DeviceBuf pyrArena, blurArena, candArena, nodeArena, keptArena, counts;
   DeviceBuf outKps, outDesc, outN;    // device staging for the host-buffer entry points
+  DeviceBuf stereoBuf;                // stereo sequences: uRight | depth | sad | nKept | row table of the chunk's pairs
   void* hostStage = nullptr;          // pinned: kps | desc | n | overflow flag
   size_t hostStageBytes = 0;
   void release();

@@ -129,13 +129,13 @@ bf2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, lo
 // Merge nshards partial results ([shard][nq], shards in ascending index order); optional ratio test.
 __global__ void __launch_bounds__(256)
 merge_kernel(const int* __restrict__ pIdx, const int* __restrict__ pD1, const int* __restrict__ pD2, int nshards,
-             int nq, float ratio, int th, int* __restrict__ oIdx, int* __restrict__ oD1, int* __restrict__ oD2,
-             uint8_t* __restrict__ accepted) {
+             long long shardStride, int nq, float ratio, int th, int* __restrict__ oIdx, int* __restrict__ oD1,
+             int* __restrict__ oD2, uint8_t* __restrict__ accepted) {
   const int qi = blockIdx.x * blockDim.x + threadIdx.x;
   if (qi >= nq) return;
   int best = INT_MAX, best2 = INT_MAX, idx = -1;
   for (int s = 0; s < nshards; s++) {
-    const long long o = (long long)s * nq + qi;
+    const long long o = (long long)s * shardStride + qi;
     const int a1 = pD1[o], a2 = pD2[o];
     if (a1 < best) {
       best2 = min(best, a2);
@@ -180,7 +180,14 @@ void launch_bf2(const uint8_t* q, int nq, const uint8_t* db, long long ndb, int 
 
 void launch_merge(const int* pIdx, const int* pD1, const int* pD2, int nshards, int nq, float ratio, int th,
                   int* oIdx, int* oD1, int* oD2, uint8_t* accepted, cudaStream_t s) {
-  merge_kernel<<<(nq + 255) / 256, 256, 0, s>>>(pIdx, pD1, pD2, nshards, nq, ratio, th, oIdx, oD1, oD2, accepted);
+  merge_kernel<<<(nq + 255) / 256, 256, 0, s>>>(pIdx, pD1, pD2, nshards, nq, nq, ratio, th, oIdx, oD1, oD2, accepted);
+}
+
+// shard s of array X starts at X + s*shardStride (the all-gathered layout [rank][idx | d1 | d2][nq] is read in place)
+void launch_merge_strided(const int* pIdx, const int* pD1, const int* pD2, int nshards, long long shardStride, int nq,
+                          float ratio, int th, int* oIdx, int* oD1, int* oD2, uint8_t* accepted, cudaStream_t s) {
+  merge_kernel<<<(nq + 255) / 256, 256, 0, s>>>(pIdx, pD1, pD2, nshards, shardStride, nq, ratio, th, oIdx, oD1, oD2,
+                                                accepted);
 }
 
 void launch_distance(const uint8_t* a, const uint8_t* b, int* d, long long n, cudaStream_t s) {

@@ -178,7 +178,7 @@ stereo_match_kernel(const __grid_constant__ StereoLevels lv, const __grid_consta
     float bestuR = __fmul_rn(lv.scale[levelL], __fadd_rn(__fadd_rn(scaleduR0, (float)bestincR), deltaR));
     float disparity = __fsub_rn(uL, bestuR);
     if (disparity >= 0 && disparity < maxD) {
-      if (disparity <= 0) { disparity = 0.01f; bestuR = __fsub_rn(uL, 0.01f); }
+      if (disparity <= 0) { disparity = 0.01f; bestuR = __double2float_rn(__dsub_rn((double)uL, 0.01)); }  // :742-743: uL-0.01 is a double expression
       depth[iL] = __fdiv_rn(mbf, disparity);
       uRight[iL] = bestuR;
       sad[iL] = bestSad;

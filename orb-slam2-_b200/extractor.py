@@ -128,6 +128,24 @@ class ORBextractor:
                                               ptr(kps), ptr(desc), cap, ptr(n), C.byref(ticket)))
         return ticket.value
 
+    def stereo_batch_submit(self, frames, kps, desc, n, mbf, mb, u_right, depth, n_matched):
+        """orbx_stereo_batch_submit: frames are L R L R ...; every chunk also runs Frame::ComputeStereoMatches on its
+        pairs. u_right / depth (B/2, cap) float32 and n_matched (B/2,) int32, all page-locked. Returns the ticket."""
+        if frames.dtype != np.uint8 or frames.ndim != 3 or frames.strides[2] != 1:
+            raise TypeError("frames must be a (B, H, W) uint8 array with contiguous rows")
+        cnt, h, w = frames.shape
+        cap = kps.shape[1]
+        if (kps.dtype != KP_DTYPE or kps.shape[0] < cnt or desc.shape[:2] != kps.shape[:2] or n.shape[0] < cnt or n.dtype != np.int32
+                or u_right.dtype != np.float32 or depth.dtype != np.float32 or n_matched.dtype != np.int32
+                or u_right.shape != (cnt // 2, cap) or depth.shape != (cnt // 2, cap) or n_matched.shape[0] < cnt // 2):
+            raise TypeError("output arrays do not match the batch")
+        ptrs = frames.ctypes.data + frames.strides[0] * np.arange(cnt, dtype=np.int64)
+        ticket = C.c_int32(0)
+        check(lib().orbx_stereo_batch_submit(self._h, C.cast(ptr(ptrs), C.POINTER(C.c_void_p)), cnt, w, h, frames.strides[1],
+                                             ptr(kps), ptr(desc), cap, ptr(n), mbf, mb, ptr(u_right), ptr(depth),
+                                             ptr(n_matched), C.byref(ticket)))
+        return ticket.value
+
     def extract_batch_wait(self, ticket):
         check(lib().orbx_extract_batch_wait(self._h, ticket))
 

@@ -13,6 +13,23 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
 
 
+def pytest_collection_modifyitems(config, items):
+    """Without a CUDA device every gpu-marked test is skipped (liborbx has no CPU fallback, and the C++ drop-in
+    aborts the interpreter when a call fails), whatever -m / -k selected."""
+    gpu_items = [it for it in items if it.get_closest_marker("gpu")]
+    if not gpu_items:
+        return
+    try:
+        import orbslam2_b200
+        have = orbslam2_b200.device_count() > 0
+    except Exception:
+        have = False
+    if not have:
+        skip = pytest.mark.skip(reason="no CUDA device")
+        for it in gpu_items:
+            it.add_marker(skip)
+
+
 @pytest.fixture(scope="session")
 def pkg():
     import orbslam2_b200

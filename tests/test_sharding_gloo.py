@@ -50,7 +50,7 @@ def _worker(rank, world, port, nq, ndb, ret):
         gathered = [torch.empty_like(part) for _ in range(world)]
         dist.all_gather(gathered, part)
         g = torch.stack(gathered).numpy()                       # [world, 3, nq]
-        assert g.shape[::2] == pkg.sharding.gather_layout(world, nq)
+        assert g.shape == (world, 3, nq)                        # what ncclAllGather delivers in csrc/orbx_shard.cu
         midx, m1, m2 = merge_rule(g[:, 0], g[:, 1], g[:, 2])
         eidx, e1, e2, _ = oracle_lib.match_bf2(q, db, np.float32(0.6), 50, nthreads=2)
         ok = np.array_equal(midx, eidx) and np.array_equal(m1, e1) and np.array_equal(m2, e2)

@@ -12,7 +12,7 @@ tail -15 $OUT/pytest.log
 timeout 600 python bench.py > $OUT/bench.json 2> $OUT/bench.err
 echo "bench exit $?"; cat $OUT/bench.json; tail -3 $OUT/bench.err
 [ "$MODE" = quick ] && exit 0
-CMD="python bench.py --steps 1 --warmup 3 --skip-e2e --skip-cpu --skip-hamming"
+CMD="python bench.py --steps 1 --warmup 3 --skip-e2e --skip-cpu --skip-hamming --skip-workloads --skip-parity"
 KRE='fast_cells|describe_kernel|blur_kernel|resize4|resize_kernel|octree_kernel'
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"$KRE" --launch-skip 33 -c 11 --csv \
   --log-file $OUT/launches.csv $CMD > $OUT/ncu_launches.log 2>&1

@@ -4,7 +4,7 @@
 TAG=$1; KRE=$2; SKIP=${3:-3}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
-CMD="python bench.py --steps 1 --warmup 3 --skip-e2e --skip-cpu --skip-hamming"
+CMD="python bench.py --steps 1 --warmup 3 --skip-e2e --skip-cpu --skip-hamming --skip-workloads --skip-parity"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"$KRE" --launch-skip $SKIP --launch-count 1 \
   -o $OUT/one -f $CMD > $OUT/ncu_one.log 2>&1
 echo "ncu exit $?"

@@ -6,7 +6,7 @@ OUT=gpurun_out/$TAG
 mkdir -p $OUT
 for v in "$@"; do
   if [ "$v" = base ]; then unset ORBX_LIB; else export ORBX_LIB=$PWD/orb-slam2-_b200/variants/liborbx_$v.so; fi
-  timeout 300 python bench.py --steps 10 --warmup 3 --skip-e2e --skip-cpu --skip-hamming > $OUT/$v.json 2> $OUT/$v.err
+  timeout 300 python bench.py --steps 10 --warmup 3 --skip-e2e --skip-cpu --skip-hamming --skip-workloads --skip-parity > $OUT/$v.json 2> $OUT/$v.err
   python - "$v" $OUT/$v.json <<'PY'
 import json, sys
 d = json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])
