@@ -16,9 +16,8 @@
 //    the FIRST max-response point of a node); it is a function of (cell row, cell col, y, x), which
 //    the octree kernel recomputes from the coordinates, so candidates are appended unordered.
 //
-// Kernel shape (v3, kept in v4): one WARP per cell, 8 warps per CTA, shared memory sized on the host for the
-// largest cell of the shape. v4 makes the warps persistent and stages the patch asynchronously (see "asynchronous
-// staging" below). The cell patch is staged word-aligned in shared memory; every lane scores
+// Kernel shape (v3): one WARP per cell, 8 cells per CTA, shared memory sized on the host for the
+// largest cell of the shape. The cell patch is staged word-aligned in shared memory; every lane scores
 // 4 horizontally adjacent pixels per task with branch-free packed 16x2 min/max (VIMNMX3.U16x2):
 // the patch is staged as 16-bit lanes, so 6 of the 16 ring offsets are plain words and 10 cost one PRMT;
 // 72 packed min/max per PAIR of pixels, no divergence, no per-pixel early-outs -- the cost per pixel
@@ -35,7 +34,7 @@ namespace orbx {
 #define ORBX_FAST_WARPS 8
 #endif
 #ifndef ORBX_FAST_MINB
-#define ORBX_FAST_MINB 3
+#define ORBX_FAST_MINB 4
 #endif
 constexpr int kFastWarps = ORBX_FAST_WARPS;   // cells per CTA
 constexpr int kFastThreads = kFastWarps * 32;
@@ -135,140 +134,105 @@ __device__ __forceinline__ uint32_t fast_compass_bound(uint32_t n, uint32_t s, u
   return __viaddmax_s16x2_relu(__vmaxu2(dark, bright), negThBias, 0u);
 }
 
-// ---- asynchronous staging (v4) ------------------------------------------------------------------------------
-// A warp is persistent: it walks a strided list of (frame, cell) work items. While it scores cell k, the raw bytes
-// of cell k+1 land in its `raw` buffer: one cp.async.bulk (the TMA unit's 1-D bulk copy, SASS UBLKCP) per cell row,
-// 16-byte aligned segments of <= kRawRowMax bytes, all completing on the warp's own mbarrier. When the warp gets to
-// cell k+1 the bytes are (nearly always) already there; the byte -> 16-bit-lane expansion is then a shared -> shared
-// pass (LDS.32, 2 PRMT, STS.64) instead of the global-load round trip that made the staging region 21 % of the v3
-// kernel's stall samples. Planes whose base or pitch is not 16-byte aligned (a caller's level 0) take the
-// synchronous path of v3.
-constexpr int kRawRowMax = 96;   // bytes per staged raw row: <= 12 (alignment) + 4 * nW, rounded up to 16
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
-
-// words of shared memory one warp needs: patch staged as 16-bit lanes (ch x 2nW) + score map ((sh+2) x nW)
-// + the queue of tasks with a non-zero score word (16 bits per task), rounded to 16 bytes, + the raw rows
-__host__ __device__ inline int fast_tile_words(int wCell, int hCell) {
+// words of shared memory one cell needs: patch staged as 16-bit lanes (ch x 2nW) + score map ((sh+2) x nW)
+// + the queue of tasks with a non-zero score word (16 bits per task); even, so that every warp's patch
+// stays 8-byte aligned
+__host__ __device__ inline int fast_cell_words(int wCell, int hCell) {
   const int nW = ((7 + wCell - 1) >> 2) + 2;  // worst alignment: a = 7
   const int words = (hCell + 6) * 2 * nW + (hCell + 2) * nW + (hCell * (nW - 2) + 1) / 2 + 1;
-  return (words + 3) & ~3;
-}
-__host__ __device__ inline int fast_raw_row_bytes(int wCell) {
-  const int nW = ((7 + wCell - 1) >> 2) + 2;
-  return (12 + 4 * nW + 15) & ~15;
-}
-
-// One (frame, cell) work item, warp-uniform.
-struct FastCell {
-  int level, f, ci, cj, iniX, iniY, ch, sw, sh, gx0;
-  const uint8_t* src;   // global address of tile column 0 of row iniY
-  int pitch;
-  bool valid, bulk;
-};
-
-__device__ __forceinline__ FastCell fast_cell_of(const PyramidPtrs& pyr, const FrameSetGeom& g, int work, int totalWork) {
-  FastCell c;
-  c.valid = false;
-  c.bulk = false;
-  c.level = c.f = c.ci = c.cj = c.iniX = c.iniY = c.ch = c.sw = c.sh = c.gx0 = c.pitch = 0;
-  c.src = nullptr;
-  if (work >= totalWork) return c;
-  const int f = work / g.totalCells;
-  const int cell = work - f * g.totalCells;
-  int level = 0;
-  while (level + 1 < g.nlevels && cell >= g.lv[level + 1].cellBase) level++;
-  const LevelGeom& L = g.lv[level];
-  const int cidx = cell - L.cellBase;
-  const int ci = (L.nCols <= 64 && cidx < 1024) ? div_small(cidx, L.nCols) : cidx / L.nCols;
-  const int cj = cidx - ci * L.nCols;
-  c.level = level; c.f = f; c.ci = ci; c.cj = cj;
-  // cell rectangle (R/src/ORBextractor.cpp:851-870)
-  c.iniY = kMinBorder + ci * L.hCell;
-  c.iniX = kMinBorder + cj * L.wCell;
-  if (c.iniY >= L.maxBY - 3 || c.iniX >= L.maxBX - 6) return c;
-  const int maxY = min(c.iniY + L.hCell + 6, L.maxBY);
-  const int maxX = min(c.iniX + L.wCell + 6, L.maxBX);
-  c.ch = maxY - c.iniY;
-  c.sw = maxX - c.iniX - 6;  // cv::FAST scans [3,cw-3)x[3,ch-3)
-  c.sh = c.ch - 6;
-  if (c.sw <= 0 || c.sh <= 0) return c;
-  // Tile column 0 is global column gx0 (a multiple of 4, <= iniX-1): the first scanned pixel sits at
-  // tile column a in 4..7, so every 4-pixel group starts on a word boundary and its ring (+-3) stays
-  // inside the 12-byte window of words q, q+1, q+2.
-  c.gx0 = ((c.iniX + 3) & ~3) - 4;
-  c.pitch = pyr.pitch[level];
-  const uint8_t* plane = pyr.lvl[level] + (long long)f * pyr.frameStride[level];
-  c.src = plane + (long long)c.iniY * c.pitch + c.gx0;
-  c.bulk = ((reinterpret_cast<uintptr_t>(plane) | (uintptr_t)c.pitch) & 15) == 0;
-  c.valid = true;
-  return c;
-}
-
-// rows of the raw patch of `c` into `raw`, asynchronously: row r = the 16-byte aligned segment that holds tile words
-// 0 .. nW-1 of image row iniY + r. Returns nothing; completion is observed on `bar`.
-__device__ __forceinline__ void fast_issue_rows(const FastCell& c, uint8_t* raw, int rawPitch, uint64_t* bar, int lane) {
-  const int a = c.iniX + 3 - c.gx0, b = a + c.sw;
-  const int nW = ((b - 1) >> 2) + 2;
-  const int head = c.gx0 & 15;                       // bytes between the aligned segment start and tile column 0
-  const uint32_t rowBytes = (uint32_t)((head + 4 * nW + 15) & ~15);
-#if defined(ORBX_FAST_EXP2)   // timing experiment only: no copies at all (wrong results)
-  (void)rowBytes; (void)raw; (void)bar;
-#elif defined(ORBX_FAST_EXP1) // timing experiment only: ONE copy of the patch's byte count (wrong results)
-  if (lane == 0) {
-    mbar_expect_tx(bar, rowBytes * (uint32_t)c.ch);
-    bulk_g2s(raw, c.src - head, rowBytes * (uint32_t)c.ch, bar);
-  }
-  __syncwarp();
-#else
-  if (lane == 0) mbar_expect_tx(bar, rowBytes * (uint32_t)c.ch);
-  __syncwarp();
-  for (int r = lane; r < c.ch; r += 32)
-    bulk_g2s(raw + r * rawPitch, c.src - head + (long long)r * c.pitch, rowBytes, bar);
-#endif
+  return (words + 1) & ~1;
 }
 
 __global__ void __launch_bounds__(kFastThreads, ORBX_FAST_MINB)
 fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
                   uint32_t* __restrict__ cand, int* __restrict__ candCount, int* __restrict__ overflow,
-                  int wordsPerWarp, int tileWords, int rawPitch, int totalWork) {
+                  int wordsPerWarp) {
+  pdl_wait();
   extern __shared__ __align__(16) uint32_t smemFast[];
-  __shared__ __align__(8) uint64_t sBar[kFastWarps];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int stride = gridDim.x * kFastWarps;
-  int work = blockIdx.x * kFastWarps + warp;
-  if (work >= totalWork) return;  // warps are independent: no block-wide barrier below
+  const int cell = blockIdx.x * kFastWarps + warp;
+  if (cell >= g.totalCells) return;  // warps are independent: no block-wide barrier below
   const int nl = g.nlevels;
+  int level = 0;
+  while (level + 1 < nl && cell >= g.lv[level + 1].cellBase) level++;
+  const LevelGeom& L = g.lv[level];
+  const int cidx = cell - L.cellBase;
+  const int ci = (L.nCols <= 64 && cidx < 1024) ? div_small(cidx, L.nCols) : cidx / L.nCols;
+  const int cj = cidx - ci * L.nCols;
+  const int f = blockIdx.y;
 
-  uint32_t* tile = smemFast + warp * wordsPerWarp;                       // ch rows x 2nW words: one 16-bit lane per pixel
-  uint8_t* raw = reinterpret_cast<uint8_t*>(tile + tileWords);           // ch rows x rawPitch bytes, as they lie in the plane
-  uint64_t* bar = &sBar[warp];
-  if (lane == 0) mbar_init(bar, 1);
+  // cell rectangle (R/src/ORBextractor.cpp:851-870)
+  const int iniY = kMinBorder + ci * L.hCell;
+  const int iniX = kMinBorder + cj * L.wCell;
+  if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6) return;
+  const int maxY = min(iniY + L.hCell + 6, L.maxBY);
+  const int maxX = min(iniX + L.wCell + 6, L.maxBX);
+  const int ch = maxY - iniY;
+  const int sw = maxX - iniX - 6, sh = ch - 6;  // cv::FAST scans [3,cw-3)x[3,ch-3)
+  if (sw <= 0 || sh <= 0) return;
+
+  // Tile column 0 is global column gx0 (a multiple of 4, <= iniX-1): the first scanned pixel sits at
+  // tile column a in 4..7, so every 4-pixel group starts on a word boundary and its ring (+-3) stays
+  // inside the 12-byte window of words q, q+1, q+2.
+  const int gx0 = ((iniX + 3) & ~3) - 4;
+  const int a = iniX + 3 - gx0;
+  const int b = a + sw;
+  const int nG = (b - 1) >> 2;  // groups q = 0..nG-1 cover tile words 1..nG
+  const int nW = nG + 2;        // staged words per row
+
+  uint32_t* tile = smemFast + warp * wordsPerWarp;  // ch rows x 2nW words: one 16-bit lane per pixel
+  uint32_t* smap = tile + ch * 2 * nW;              // (sh+2) rows x nW words, rows 0 and sh+1 stay zero
+  uint16_t* queue = reinterpret_cast<uint16_t*>(smap + (sh + 2) * nW);  // y<<8 | q of the tasks worth a second look
+
+  const int pitch = pyr.pitch[level];
+  const uint8_t* src = pyr.lvl[level] + (long long)f * pyr.frameStride[level] + (long long)iniY * pitch + gx0;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)pitch) & 3) == 0;
+  {
+    // Word idx of the patch (row idx / nW, word idx % nW) goes to tile[2 idx]; lane handles idx = lane, lane+32, ...
+    // Row and column advance incrementally (32 = dr * nW + dc per step), so a word costs a pointer add, the load,
+    // two PRMT and one 8-byte store. Eight loads are in flight per lane before the first one is used: with one
+    // load per loop trip the warp sat out a full DRAM latency 13 times per cell.
+    const int total = ch * nW;
+    const int dr = div_small(32, nW), dc = 32 - dr * nW;
+    int r = div_small(lane, nW);
+    int c = lane - r * nW;
+    const uint8_t* p = src + (long long)r * pitch + 4 * c;
+    const long long stepNoWrap = (long long)dr * pitch + 4 * dc;
+    const long long stepWrap = stepNoWrap + pitch - 4 * nW;
+    constexpr int kInFlight = 8;
+    auto stage = [&](auto alignedTag) {
+      constexpr bool kAligned = decltype(alignedTag)::value;
+      for (int base = lane; base < total; base += 32 * kInFlight) {
+        uint32_t w[kInFlight];
+#pragma unroll
+        for (int k = 0; k < kInFlight; k++) {
+          w[k] = 0u;
+          if (base + 32 * k < total) {
+            if constexpr (kAligned) {
+              w[k] = *reinterpret_cast<const uint32_t*>(p);
+            } else {
+              w[k] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+            }
+          }
+          c += dc;
+          const bool wrap = c >= nW;
+          p += wrap ? stepWrap : stepNoWrap;
+          if (wrap) c -= nW;
+        }
+#pragma unroll
+        for (int k = 0; k < kInFlight; k++) {
+          // bytes -> 16-bit lanes once here instead of once per ring offset in the scoring loop
+          if (base + 32 * k < total)
+            *reinterpret_cast<uint2*>(&tile[2 * (base + 32 * k)]) =
+                make_uint2(__byte_perm(w[k], 0u, 0x4140), __byte_perm(w[k], 0u, 0x4342));
+        }
+      }
+    };
+    if (aligned) stage(std::true_type{});
+    else stage(std::false_type{});
+  }
+  for (int i = lane; i < (sh + 2) * nW; i += 32) smap[i] = 0u;
   __syncwarp();
-  uint32_t parity = 0;
 
   const int minTh = g.minTh, iniTh = g.iniTh;
   // per 16-bit lane: -(256 + minTh)
@@ -277,320 +241,193 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   // Scores are kept as max(m - minTh, 0): a pixel whose margin exceeds iniTh stores at least iniByte.
   const int iniByte = max(iniTh - minTh + 1, 1);
   const uint32_t negIni = ((uint32_t)(-(iniByte - 1)) & 0xffffu) * 0x00010001u;
+  const int nTasks = sh * nG;
+  const int dy = div_small(32, nG), dq = 32 - dy * nG;
+  const int y0 = div_small(lane, nG), q0 = lane - y0 * nG;
   const uint32_t below = (1u << lane) - 1u;
 
-  pdl_wait();  // the planes are the pyramid kernels' output
-  FastCell nxt = fast_cell_of(pyr, g, work, totalWork);
-  if (nxt.valid && nxt.bulk) fast_issue_rows(nxt, raw, rawPitch, bar, lane);
+  // ---- pass 1, every task: compass bound. Any 9-arc of the ring contains two adjacent compass pixels
+  //      (p0, p4, p8, p12), so  A >= Ac = min over adjacent compass pairs of their max  and
+  //      B <= Bc = max over those pairs of their min, hence m <= max(v - Ac, Bc - v): a task whose four
+  //      bounds are all <= minTh has an all-zero score word and is dropped after 12 instead of 92 packed
+  //      operations per pixel pair. The others are queued as y<<8 | q in two classes: list A (some bound
+  //      above iniTh) grows from the front of the queue, list B (bounds in (minTh, iniTh]) from its back.
+  //      B is only ever scored if the cell turns out empty at iniTh (phase 1 below). Rounds are warp-uniform
+  //      (lanes past the last task idle inside the round) so that the ballots are full-warp ones. ----
+  int nA = 0, backB = nTasks - 1;  // next free slot of list B
+  {
+    int y = y0, q = q0;
+    for (int t0 = 0; t0 < nTasks; t0 += 32) {
+      uint32_t any = 0u, hi = 0u;
+      if (t0 + lane < nTasks) {
+        const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);  // window = tile columns 4q..4q+11
+        const uint2 top = tp[1], bot = tp[6 * nW + 1];                             // columns 4..7 of rows y-3, y+3
+        const uint2 c01 = tp[3 * nW], c23 = tp[3 * nW + 1], c45 = tp[3 * nW + 2];
+        const uint32_t C[6] = {c01.x, c01.y, c23.x, c23.y, c45.x, c45.y};
+        const uint32_t b01 = fast_compass_bound(top.x, bot.x, pair16<7>(C), pair16<1>(C), C[2], negThBias);
+        const uint32_t b23 = fast_compass_bound(top.y, bot.y, pair16<9>(C), pair16<3>(C), C[3], negThBias);
+        any = b01 | b23;
+        hi = __viaddmax_s16x2_relu(__vmaxu2(b01, b23), negIni, 0u);
+      }
+      const uint32_t maskA = __ballot_sync(0xffffffffu, hi != 0u);
+      const uint32_t maskB = __ballot_sync(0xffffffffu, any != 0u) & ~maskA;
+      if (any != 0u) {  // one store: front slot for class A, back slot for class B
+        const bool isA = hi != 0u;
+        const int rank = __popc((isA ? maskA : maskB) & below);
+        queue[isA ? nA + rank : backB - rank] = (uint16_t)((y << 8) | q);
+      }
+      nA += __popc(maskA);
+      backB -= __popc(maskB);
+      y += dy; q += dq;
+      if (q >= nG) { q -= nG; y++; }
+    }
+  }
+  __syncwarp();
+  const int nB = nTasks - 1 - backB;
+  if (nA + nB == 0) return;
 
+  // Phase 0 scores list A and suppresses at iniTh. A pixel above iniTh can only lose to a neighbour whose margin
+  // is also above iniTh, and such a neighbour's task is in A: the phase-0 result is exactly cv::FAST(cell, iniTh).
+  // If it is empty (:875-883), phase 1 scores list B as well and suppresses everything at minTh.
+  uint32_t* kept = tile;  // survivors' score words; only written once the patch is dead (see below)
+  int nQ = 0;             // tasks whose score word holds a corner at minTh: queue[0 .. nQ)
+  int nS = 0;             // tasks that keep a corner after suppression: queue[0 .. nS), kept[0 .. nS)
 #pragma unroll 1
-  for (; work < totalWork; work += stride) {
-    const FastCell cur = nxt;
-    if (!cur.valid) {
-      nxt = fast_cell_of(pyr, g, work + stride, totalWork);
-      if (nxt.valid && nxt.bulk) fast_issue_rows(nxt, raw, rawPitch, bar, lane);
-      continue;
-    }
-    const LevelGeom& L = g.lv[cur.level];
-    const int level = cur.level, f = cur.f, ci = cur.ci, cj = cur.cj;
-    const int ch = cur.ch, sw = cur.sw, sh = cur.sh;
-    const int a = cur.iniX + 3 - cur.gx0;
-    const int b = a + sw;
-    const int nG = (b - 1) >> 2;  // groups q = 0..nG-1 cover tile words 1..nG
-    const int nW = nG + 2;        // staged words per row
-    uint32_t* smap = tile + ch * 2 * nW;              // (sh+2) rows x nW words, rows 0 and sh+1 stay zero
-    uint16_t* queue = reinterpret_cast<uint16_t*>(smap + (sh + 2) * nW);  // y<<8 | q of the tasks worth a second look
-
-    {
-      // Word idx of the patch (row idx / nW, word idx % nW) goes to tile[2 idx]; lane handles idx = lane, lane+32, ...
-      // Row and column advance incrementally (32 = dr * nW + dc per step), so a word costs a pointer add, the load,
-      // two PRMT and one 8-byte store.
-      const int total = ch * nW;
-      const int dr = div_small(32, nW), dc = 32 - dr * nW;
-      int r = div_small(lane, nW);
-      int c = lane - r * nW;
-      if (cur.bulk) {
-#ifndef ORBX_FAST_EXP2
-        mbar_wait(bar, parity);
-        parity ^= 1u;
-#endif
-        const uint8_t* p = raw + (cur.gx0 & 15) + r * rawPitch + 4 * c;
-        const int stepNoWrap = dr * rawPitch + 4 * dc;
-        const int stepWrap = stepNoWrap + rawPitch - 4 * nW;
-#pragma unroll 4
-        for (int idx = lane; idx < total; idx += 32) {
-          const uint32_t w = *reinterpret_cast<const uint32_t*>(p);
-          // bytes -> 16-bit lanes once here instead of once per ring offset in the scoring loop
-          *reinterpret_cast<uint2*>(&tile[2 * idx]) = make_uint2(__byte_perm(w, 0u, 0x4140), __byte_perm(w, 0u, 0x4342));
-          c += dc;
-          const bool wrap = c >= nW;
-          p += wrap ? stepWrap : stepNoWrap;
-          if (wrap) c -= nW;
-        }
-      } else {
-        // synchronous path (plane base or pitch not 16-byte aligned): eight loads in flight per lane
-        const int pitch = cur.pitch;
-        const bool aligned = ((reinterpret_cast<uintptr_t>(cur.src) | (uintptr_t)pitch) & 3) == 0;
-        const uint8_t* p = cur.src + (long long)r * pitch + 4 * c;
-        const long long stepNoWrap = (long long)dr * pitch + 4 * dc;
-        const long long stepWrap = stepNoWrap + pitch - 4 * nW;
-        constexpr int kInFlight = 8;
-        auto stage = [&](auto alignedTag) {
-          constexpr bool kAligned = decltype(alignedTag)::value;
-          for (int base = lane; base < total; base += 32 * kInFlight) {
-            uint32_t w[kInFlight];
+  for (int phase = 0; phase < 2; phase++) {
+    const int srcBase = phase == 0 ? 0 : nTasks - nB;
+    const int srcN = phase == 0 ? nA : nB;
+    // ---- pass 2, listed tasks: score map max(m - minTh, 0) (0 = not a corner at minTh). Only a task whose
+    //      word holds a corner can keep one after suppression: those are appended to queue[0 .. nQ). Entry j of
+    //      a round is read before the round's ballot and nQ never overtakes the read position (phase 0: nQ <=
+    //      entries read; phase 1: nQ <= nA + entries of B read <= nTasks - nB + entries read). ----
+    for (int j0 = 0; j0 < srcN; j0 += 32) {
+      uint32_t word = 0u;
+      int e = 0;
+      if (j0 + lane < srcN) {
+        e = queue[srcBase + j0 + lane];
+        const int y = e >> 8, q = e & 0xff;
+        const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);
+        uint32_t W[7][6];
 #pragma unroll
-            for (int k = 0; k < kInFlight; k++) {
-              w[k] = 0u;
-              if (base + 32 * k < total) {
-                if constexpr (kAligned) {
-                  w[k] = *reinterpret_cast<const uint32_t*>(p);
-                } else {
-                  w[k] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
-                }
-              }
-              c += dc;
-              const bool wrap = c >= nW;
-              p += wrap ? stepWrap : stepNoWrap;
-              if (wrap) c -= nW;
-            }
-#pragma unroll
-            for (int k = 0; k < kInFlight; k++) {
-              if (base + 32 * k < total)
-                *reinterpret_cast<uint2*>(&tile[2 * (base + 32 * k)]) =
-                    make_uint2(__byte_perm(w[k], 0u, 0x4140), __byte_perm(w[k], 0u, 0x4342));
-            }
-          }
-        };
-        if (aligned) stage(std::true_type{});
-        else stage(std::false_type{});
-      }
-    }
-    for (int i = lane; i < (sh + 2) * nW; i += 32) smap[i] = 0u;
-    __syncwarp();
-    // the raw rows are consumed: the next cell's rows start landing while this one is scored
-    nxt = fast_cell_of(pyr, g, work + stride, totalWork);
-    if (nxt.valid && nxt.bulk) fast_issue_rows(nxt, raw, rawPitch, bar, lane);
-
-    const int nTasks = sh * nG;
-    const int dy = div_small(32, nG), dq = 32 - dy * nG;
-    const int y0 = div_small(lane, nG), q0 = lane - y0 * nG;
-
-    // ---- pass 1, every task: compass bound. Any 9-arc of the ring contains two adjacent compass pixels
-    //      (p0, p4, p8, p12), so  A >= Ac = min over adjacent compass pairs of their max  and
-    //      B <= Bc = max over those pairs of their min, hence m <= max(v - Ac, Bc - v): a task whose four
-    //      bounds are all <= minTh has an all-zero score word and is dropped after 12 instead of 92 packed
-    //      operations per pixel pair. The others are queued as y<<8 | q in two classes: list A (some bound
-    //      above iniTh) grows from the front of the queue, list B (bounds in (minTh, iniTh]) from its back.
-    //      B is only ever scored if the cell turns out empty at iniTh (phase 1 below). Rounds are warp-uniform
-    //      (lanes past the last task idle inside the round) so that the ballots are full-warp ones. ----
-    int nA = 0, backB = nTasks - 1;  // next free slot of list B
-    {
-      int y = y0, q = q0;
-      for (int t0 = 0; t0 < nTasks; t0 += 32) {
-        uint32_t any = 0u, hi = 0u;
-        if (t0 + lane < nTasks) {
-          const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);  // window = tile columns 4q..4q+11
-          const uint2 top = tp[1], bot = tp[6 * nW + 1];                             // columns 4..7 of rows y-3, y+3
-          const uint2 c01 = tp[3 * nW], c23 = tp[3 * nW + 1], c45 = tp[3 * nW + 2];
-          const uint32_t C[6] = {c01.x, c01.y, c23.x, c23.y, c45.x, c45.y};
-          const uint32_t b01 = fast_compass_bound(top.x, bot.x, pair16<7>(C), pair16<1>(C), C[2], negThBias);
-          const uint32_t b23 = fast_compass_bound(top.y, bot.y, pair16<9>(C), pair16<3>(C), C[3], negThBias);
-          any = b01 | b23;
-          hi = __viaddmax_s16x2_relu(__vmaxu2(b01, b23), negIni, 0u);
+        for (int j = 0; j < 7; j++) {
+          const uint2 w01 = tp[j * nW], w23 = tp[j * nW + 1], w45 = tp[j * nW + 2];
+          W[j][0] = w01.x; W[j][1] = w01.y; W[j][2] = w23.x; W[j][3] = w23.y; W[j][4] = w45.x; W[j][5] = w45.y;
         }
-        const uint32_t maskA = __ballot_sync(0xffffffffu, hi != 0u);
-        const uint32_t maskB = __ballot_sync(0xffffffffu, any != 0u) & ~maskA;
-        if (any != 0u) {  // one store: front slot for class A, back slot for class B
-          const bool isA = hi != 0u;
-          const int rank = __popc((isA ? maskA : maskB) & below);
-          queue[isA ? nA + rank : backB - rank] = (uint16_t)((y << 8) | q);
-        }
-        nA += __popc(maskA);
-        backB -= __popc(maskB);
-        y += dy; q += dq;
-        if (q >= nG) { q -= nG; y++; }
+        const uint32_t u01 = fast_margin2<4>(W, negThBias);
+        const uint32_t u23 = fast_margin2<6>(W, negThBias);
+        word = __byte_perm(u01, u23, 0x6420);
+        const int col0 = 4 * (q + 1);
+        const int skipLo = a - col0, skipHi = col0 + 4 - b;
+        if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
+        if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
+        smap[(y + 1) * nW + q + 1] = word;
       }
+      const uint32_t liveMask = __ballot_sync(0xffffffffu, word != 0u);
+      if (word != 0u) queue[nQ + __popc(liveMask & (below))] = (uint16_t)e;
+      nQ += __popc(liveMask);
     }
     __syncwarp();
-    const int nB = nTasks - 1 - backB;
-    if (nA + nB == 0) continue;
 
-    // Phase 0 scores list A and suppresses at iniTh. A pixel above iniTh can only lose to a neighbour whose margin
-    // is also above iniTh, and such a neighbour's task is in A: the phase-0 result is exactly cv::FAST(cell, iniTh).
-    // If it is empty (:875-883), phase 1 scores list B as well and suppresses everything at minTh.
-    uint32_t* kept = tile;  // survivors' score words; only written once the patch is dead (see below)
-    int nQ = 0;             // tasks whose score word holds a corner at minTh: queue[0 .. nQ)
-    int nS = 0;             // tasks that keep a corner after suppression: queue[0 .. nS), kept[0 .. nS)
-#pragma unroll 1
-    for (int phase = 0; phase < 2; phase++) {
-      const int srcBase = phase == 0 ? 0 : nTasks - nB;
-      const int srcN = phase == 0 ? nA : nB;
-      // ---- pass 2, listed tasks: score map max(m - minTh, 0) (0 = not a corner at minTh). Only a task whose
-      //      word holds a corner can keep one after suppression: those are appended to queue[0 .. nQ). Entry j of
-      //      a round is read before the round's ballot and nQ never overtakes the read position (phase 0: nQ <=
-      //      entries read; phase 1: nQ <= nA + entries of B read <= nTasks - nB + entries read). ----
-      for (int j0 = 0; j0 < srcN; j0 += 32) {
-        uint32_t word = 0u;
-        int e = 0;
-        if (j0 + lane < srcN) {
-          e = queue[srcBase + j0 + lane];
-          const int y = e >> 8, q = e & 0xff;
-          const uint2* tp = reinterpret_cast<const uint2*>(&tile[(y * nW + q) * 2]);
-          uint32_t W[7][6];
+    // ---- cell-local 3x3 strict non-max suppression, packed: the 8-neighbour maximum of two adjacent pixels is
+    //      4 VIMNMX on 16x2 lanes. Scores below this phase's threshold are cleared and the tasks that keep a
+    //      corner are compacted in place once more, their score words going to kept[], which reuses the patch
+    //      rows: a word is only stored when a survivor exists, i.e. when no further phase needs the patch (and
+    //      then nothing was compacted either: queue[0 .. nQ) is still whole for phase 1). ----
+    const uint32_t negKeep = phase == 0 ? negIni : 0u;
+    for (int j0 = 0; j0 < nQ; j0 += 32) {
+      uint32_t word = 0u;
+      int e = 0;
+      if (j0 + lane < nQ) {
+        e = queue[j0 + lane];
+        const int y = e >> 8, q = e & 0xff;
+        const uint32_t* mp = &smap[y * nW + q];  // map rows y, y+1, y+2 = image rows y-1, y, y+1
+        uint32_t E[3][5];                        // column pairs (3,4) (4,5) (5,6) (6,7) (7,8) of the 12-byte window
 #pragma unroll
-          for (int j = 0; j < 7; j++) {
-            const uint2 w01 = tp[j * nW], w23 = tp[j * nW + 1], w45 = tp[j * nW + 2];
-            W[j][0] = w01.x; W[j][1] = w01.y; W[j][2] = w23.x; W[j][3] = w23.y; W[j][4] = w45.x; W[j][5] = w45.y;
-          }
-          const uint32_t u01 = fast_margin2<4>(W, negThBias);
-          const uint32_t u23 = fast_margin2<6>(W, negThBias);
-          word = __byte_perm(u01, u23, 0x6420);
-          const int col0 = 4 * (q + 1);
-          const int skipLo = a - col0, skipHi = col0 + 4 - b;
-          if (skipLo > 0) word &= 0xffffffffu << (8 * skipLo);
-          if (skipHi > 0) word &= 0xffffffffu >> (8 * skipHi);
-          smap[(y + 1) * nW + q + 1] = word;
+        for (int r = 0; r < 3; r++) {
+          const uint32_t w0 = mp[r * nW], w1 = mp[r * nW + 1], w2 = mp[r * nW + 2];
+          E[r][0] = ex2<3>(w0, w1, w2);
+          E[r][1] = ex2<4>(w0, w1, w2);
+          E[r][2] = ex2<5>(w0, w1, w2);
+          E[r][3] = ex2<6>(w0, w1, w2);
+          E[r][4] = ex2<7>(w0, w1, w2);
         }
-        const uint32_t liveMask = __ballot_sync(0xffffffffu, word != 0u);
-        if (word != 0u) queue[nQ + __popc(liveMask & (below))] = (uint16_t)e;
-        nQ += __popc(liveMask);
+        uint32_t k2[2];
+#pragma unroll
+        for (int p = 0; p < 2; p++) {  // pixel pairs (0,1) and (2,3): left/centre/right pairs E[.][2p .. 2p+2]
+          const uint32_t up = __vimax3_u16x2(E[0][2 * p], E[0][2 * p + 1], E[0][2 * p + 2]);
+          const uint32_t dn = __vimax3_u16x2(E[2][2 * p], E[2][2 * p + 1], E[2][2 * p + 2]);
+          const uint32_t M = __vimax3_u16x2(up, dn, __vmaxu2(E[1][2 * p], E[1][2 * p + 2]));
+          const uint32_t sc = E[1][2 * p + 1];
+          const uint32_t d = __viaddmax_s16x2_relu(sc + 0x01000100u - M, 0xff00ff00u, 0u);  // max(s - M, 0)
+          const uint32_t won = __vminu2(sc, d << 8);                                         // s if s > M else 0
+          // keep s only if s >= threshold byte: max(s - (th-1), 0) != 0 per lane
+          const uint32_t over = __viaddmax_s16x2_relu(won, negKeep, 0u);
+          k2[p] = __vminu2(won, over * 0xffu);  // over <= 255 per lane: over*255 >= won iff over != 0
+        }
+        word = __byte_perm(k2[0], k2[1], 0x6420);
       }
-      __syncwarp();
-
-      // ---- cell-local 3x3 strict non-max suppression, packed: the 8-neighbour maximum of two adjacent pixels is
-      //      4 VIMNMX on 16x2 lanes. Scores below this phase's threshold are cleared and the tasks that keep a
-      //      corner are compacted in place once more, their score words going to kept[], which reuses the patch
-      //      rows: a word is only stored when a survivor exists, i.e. when no further phase needs the patch (and
-      //      then nothing was compacted either: queue[0 .. nQ) is still whole for phase 1). ----
-      const uint32_t negKeep = phase == 0 ? negIni : 0u;
-      for (int j0 = 0; j0 < nQ; j0 += 32) {
-        uint32_t word = 0u;
-        int e = 0;
-        if (j0 + lane < nQ) {
-          e = queue[j0 + lane];
-          const int y = e >> 8, q = e & 0xff;
-          const uint32_t* mp = &smap[y * nW + q];  // map rows y, y+1, y+2 = image rows y-1, y, y+1
-          uint32_t E[3][5];                        // column pairs (3,4) (4,5) (5,6) (6,7) (7,8) of the 12-byte window
-#pragma unroll
-          for (int r = 0; r < 3; r++) {
-            const uint32_t w0 = mp[r * nW], w1 = mp[r * nW + 1], w2 = mp[r * nW + 2];
-            E[r][0] = ex2<3>(w0, w1, w2);
-            E[r][1] = ex2<4>(w0, w1, w2);
-            E[r][2] = ex2<5>(w0, w1, w2);
-            E[r][3] = ex2<6>(w0, w1, w2);
-            E[r][4] = ex2<7>(w0, w1, w2);
-          }
-          uint32_t k2[2];
-#pragma unroll
-          for (int p = 0; p < 2; p++) {  // pixel pairs (0,1) and (2,3): left/centre/right pairs E[.][2p .. 2p+2]
-            const uint32_t up = __vimax3_u16x2(E[0][2 * p], E[0][2 * p + 1], E[0][2 * p + 2]);
-            const uint32_t dn = __vimax3_u16x2(E[2][2 * p], E[2][2 * p + 1], E[2][2 * p + 2]);
-            const uint32_t M = __vimax3_u16x2(up, dn, __vmaxu2(E[1][2 * p], E[1][2 * p + 2]));
-            const uint32_t sc = E[1][2 * p + 1];
-            const uint32_t d = __viaddmax_s16x2_relu(sc + 0x01000100u - M, 0xff00ff00u, 0u);  // max(s - M, 0)
-            const uint32_t won = __vminu2(sc, d << 8);                                         // s if s > M else 0
-            // keep s only if s >= threshold byte: max(s - (th-1), 0) != 0 per lane
-            const uint32_t over = __viaddmax_s16x2_relu(won, negKeep, 0u);
-            k2[p] = __vminu2(won, over * 0xffu);  // over <= 255 per lane: over*255 >= won iff over != 0
-          }
-          word = __byte_perm(k2[0], k2[1], 0x6420);
-        }
-        const uint32_t keepMask = __ballot_sync(0xffffffffu, word != 0u);
-        if (word != 0u) {
-          const int slot = nS + __popc(keepMask & (below));
-          queue[slot] = (uint16_t)e;
-          kept[slot] = word;
-        }
-        nS += __popc(keepMask);
+      const uint32_t keepMask = __ballot_sync(0xffffffffu, word != 0u);
+      if (word != 0u) {
+        const int slot = nS + __popc(keepMask & (below));
+        queue[slot] = (uint16_t)e;
+        kept[slot] = word;
       }
-      __syncwarp();
-      if (nS > 0 || iniByte == 1) break;  // iniByte == 1: phase 0 already was the suppression at minTh
+      nS += __popc(keepMask);
     }
-    if (nS == 0) continue;
+    __syncwarp();
+    if (nS > 0 || iniByte == 1) break;  // iniByte == 1: phase 0 already was the suppression at minTh
+  }
+  if (nS == 0) return;
 
-    int mine = 0;
-    for (int j = lane; j < nS; j += 32) {
-      const uint32_t word = kept[j];
+  int mine = 0;
+  for (int j = lane; j < nS; j += 32) {
+    const uint32_t word = kept[j];
 #pragma unroll
-      for (int i = 0; i < 4; i++) mine += ((word >> (8 * i)) & 0xff) != 0;
-    }
-    // exclusive prefix of `mine` over the warp + total
-    int incl = mine;
+    for (int i = 0; i < 4; i++) mine += ((word >> (8 * i)) & 0xff) != 0;
+  }
+  // exclusive prefix of `mine` over the warp + total
+  int incl = mine;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    const int total = __shfl_sync(0xffffffffu, incl, 31);
-    int base = 0;
-    if (lane == 0) {
-      base = atomicAdd(&candCount[f * nl + level], total);
-      if (base + total > L.candCap) atomicExch(overflow, 1);
-    }
-    base = __shfl_sync(0xffffffffu, base, 0);
-    int slot = base + incl - mine;
-    const long long slotBase = L.candOff + (long long)f * L.candCap;
-    for (int j = lane; j < nS; j += 32) {
-      const uint32_t word = kept[j];
-      const int e = queue[j], y = e >> 8, q = e & 0xff;
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  const int total = __shfl_sync(0xffffffffu, incl, 31);
+  int base = 0;
+  if (lane == 0) {
+    base = atomicAdd(&candCount[f * nl + level], total);
+    if (base + total > L.candCap) atomicExch(overflow, 1);
+  }
+  base = __shfl_sync(0xffffffffu, base, 0);
+  int slot = base + incl - mine;
+  const long long slotBase = L.candOff + (long long)f * L.candCap;
+  for (int j = lane; j < nS; j += 32) {
+    const uint32_t word = kept[j];
+    const int e = queue[j], y = e >> 8, q = e & 0xff;
 #pragma unroll
-      for (int i = 0; i < 4; i++) {
-        const int sc = (word >> (8 * i)) & 0xff;
-        if (sc) {
-          // cv::FAST's cornerScore = sc + minTh - 1; coordinates relative to minBorder:
-          // cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
-          if (slot < L.candCap)
-            cand[slotBase + slot] = pack_cand(4 * (q + 1) + i - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, sc + minTh - 1);
-          slot++;
-        }
+    for (int i = 0; i < 4; i++) {
+      const int sc = (word >> (8 * i)) & 0xff;
+      if (sc) {
+        // cv::FAST's cornerScore = sc + minTh - 1; coordinates relative to minBorder:
+        // cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
+        if (slot < L.candCap)
+          cand[slotBase + slot] = pack_cand(4 * (q + 1) + i - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, sc + minTh - 1);
+        slot++;
       }
     }
-    __syncwarp();  // kept[] / queue[] are read out before the next cell's expansion overwrites the patch
   }
 }
 
 int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
                 int nframes, cudaStream_t s) {
-  int tileWords = 0, rawRow = 0, maxRows = 0;
-  for (int l = 0; l < hGeom.nlevels; l++) {
-    tileWords = max(tileWords, fast_tile_words(hGeom.lv[l].wCell, hGeom.lv[l].hCell));
-    rawRow = max(rawRow, fast_raw_row_bytes(hGeom.lv[l].wCell));
-    maxRows = max(maxRows, hGeom.lv[l].hCell + 6);
-  }
-  if (rawRow > kRawRowMax) return (int)cudaErrorInvalidConfiguration;  // cells wider than 60 pixels do not occur (:844-847)
-  const int words = tileWords + maxRows * rawRow / 4;
+  int words = 0;
+  for (int l = 0; l < hGeom.nlevels; l++) words = max(words, fast_cell_words(hGeom.lv[l].wCell, hGeom.lv[l].hCell));
   const size_t smem = (size_t)words * 4 * kFastWarps;
   static SmemLimit limit;
   cudaError_t e = raise_dynamic_smem(reinterpret_cast<const void*>(fast_cells_kernel), smem, &limit);
   if (e != cudaSuccess) return (int)e;
-  // persistent warps: as many CTAs as stay resident, each warp strides over the (frame, cell) list
-  static std::mutex mu;
-  static int smCount[64] = {};
-  static int perSm[64] = {};
-  static size_t perSmFor[64] = {};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  dev &= 63;
-  int resident;
-  {
-    std::lock_guard<std::mutex> lock(mu);
-    if (!smCount[dev]) cudaDeviceGetAttribute(&smCount[dev], cudaDevAttrMultiProcessorCount, dev);
-    if (!perSm[dev] || perSmFor[dev] != smem) {
-      int n = 0;
-      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fast_cells_kernel, kFastThreads, smem);
-      if (e != cudaSuccess) return (int)e;
-      perSm[dev] = max(n, 1);
-      perSmFor[dev] = smem;
-    }
-    resident = smCount[dev] * perSm[dev];
-  }
-  const long long totalWork = (long long)hGeom.totalCells * nframes;
-  if (totalWork > 0x7fffffffLL) return (int)cudaErrorInvalidValue;
-  const int wanted = (int)((totalWork + kFastWarps - 1) / kFastWarps);
-  dim3 grid(min(wanted, resident));
-  launch_pdl(fast_cells_kernel, grid, dim3(kFastThreads), smem, s, pyr, hGeom, cand, candCount, overflow, words, tileWords,
-             rawRow, (int)totalWork);
+  dim3 grid((hGeom.totalCells + kFastWarps - 1) / kFastWarps, nframes);
+  launch_pdl(fast_cells_kernel, grid, dim3(kFastThreads), smem, s, pyr, hGeom, cand, candCount, overflow, words);
   return 0;
 }
 
