@@ -884,12 +884,14 @@ def run_hamming(c, pkg, args):
     # ---- the bound: integer issue, not HBM ----
     clk = (clocks or {}).get("sm_mhz") or 1965.0
     sms = torch.cuda.get_device_properties(c.local).multi_processor_count
-    alu_peak = sms * 64 * clk * 1e6 / 18.5 / 1e9 * world       # Gpairs/s if the ALU pipe did nothing but this kernel's 18.5 ops per pair
+    ALU_OPS = 16.75   # 8 XOR + 8 LOP3 (carry-save adders) + 0.5 VIMNMX3 + 0.25 ISETP per pair (csrc/orbx_match.cu)
+    alu_peak = sms * 64 * clk * 1e6 / ALU_OPS / 1e9 * world    # Gpairs/s if the ALU pipe did nothing but this kernel's ops
     popc_peak = sms * 16 * clk * 1e6 / 4 / 1e9 * world
     roof = {"bound": "alu", "kernel": "bf2_kernel", "achieved": gp, "peak": alu_peak, "unit": "Gpairs/s", "frac": gp / alu_peak,
             "traffic": None,
-            "peak_source": f"{sms} SMs x 64 ALU-pipe lanes/clk x {clk:.0f} MHz (median under load) / 18.5 ALU-pipe ops per pair "
-                           "(8 XOR + 8 LOP3 + 2.5 VIMNMX; profiles/r1_pipe_probe.txt), x N GPUs",
+            "peak_source": f"{sms} SMs x 64 ALU-pipe lanes/clk x {clk:.0f} MHz (median under load) / {ALU_OPS} ALU-pipe ops per pair "
+                           "(8 XOR + 8 LOP3 + 0.5 VIMNMX3 + 0.25 ISETP; pipe rates: profiles/r1_pipe_probe.txt), x N GPUs; the 4 POPC per pair "
+                           "on the quarter-rate pipe (popc_pipe_peak) co-limit the loop",
             "popc_pipe_peak": popc_peak, "popc_pipe_frac": gp / popc_peak,
             "hbm_gbs": (HAM_NDB * 32 / world) / (ms * 1e-3) / 1e9, "hbm_frac": (HAM_NDB * 32 / world) / (ms * 1e-3) / 1e9 / c.peak,
             "note": "not HBM-bound by construction: 320 MB of compulsory traffic against 1e11 pairs"}

@@ -1,7 +1,7 @@
 // Hamming matching kernels (R/src/ORBmatcher.cpp DescriptorDistance
 // :1901-1917 and the running best / second-best loops :266-300, :526-556).
 //
-// Brute-force top-2: bound by the integer pipe (8 XOR + 8 POPC per pair), not by HBM: a 32-byte
+// Brute-force top-2: bound by the integer pipe (8 XOR + 8 LOP3 + 4 POPC per pair after carry-save compression), not by HBM: a 32-byte
 // database row is read once per CTA from global memory and reused by 1024 queries from shared
 // memory (broadcast LDS), queries live in registers. No tensor cores: Hamming distance is not a
 // dense contraction and sm_100a has no native 1-bit MMA.
@@ -22,6 +22,10 @@ constexpr int kBfQPT = 4;                       // queries per thread
 constexpr int kBfQueriesPerCta = kBfThreads * kBfQPT;
 constexpr int kBfTileRows = 512;                // database rows staged per step (16 KB)
 constexpr unsigned kKeyNone = 0xFFFFFFFFu;
+#ifndef ORBX_BF_GROUP
+#define ORBX_BF_GROUP 4
+#endif
+constexpr int kBfGroup = ORBX_BF_GROUP;         // rows per guarded group (even)
 
 __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
   return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
@@ -92,6 +96,46 @@ bf2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, lo
     __syncthreads();
     unsigned rowKey = (unsigned)(t0 - rowBegin);
     int r = 0;
+    // Groups of kBfGroup rows: the fast path only tracks the smallest key of the group per query (half a VIMNMX3
+    // per pair) and compares it with the query's second-best key once per group. A key >= k2 (>= k1) changes
+    // neither k1 nor k2, so a group without a key below k2 is skipped exactly; after n rows a group holds an
+    // improving row with probability ~2*kBfGroup/n, so the exact update (5 min/max per row pair) runs on a few
+    // per cent of the groups only (ALU-pipe operations per pair: 8 XOR + 8 LOP3 + 0.5 VIMNMX3 + 0.25 ISETP instead of
+    // + 2.5 VIMNMX). Measured on config 5 (10k x 10M, 1 GPU): unguarded 801, groups of 16 / 8 / 4 rows 777 / 818 / 841
+    // Gpairs/s -- with the ALU pipe relieved the 4 POPC per pair (a quarter-rate pipe: 32 issue cycles per pair against
+    // 33 on the ALU pipe) co-limit the loop.
+    for (; r + kBfGroup <= rows; r += kBfGroup, rowKey += kBfGroup) {
+      unsigned m[kBfQPT];
+#pragma unroll
+      for (int k = 0; k < kBfQPT; k++) m[k] = kKeyNone;
+#pragma unroll
+      for (int i = 0; i < kBfGroup; i += 2) {
+        const uint4 d0 = tile[2 * (r + i)], d1 = tile[2 * (r + i) + 1], e0 = tile[2 * (r + i) + 2], e1 = tile[2 * (r + i) + 3];
+#pragma unroll
+        for (int k = 0; k < kBfQPT; k++) {
+          const unsigned ka = hamming_key(qa[k], qb[k], d0, d1, rowKey + i, km);
+          const unsigned kb = hamming_key(qa[k], qb[k], e0, e1, rowKey + i + 1, km);
+          m[k] = min(m[k], min(ka, kb));
+        }
+      }
+      bool improved = false;
+#pragma unroll
+      for (int k = 0; k < kBfQPT; k++) improved = improved || m[k] < k2[k];
+      if (improved) {
+#pragma unroll 1
+        for (int i = 0; i < kBfGroup; i += 2) {
+          const uint4 d0 = tile[2 * (r + i)], d1 = tile[2 * (r + i) + 1], e0 = tile[2 * (r + i) + 2], e1 = tile[2 * (r + i) + 3];
+#pragma unroll
+          for (int k = 0; k < kBfQPT; k++) {
+            const unsigned ka = hamming_key(qa[k], qb[k], d0, d1, rowKey + i, km);
+            const unsigned kb = hamming_key(qa[k], qb[k], e0, e1, rowKey + i + 1, km);
+            const unsigned lo = min(ka, kb), hi = max(ka, kb);
+            k2[k] = min(min(k2[k], hi), max(k1[k], lo));
+            k1[k] = min(k1[k], lo);
+          }
+        }
+      }
+    }
     // two rows per step: the (k1, k2) update of a sorted pair (lo, hi) is 5 min/max instead of 6
     for (; r + 1 < rows; r += 2, rowKey += 2) {
       const uint4 d0 = tile[2 * r], d1 = tile[2 * r + 1], e0 = tile[2 * r + 2], e1 = tile[2 * r + 3];
