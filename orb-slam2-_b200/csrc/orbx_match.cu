@@ -101,8 +101,10 @@ bf2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, lo
     // neither k1 nor k2, so a group without a key below k2 is skipped exactly; after n rows a group holds an
     // improving row with probability ~2*kBfGroup/n, so the exact update (5 min/max per row pair) runs on a few
     // per cent of the groups only (ALU-pipe operations per pair: 8 XOR + 8 LOP3 + 0.5 VIMNMX3 + 0.25 ISETP instead of
-    // + 2.5 VIMNMX). Measured on config 5 (10k x 10M, 1 GPU): unguarded 801, groups of 16 / 8 / 4 rows 777 / 818 / 841
-    // Gpairs/s -- with the ALU pipe relieved the 4 POPC per pair (a quarter-rate pipe: 32 issue cycles per pair against
+    // + 2.5 VIMNMX). Measured on config 5 (10k x 10M, 1 GPU): unguarded 801; exact update for all four queries of a thread
+    // when any improves, groups of 16 / 8 / 4 rows: 777 / 818 / 841; exact update per improving query (this code),
+    // groups of 16 / 8 / 4 / 2: 863 / 874 / 868 / 798 Gpairs/s, and 726 / 784 / 807 / 808 on one 1.25M-row shard of the
+    // 8-GPU split (shorter chunks spend more of their rows settling) -- with the ALU pipe relieved the 4 POPC per pair (a quarter-rate pipe: 32 issue cycles per pair against
     // 33 on the ALU pipe) co-limit the loop.
     for (; r + kBfGroup <= rows; r += kBfGroup, rowKey += kBfGroup) {
       unsigned m[kBfQPT];
@@ -118,15 +120,13 @@ bf2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, lo
           m[k] = min(m[k], min(ka, kb));
         }
       }
-      bool improved = false;
+      // exact update, only for the queries of this thread whose group minimum beats their second best
 #pragma unroll
-      for (int k = 0; k < kBfQPT; k++) improved = improved || m[k] < k2[k];
-      if (improved) {
+      for (int k = 0; k < kBfQPT; k++) {
+        if (m[k] < k2[k]) {
 #pragma unroll 1
-        for (int i = 0; i < kBfGroup; i += 2) {
-          const uint4 d0 = tile[2 * (r + i)], d1 = tile[2 * (r + i) + 1], e0 = tile[2 * (r + i) + 2], e1 = tile[2 * (r + i) + 3];
-#pragma unroll
-          for (int k = 0; k < kBfQPT; k++) {
+          for (int i = 0; i < kBfGroup; i += 2) {
+            const uint4 d0 = tile[2 * (r + i)], d1 = tile[2 * (r + i) + 1], e0 = tile[2 * (r + i) + 2], e1 = tile[2 * (r + i) + 3];
             const unsigned ka = hamming_key(qa[k], qb[k], d0, d1, rowKey + i, km);
             const unsigned kb = hamming_key(qa[k], qb[k], e0, e1, rowKey + i + 1, km);
             const unsigned lo = min(ka, kb), hi = max(ka, kb);
@@ -203,8 +203,12 @@ __global__ void distance_kernel(const uint4* __restrict__ a, const uint4* __rest
 }
 
 int bf2_plan_chunks(int nq, long long ndb, int smCount, int* rowsPerChunk) {
+  // ~8 CTAs per SM overall (2.7 waves of the 3 resident ones). Every chunk restarts its top-2 from scratch and runs
+  // the exact update until its second best has settled, so fewer chunks would be cheaper per pair, but exactly one
+  // wave of equal CTAs measured slower (config 5 on one GPU: 829 vs 868 Gpairs/s; one of its 8 shards: 799 vs 806):
+  // the dynamic hand-out of many CTAs balances the SMs better than one CTA set that finishes together.
   const int qGroups = (nq + kBfQueriesPerCta - 1) / kBfQueriesPerCta;
-  long long chunks = (8LL * smCount + qGroups - 1) / qGroups;  // ~8 CTAs per SM in flight overall
+  long long chunks = (8LL * smCount + qGroups - 1) / qGroups;
   const long long maxChunks = (ndb + kBfTileRows - 1) / kBfTileRows;
   chunks = max(1LL, min(chunks, maxChunks));
   long long rpc = (ndb + chunks - 1) / chunks;

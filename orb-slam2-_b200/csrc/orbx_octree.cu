@@ -1,8 +1,8 @@
 // DistributeOctTree on the GPU (R/src/ORBextractor.cpp:513-817).
 //
 // The reference walks a std::list of quadtree leaves serially. What it computes can be stated
-// without the list (this is what the kernel implements; tests/test_octree_parity.py checks it
-// against the list-walking oracle, order included):
+// without the list (this is what the kernel implements; tests/test_gpu_extractor.py::test_octree_matches_oracle_in_order
+// and tests/test_gpu_fuzz.py check it against the list-walking oracle, order included):
 //
 //  * The leaf list is always: [children created in the latest round, newest first] ++ [older leaves
 //    in their previous order]  (children are push_front'ed in creation order, parents erased in

@@ -3,8 +3,22 @@
 launches) DRAM bytes and pipe utilisation. bench.py copies these into roofline.traffic / roofline.limiter.
 Usage: python tools/ncu_digest.py gpurun_out/<tag>/pipeline_full_raw.csv profiles/<name>_pipeline_ncu_raw.csv 512"""
 import csv
+import hashlib
 import json
 import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def csrc_hash():
+    """the same hash bench.py computes over the kernel sources: the digest is only used for the build it describes"""
+    h = hashlib.sha256()
+    for p in sorted((ROOT / "orb-slam2-_b200" / "csrc").glob("*.cu*")):
+        h.update(p.name.encode())
+        h.update(p.read_bytes())
+    return h.hexdigest()[:16]
+
 
 M = {"dram_rd": "dram__bytes_read.sum", "dram_wr": "dram__bytes_write.sum",
      "alu": "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
@@ -30,9 +44,10 @@ def main(path, committed_as, frames):
         for k in ("alu", "fma", "issue", "l1"):
             d[k].append(f(k))
     out = {"_comment": "per pipeline step (one launch set over frames_per_launch frames), read from an ncu --set full capture; "
-                       "bench.py copies these into roofline.traffic / roofline.limiter. Regenerate with tools/ncu_digest.py.",
+                       "bench.py copies these into roofline.traffic / roofline.limiter when csrc_sha16 matches the kernel sources it "
+                       "times (run this script with the captured sources checked out). Regenerate with tools/ncu_digest.py.",
            "source": f"profiles/{committed_as} (ncu --set full --clock-control none, B200, {frames} frames per launch)",
-           "frames_per_launch": int(frames), "kernels": {}}
+           "frames_per_launch": int(frames), "workload": "C1", "csrc_sha16": csrc_hash(), "kernels": {}}
     for name, d in acc.items():
         out["kernels"][name] = {"dram_bytes": round(d["dram_bytes"]), "launches": d["launches"],
                                 "alu_pipe_pct": round(max(d["alu"]), 1), "fma_pipe_pct": round(max(d["fma"]), 1),
