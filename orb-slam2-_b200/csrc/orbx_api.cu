@@ -229,36 +229,44 @@ int ensure_lane_staging(Lane& L) {
   return ORBX_OK;
 }
 
-// The extraction pipeline on `count` frames whose level 0 is already on the device, on stream `s`.
-int run_pipeline(orbx_extractor* h, Lane& L, const uint8_t* dL0, int l0Pitch, long long l0FrameStride, int count,
-                 orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dN, cudaStream_t s) {
-  const FrameSetGeom& g = L.geom;
-  const int nl = g.nlevels;
+// Frames per call up to which the fork / join form of the pipeline is used (ORBX_FORK=0 disables it).
+int fork_frames() {
+  static const int v = [] {
+    const char* e = std::getenv("ORBX_FORK");
+    return e ? std::atoi(e) : 4;
+  }();
+  return v;
+}
+
+struct PipelineArgs {
   PyramidPtrs pyr;
-  for (int l = 0; l < kMaxLevels; l++) { pyr.lvl[l] = nullptr; pyr.frameStride[l] = 0; pyr.pitch[l] = 0; }
-  pyr.lvl[0] = dL0; pyr.frameStride[0] = l0FrameStride; pyr.pitch[0] = l0Pitch;
+  int count, cap;
+  orbx_keypoint* dKps;
+  uint8_t* dDesc;
+  int* dN;
+};
+
+// One stream after the other: what batches use (every kernel fills the GPU by itself; the programmatic launches hide
+// the launch latencies). Stage events for orbx_last_stage_ms when profiling.
+int enqueue_linear(orbx_extractor* h, Lane& L, const PipelineArgs& a, cudaStream_t s) {
+  const FrameSetGeom& g = L.geom;
+  const int nl = g.nlevels, count = a.count;
   uint8_t* arena = static_cast<uint8_t*>(L.pyrArena.p);
-  for (int l = 1; l < nl; l++) {
-    pyr.lvl[l] = arena + g.lv[l].planeOff;
-    pyr.frameStride[l] = g.lv[l].planeBytes;
-    pyr.pitch[l] = g.lv[l].pitch;
-  }
   int* candCount = static_cast<int*>(L.counts.p);
   int* keptCount = candCount + L.batchCap * nl;
   int* overflow = keptCount + L.batchCap * nl;
   const FrameSetGeom* dG = static_cast<const FrameSetGeom*>(L.dGeom.p);
   const bool prof = h->profiling;
-
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[0], s));
   ORBX_CUDA_TRY(cudaMemsetAsync(candCount, 0, (size_t)(2 * L.batchCap * nl + 1) * sizeof(int), s));
   for (int l = 1; l < nl; l++) {
-    launch_resize(pyr.lvl[l - 1], pyr.frameStride[l - 1], pyr.pitch[l - 1], g.lv[l - 1].w, g.lv[l - 1].h,
+    launch_resize(a.pyr.lvl[l - 1], a.pyr.frameStride[l - 1], a.pyr.pitch[l - 1], g.lv[l - 1].w, g.lv[l - 1].h,
                   arena + g.lv[l].planeOff, g.lv[l].planeBytes, g.lv[l].pitch, g.lv[l].w, g.lv[l].h, h->taps[l],
                   count, s);
     h->launches++;
   }
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[1], s));
-  int fe = launch_fast(pyr, g, static_cast<uint32_t*>(L.candArena.p), candCount, overflow, count, s);
+  int fe = launch_fast(a.pyr, g, static_cast<uint32_t*>(L.candArena.p), candCount, overflow, count, s);
   if (fe) { set_error("FAST kernel configuration failed: %s", cudaGetErrorString((cudaError_t)fe)); return ORBX_ERR_CUDA; }
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[2], s));
@@ -268,14 +276,136 @@ int run_pipeline(orbx_extractor* h, Lane& L, const uint8_t* dL0, int l0Pitch, lo
   if (oe) { set_error("octree kernel configuration failed: %s", cudaGetErrorString((cudaError_t)oe)); return ORBX_ERR_CUDA; }
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[3], s));
-  launch_blur(pyr, g, static_cast<uint8_t*>(L.blurArena.p), count, s);
+  launch_blur(a.pyr, g, static_cast<uint8_t*>(L.blurArena.p), count, s);
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[4], s));
-  launch_describe(pyr, static_cast<const uint8_t*>(L.blurArena.p), g, static_cast<const uint32_t*>(L.keptArena.p),
-                  keptCount, candCount, dKps, dDesc, cap, dN, count, s);
+  launch_describe(a.pyr, static_cast<const uint8_t*>(L.blurArena.p), g, static_cast<const uint32_t*>(L.keptArena.p),
+                  keptCount, candCount, a.dKps, a.dDesc, a.cap, a.dN, count, s);
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[5], s));
   ORBX_CUDA_TRY(cudaGetLastError());
+  return ORBX_OK;
+}
+
+// Fork / join: s carries the memset, the resize chain and the blur; aux[l] carries FAST + octree of level l from the
+// moment level l exists (level 0: at once); describe joins everything. One frame is far too small to fill the GPU, so
+// its latency is the longest dependent chain: 7 resizes + FAST + octree + blur + describe in a row before (107 us at
+// 640x480), max(resizes + blur, l resizes + FAST(l) + octree(l)) + describe now. Plain launches (no programmatic
+// edges): the set is meant to be captured. *kernels = number of kernel launches enqueued.
+int enqueue_forked(orbx_extractor* h, Lane& L, const PipelineArgs& a, cudaStream_t s, int* kernels) {
+  const FrameSetGeom& g = L.geom;
+  const int nl = g.nlevels, count = a.count;
+  uint8_t* arena = static_cast<uint8_t*>(L.pyrArena.p);
+  int* candCount = static_cast<int*>(L.counts.p);
+  int* keptCount = candCount + L.batchCap * nl;
+  int* overflow = keptCount + L.batchCap * nl;
+  const FrameSetGeom* dG = static_cast<const FrameSetGeom*>(L.dGeom.p);
+  int n = 0;
+  static const bool keepPdl = [] { const char* e = std::getenv("ORBX_FORK_PDL"); return e && std::atoi(e) > 0; }();
+  struct PdlOff { PdlOff() { tl_programmatic_launch = keepPdl; } ~PdlOff() { tl_programmatic_launch = true; } } pdlOff;
+  ORBX_CUDA_TRY(cudaMemsetAsync(candCount, 0, (size_t)(2 * L.batchCap * nl + 1) * sizeof(int), s));
+  for (int l = 0; l < nl; l++) {
+    if (l > 0) {
+      launch_resize(a.pyr.lvl[l - 1], a.pyr.frameStride[l - 1], a.pyr.pitch[l - 1], g.lv[l - 1].w, g.lv[l - 1].h,
+                    arena + g.lv[l].planeOff, g.lv[l].planeBytes, g.lv[l].pitch, g.lv[l].w, g.lv[l].h, h->taps[l],
+                    count, s);
+      n++;
+    }
+    ORBX_CUDA_TRY(cudaEventRecord(L.evFork[l], s));
+    ORBX_CUDA_TRY(cudaStreamWaitEvent(L.aux[l], L.evFork[l], 0));
+    int fe = launch_fast(a.pyr, g, static_cast<uint32_t*>(L.candArena.p), candCount, overflow, count, L.aux[l], l, l + 1);
+    if (fe) { set_error("FAST kernel configuration failed: %s", cudaGetErrorString((cudaError_t)fe)); return ORBX_ERR_CUDA; }
+    int oe = launch_octree(dG, g, static_cast<const uint32_t*>(L.candArena.p), candCount, static_cast<uint16_t*>(L.nodeArena.p),
+                           static_cast<uint32_t*>(L.keptArena.p), keptCount, count, L.aux[l], l, l + 1);
+    if (oe) { set_error("octree kernel configuration failed: %s", cudaGetErrorString((cudaError_t)oe)); return ORBX_ERR_CUDA; }
+    n += 2;
+    ORBX_CUDA_TRY(cudaEventRecord(L.evJoin[l], L.aux[l]));
+  }
+  launch_blur(a.pyr, g, static_cast<uint8_t*>(L.blurArena.p), count, s);
+  n++;
+  for (int l = 0; l < nl; l++) ORBX_CUDA_TRY(cudaStreamWaitEvent(s, L.evJoin[l], 0));
+  launch_describe(a.pyr, static_cast<const uint8_t*>(L.blurArena.p), g, static_cast<const uint32_t*>(L.keptArena.p),
+                  keptCount, candCount, a.dKps, a.dDesc, a.cap, a.dN, count, s);
+  n++;
+  ORBX_CUDA_TRY(cudaGetLastError());
+  *kernels = n;
+  return ORBX_OK;
+}
+
+int ensure_fork_resources(Lane& L, int nl) {
+  for (int l = 0; l < nl; l++) {
+    if (!L.aux[l]) ORBX_CUDA_TRY(cudaStreamCreateWithFlags(&L.aux[l], cudaStreamNonBlocking));
+    if (!L.evFork[l]) ORBX_CUDA_TRY(cudaEventCreateWithFlags(&L.evFork[l], cudaEventDisableTiming));
+    if (!L.evJoin[l]) ORBX_CUDA_TRY(cudaEventCreateWithFlags(&L.evJoin[l], cudaEventDisableTiming));
+  }
+  return ORBX_OK;
+}
+
+// The extraction pipeline on `count` frames whose level 0 is already on the device, on stream `s`.
+int run_pipeline(orbx_extractor* h, Lane& L, const uint8_t* dL0, int l0Pitch, long long l0FrameStride, int count,
+                 orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dN, cudaStream_t s) {
+  const FrameSetGeom& g = L.geom;
+  const int nl = g.nlevels;
+  PipelineArgs a;
+  for (int l = 0; l < kMaxLevels; l++) { a.pyr.lvl[l] = nullptr; a.pyr.frameStride[l] = 0; a.pyr.pitch[l] = 0; }
+  a.pyr.lvl[0] = dL0; a.pyr.frameStride[0] = l0FrameStride; a.pyr.pitch[0] = l0Pitch;
+  uint8_t* arena = static_cast<uint8_t*>(L.pyrArena.p);
+  for (int l = 1; l < nl; l++) {
+    a.pyr.lvl[l] = arena + g.lv[l].planeOff;
+    a.pyr.frameStride[l] = g.lv[l].planeBytes;
+    a.pyr.pitch[l] = g.lv[l].pitch;
+  }
+  a.count = count; a.cap = cap; a.dKps = dKps; a.dDesc = dDesc; a.dN = dN;
+
+  int rc;
+  cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &capturing) != cudaSuccess) { cudaGetLastError(); capturing = cudaStreamCaptureStatusNone; }
+  if (h->profiling || count > fork_frames() || nl < 2 || capturing != cudaStreamCaptureStatusNone) {
+    // (a caller that captures this call into a graph of its own gets the single-stream form)
+    if ((rc = enqueue_linear(h, L, a, s))) return rc;
+  } else {
+    if ((rc = ensure_fork_resources(L, nl))) return rc;
+    // everything a captured launch set has baked in
+    Lane::GraphKey key = {};
+    const void* ptrs[12] = {dL0, dKps, dDesc, dN, L.pyrArena.p, L.blurArena.p, L.candArena.p, L.nodeArena.p, L.keptArena.p,
+                            L.counts.p, L.dGeom.p, h->tapArena.p};
+    for (int i = 0; i < 12; i++) key.p[i] = ptrs[i];
+    key.stride = l0FrameStride;
+    const int vals[8] = {l0Pitch, count, cap, L.w, L.h, L.batchCap, h->tapW, h->tapH};
+    for (int i = 0; i < 8; i++) key.v[i] = vals[i];
+    const bool same = L.graphKeySet && std::memcmp(&key, &L.graphKey, sizeof(key)) == 0;
+    if (same && L.graphExec) {
+      ORBX_CUDA_TRY(cudaGraphLaunch(L.graphExec, s));
+      h->launches += L.graphKernels;
+    } else if (same) {
+      // second call in a row with the same arguments (the drop-in extractor: same arena slot, same result arrays):
+      // capture the set once, replay it from now on
+      cudaGraph_t graph = nullptr;
+      ORBX_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      int kernels = 0;
+      rc = enqueue_forked(h, L, a, s, &kernels);
+      const cudaError_t ce = cudaStreamEndCapture(s, &graph);
+      if (rc || ce != cudaSuccess || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        if (!rc) { set_error("graph capture of the extraction pipeline failed: %s", cudaGetErrorString(ce)); rc = ORBX_ERR_CUDA; }
+        return rc;
+      }
+      const cudaError_t ie = cudaGraphInstantiate(&L.graphExec, graph, 0);
+      cudaGraphDestroy(graph);
+      if (ie != cudaSuccess) { L.graphExec = nullptr; set_error("cudaGraphInstantiate failed: %s", cudaGetErrorString(ie)); return ORBX_ERR_CUDA; }
+      L.graphKernels = kernels;
+      ORBX_CUDA_TRY(cudaGraphLaunch(L.graphExec, s));
+      h->launches += kernels;
+    } else {
+      if (L.graphExec) { cudaGraphExecDestroy(L.graphExec); L.graphExec = nullptr; }
+      L.graphKey = key;
+      L.graphKeySet = true;
+      int kernels = 0;
+      if ((rc = enqueue_forked(h, L, a, s, &kernels))) return rc;
+      h->launches += kernels;
+    }
+  }
   if (&L == &h->lane[0]) {
     h->lastCount = count;
     h->lastLevel0 = dL0; h->lastL0FrameStride = l0FrameStride; h->lastL0Pitch = l0Pitch;
@@ -423,25 +553,51 @@ int submit_chunk(orbx_extractor* h, Lane& L, const uint8_t* const* imgs, int cou
   orbx_keypoint* dK = static_cast<orbx_keypoint*>(L.outKps.p);
   uint8_t* dD = static_cast<uint8_t*>(L.outDesc.p);
   int* dN = static_cast<int*>(L.outN.p);
-  int rc = run_pipeline(h, L, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, dK, dD, rows, dN, s);
-  if (rc) return rc;
-  g_trace.mark(2, s);
   HostStage st = stage_of(L);
-  const int* dOverflow = static_cast<const int*>(L.counts.p) + 2 * L.batchCap * g.nlevels;
-  // streaming submissions hand in pinned destinations of their own: the lane's staging may be rewritten by the next
-  // chunk on this lane before anybody has looked at it
-  ORBX_CUDA_TRY(cudaMemcpyAsync(nOut ? nOut : st.n, dN, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
-  ORBX_CUDA_TRY(cudaMemcpyAsync(overflowOut ? overflowOut : st.overflow, dOverflow, sizeof(int), cudaMemcpyDeviceToHost, s));
-  if (out.direct) {
-    // one "row" per frame: the first min(rows, cap) keypoints; entries past n[f] are unspecified
-    const size_t take = (size_t)std::min(rows, out.cap);
-    ORBX_CUDA_TRY(cudaMemcpy2DAsync(out.kps, (size_t)out.cap * sizeof(orbx_keypoint), dK, (size_t)rows * sizeof(orbx_keypoint),
-                                    take * sizeof(orbx_keypoint), count, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA_TRY(cudaMemcpy2DAsync(out.desc, (size_t)out.cap * 32, dD, (size_t)rows * 32, take * 32, count,
-                                    cudaMemcpyDeviceToHost, s));
-  } else {
-    ORBX_CUDA_TRY(cudaMemcpyAsync(st.kps, dK, (size_t)count * rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA_TRY(cudaMemcpyAsync(st.desc, dD, (size_t)count * rows * 32, cudaMemcpyDeviceToHost, s));
+  // Small chunks (one frame per call is the reference's own pattern): the describe kernel writes keypoints, descriptors
+  // and counts straight into the page-locked destination (the caller's arrays, or the lane's staging for pageable
+  // ones) through their device aliases -- 75 KB of posted writes that overlap the kernel, instead of four dependent
+  // DMA copies behind it (19 us of a 126 us call at 640x480). A truncated frame reports n = -1 (describe_kernel), so
+  // the overflow word needs no copy either.
+  bool zeroCopy = false;
+  if (!stereo && count <= fork_frames()) {
+    void *zk = nullptr, *zd = nullptr, *zn = nullptr;
+    orbx_keypoint* hk = out.direct ? out.kps : st.kps;
+    uint8_t* hd = out.direct ? out.desc : st.desc;
+    int* hn = nOut ? nOut : st.n;
+    if (cudaHostGetDevicePointer(&zk, hk, 0) == cudaSuccess && cudaHostGetDevicePointer(&zd, hd, 0) == cudaSuccess &&
+        cudaHostGetDevicePointer(&zn, hn, 0) == cudaSuccess) {
+      zeroCopy = true;
+      *(overflowOut ? overflowOut : st.overflow) = 0;
+      int rc = run_pipeline(h, L, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, static_cast<orbx_keypoint*>(zk),
+                            static_cast<uint8_t*>(zd), out.direct ? out.cap : rows, static_cast<int*>(zn), s);
+      if (rc) return rc;
+      g_trace.mark(2, s);
+    } else {
+      cudaGetLastError();
+    }
+  }
+  int rc = ORBX_OK;
+  if (!zeroCopy) {
+    rc = run_pipeline(h, L, l0, g.lv[0].pitch, g.lv[0].planeBytes, count, dK, dD, rows, dN, s);
+    if (rc) return rc;
+    g_trace.mark(2, s);
+    const int* dOverflow = static_cast<const int*>(L.counts.p) + 2 * L.batchCap * g.nlevels;
+    // streaming submissions hand in pinned destinations of their own: the lane's staging may be rewritten by the next
+    // chunk on this lane before anybody has looked at it
+    ORBX_CUDA_TRY(cudaMemcpyAsync(nOut ? nOut : st.n, dN, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(overflowOut ? overflowOut : st.overflow, dOverflow, sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (out.direct) {
+      // one "row" per frame: the first min(rows, cap) keypoints; entries past n[f] are unspecified
+      const size_t take = (size_t)std::min(rows, out.cap);
+      ORBX_CUDA_TRY(cudaMemcpy2DAsync(out.kps, (size_t)out.cap * sizeof(orbx_keypoint), dK, (size_t)rows * sizeof(orbx_keypoint),
+                                      take * sizeof(orbx_keypoint), count, cudaMemcpyDeviceToHost, s));
+      ORBX_CUDA_TRY(cudaMemcpy2DAsync(out.desc, (size_t)out.cap * 32, dD, (size_t)rows * 32, take * 32, count,
+                                      cudaMemcpyDeviceToHost, s));
+    } else {
+      ORBX_CUDA_TRY(cudaMemcpyAsync(st.kps, dK, (size_t)count * rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
+      ORBX_CUDA_TRY(cudaMemcpyAsync(st.desc, dD, (size_t)count * rows * 32, cudaMemcpyDeviceToHost, s));
+    }
   }
   if (stereo && (rc = run_chunk_stereo(h, L, l0, count, dK, dD, dN, *stereo))) return rc;
   g_trace.mark(3, s);
@@ -493,6 +649,13 @@ void orbx::Lane::release() {
   if (hostStage) cudaFreeHost(hostStage);
   hostStage = nullptr; hostStageBytes = 0;
   for (int i = 0; i < 8; i++) if (ev[i]) { cudaEventDestroy(ev[i]); ev[i] = nullptr; }
+  if (graphExec) { cudaGraphExecDestroy(graphExec); graphExec = nullptr; }
+  graphKeySet = false;
+  for (int l = 0; l < kMaxLevels; l++) {
+    if (aux[l]) { cudaStreamSynchronize(aux[l]); cudaStreamDestroy(aux[l]); aux[l] = nullptr; }
+    if (evFork[l]) { cudaEventDestroy(evFork[l]); evFork[l] = nullptr; }
+    if (evJoin[l]) { cudaEventDestroy(evJoin[l]); evJoin[l] = nullptr; }
+  }
   if (done) { cudaEventDestroy(done); done = nullptr; }
   if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
   w = h = batchCap = 0;
@@ -749,8 +912,10 @@ int orbx_extract_batch_wait(orbx_extractor* h, int32_t ticket) {
       set_error("FAST candidate list overflowed its capacity (corner density above 1 per 8 pixels)");
       return ORBX_ERR_CAPACITY;
     }
-  for (int f = 0; f < t.count; f++)
+  for (int f = 0; f < t.count; f++) {
+    if (t.n[f] < 0) { set_error("FAST candidate list of frame %d overflowed its capacity", f); return ORBX_ERR_CAPACITY; }
     if (t.n[f] > t.cap) { set_error("keypoint capacity %d too small (see n[])", t.cap); return ORBX_ERR_CAPACITY; }
+  }
   return ORBX_OK;
 }
 

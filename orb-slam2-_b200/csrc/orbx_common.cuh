@@ -39,6 +39,10 @@ inline cudaError_t raise_dynamic_smem(const void* kernel, size_t bytes, SmemLimi
 
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// Per host thread: launches of the fork / join form of the pipeline (small batches, captured into a CUDA graph) are
+// plain launches; griddepcontrol.wait returns at once in a grid that was not launched programmatically.
+inline thread_local bool tl_programmatic_launch = true;
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
   cudaLaunchConfig_t cfg = {};
@@ -46,7 +50,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  cfg.attrs = attr; cfg.numAttrs = tl_programmatic_launch ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 #endif
@@ -136,13 +140,14 @@ struct PyramidPtrs {
 };
 
 // returns 0 or a cudaError_t
+// levels [levelBegin, levelEnd) only (levelEnd < 0: all levels)
 int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
-                int nframes, cudaStream_t s);
+                int nframes, cudaStream_t s, int levelBegin = 0, int levelEnd = -1);
 
 // returns 0 or a cudaError_t
 int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const uint32_t* cand,
                   const int* candCount, uint16_t* nodeScratch, uint32_t* kept, int* keptCount,
-                  int nframes, cudaStream_t s);
+                  int nframes, cudaStream_t s, int levelBegin = 0, int levelEnd = -1);
 
 void launch_blur(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint8_t* blurArena, int nframes, cudaStream_t s);
 

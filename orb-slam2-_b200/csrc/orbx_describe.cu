@@ -31,8 +31,8 @@ __constant__ int8_t cPattern[1024] = {
 __constant__ int cUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
 constexpr int kDescWarps = 8;
-constexpr int kDescKpPerWarp = 4;
-constexpr int kDescKpPerCta = kDescWarps * kDescKpPerWarp;
+constexpr int kDescKpPerWarp = 4;      // batches: the CTA prologue (pattern + weights into shared memory) is shared by 32 keypoints
+constexpr int kDescKpPerWarpSmall = 1; // a few frames: four times the CTAs, each warp done after one keypoint (latency)
 constexpr int kPatchR = 19;                      // EDGE_THRESHOLD: reach of the rotated pattern (R/src/ORBextractor.cpp:76)
 constexpr int kPatchRows = 2 * kPatchR + 1;      // 39
 constexpr int kPatchVecs = 6;                    // 8-byte vectors per staged row (39 bytes + up to 7 of misalignment)
@@ -50,6 +50,7 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
   return r;
 }
 
+template <int KPW>
 __global__ void __launch_bounds__(kDescWarps * 32)
 describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restrict__ blurArena,
                 const __grid_constant__ FrameSetGeom g, const uint32_t* __restrict__ kept,
@@ -105,8 +106,8 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
   const float factorPI = 0x1.1df46ap-6f;  // (float)(CV_PI/180.f)
 
 #pragma unroll 1
-  for (int it = 0; it < kDescKpPerWarp; it++) {
-    const int row = blockIdx.x * kDescKpPerCta + it * kDescWarps + warp;  // level-major concatenation
+  for (int it = 0; it < KPW; it++) {
+    const int row = blockIdx.x * (kDescWarps * KPW) + it * kDescWarps + warp;  // level-major concatenation
     if (row >= total || row >= cap) break;
     int level = 0;
     while (level + 1 < nl && row >= sStart[level + 1]) level++;
@@ -192,8 +193,15 @@ void launch_describe(const PyramidPtrs& pyr, const uint8_t* blurArena, const Fra
                      const uint32_t* kept, const int* keptCount, const int* candCount, orbx_keypoint* outKps,
                      uint8_t* outDesc, int cap, int* outN, int nframes, cudaStream_t s) {
   const int maxKp = hGeom.keptPerFrame;
-  dim3 grid((maxKp + kDescKpPerCta - 1) / kDescKpPerCta, nframes);
-  launch_pdl(describe_kernel, grid, dim3(kDescWarps * 32), 0, s, pyr, blurArena, hGeom, kept, keptCount, candCount, outKps, outDesc, cap, outN);
+  if (nframes <= 4) {
+    constexpr int perCta = kDescWarps * kDescKpPerWarpSmall;
+    launch_pdl(describe_kernel<kDescKpPerWarpSmall>, dim3((maxKp + perCta - 1) / perCta, nframes), dim3(kDescWarps * 32), 0, s, pyr,
+               blurArena, hGeom, kept, keptCount, candCount, outKps, outDesc, cap, outN);
+  } else {
+    constexpr int perCta = kDescWarps * kDescKpPerWarp;
+    launch_pdl(describe_kernel<kDescKpPerWarp>, dim3((maxKp + perCta - 1) / perCta, nframes), dim3(kDescWarps * 32), 0, s, pyr,
+               blurArena, hGeom, kept, keptCount, candCount, outKps, outDesc, cap, outN);
+  }
 }
 
 // ---- array versions of the float helpers, for the unit parity tests ----------------------------

@@ -146,12 +146,12 @@ __host__ __device__ inline int fast_cell_words(int wCell, int hCell) {
 __global__ void __launch_bounds__(kFastThreads, ORBX_FAST_MINB)
 fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
                   uint32_t* __restrict__ cand, int* __restrict__ candCount, int* __restrict__ overflow,
-                  int wordsPerWarp) {
+                  int wordsPerWarp, int cellBegin, int cellEnd) {
   pdl_wait();
   extern __shared__ __align__(16) uint32_t smemFast[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int cell = blockIdx.x * kFastWarps + warp;
-  if (cell >= g.totalCells) return;  // warps are independent: no block-wide barrier below
+  const int cell = cellBegin + blockIdx.x * kFastWarps + warp;
+  if (cell >= cellEnd) return;  // warps are independent: no block-wide barrier below
   const int nl = g.nlevels;
   int level = 0;
   while (level + 1 < nl && cell >= g.lv[level + 1].cellBase) level++;
@@ -419,15 +419,20 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
 }
 
 int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
-                int nframes, cudaStream_t s) {
+                int nframes, cudaStream_t s, int levelBegin, int levelEnd) {
+  if (levelEnd < 0) levelEnd = hGeom.nlevels;
   int words = 0;
   for (int l = 0; l < hGeom.nlevels; l++) words = max(words, fast_cell_words(hGeom.lv[l].wCell, hGeom.lv[l].hCell));
   const size_t smem = (size_t)words * 4 * kFastWarps;
   static SmemLimit limit;
   cudaError_t e = raise_dynamic_smem(reinterpret_cast<const void*>(fast_cells_kernel), smem, &limit);
   if (e != cudaSuccess) return (int)e;
-  dim3 grid((hGeom.totalCells + kFastWarps - 1) / kFastWarps, nframes);
-  launch_pdl(fast_cells_kernel, grid, dim3(kFastThreads), smem, s, pyr, hGeom, cand, candCount, overflow, words);
+  // cells of levels [levelBegin, levelEnd): the flat cell ids of a level are contiguous
+  const int cellBegin = hGeom.lv[levelBegin].cellBase;
+  const int cellEnd = levelEnd < hGeom.nlevels ? hGeom.lv[levelEnd].cellBase : hGeom.totalCells;
+  if (cellEnd <= cellBegin) return 0;
+  dim3 grid((cellEnd - cellBegin + kFastWarps - 1) / kFastWarps, nframes);
+  launch_pdl(fast_cells_kernel, grid, dim3(kFastThreads), smem, s, pyr, hGeom, cand, candCount, overflow, words, cellBegin, cellEnd);
   return 0;
 }
 

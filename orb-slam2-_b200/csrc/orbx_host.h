@@ -56,6 +56,19 @@ struct Lane {
   DeviceBuf stereoBuf;                // stereo sequences: uRight | depth | sad | nKept | row table of the chunk's pairs
   void* hostStage = nullptr;          // pinned: kps | desc | n | overflow flag
   size_t hostStageBytes = 0;
+  // Small batches (one frame per call is what the reference's Frame constructor does): the levels are independent after
+  // the pyramid, so FAST + octree of level l run on aux[l] as soon as level l exists, next to the rest of the resize
+  // chain and the blur; the whole fork / join set is captured into a CUDA graph once its arguments repeat.
+  cudaStream_t aux[kMaxLevels] = {};
+  cudaEvent_t evFork[kMaxLevels] = {}, evJoin[kMaxLevels] = {};
+  cudaGraphExec_t graphExec = nullptr;
+  struct GraphKey {
+    const void* p[12];
+    long long stride;
+    int v[8];
+  } graphKey = {};
+  bool graphKeySet = false;
+  int graphKernels = 0;
   void release();
 };
 

@@ -18,7 +18,10 @@
 namespace orbx {
 
 constexpr int kBfThreads = 256;
-constexpr int kBfQPT = 4;                       // queries per thread
+#ifndef ORBX_BF_QPT
+#define ORBX_BF_QPT 4
+#endif
+constexpr int kBfQPT = ORBX_BF_QPT;             // queries per thread
 constexpr int kBfQueriesPerCta = kBfThreads * kBfQPT;
 constexpr int kBfTileRows = 512;                // database rows staged per step (16 KB)
 constexpr unsigned kKeyNone = 0xFFFFFFFFu;

@@ -301,10 +301,10 @@ size_t octree_smem_bytes(int cap) {
 __global__ void __launch_bounds__(kOctThreads)
 octree_kernel(const FrameSetGeom* __restrict__ g, const uint32_t* __restrict__ cand,
               const int* __restrict__ candCount, uint16_t* __restrict__ nodeScratch,
-              uint32_t* __restrict__ kept, int* __restrict__ keptCount, int cap) {
+              uint32_t* __restrict__ kept, int* __restrict__ keptCount, int cap, int levelBase) {
   pdl_wait();
   extern __shared__ __align__(16) unsigned char smemRaw[];
-  const int level = blockIdx.x, f = blockIdx.y, nl = g->nlevels;
+  const int level = levelBase + blockIdx.x, f = blockIdx.y, nl = g->nlevels;
   const LevelGeom& L = g->lv[level];
   OctTask t;
   const long long coff = L.candOff + (long long)f * L.candCap;
@@ -329,15 +329,16 @@ octree_single_kernel(OctTask t) {
 
 int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const uint32_t* cand,
                   const int* candCount, uint16_t* nodeScratch, uint32_t* kept, int* keptCount,
-                  int nframes, cudaStream_t s) {
+                  int nframes, cudaStream_t s, int levelBegin, int levelEnd) {
+  if (levelEnd < 0) levelEnd = hGeom.nlevels;
   int cap = 0;
   for (int l = 0; l < hGeom.nlevels; l++) cap = max(cap, hGeom.lv[l].keptCap);
   const size_t smem = octree_smem_bytes(cap);
   static SmemLimit limit;
   cudaError_t e = raise_dynamic_smem(reinterpret_cast<const void*>(octree_kernel), smem, &limit);
   if (e != cudaSuccess) return (int)e;
-  dim3 grid(hGeom.nlevels, nframes);
-  launch_pdl(octree_kernel, grid, dim3(nframes >= kOctBatchFrames ? kOctThreadsBatch : kOctThreads), smem, s, dGeom, cand, candCount, nodeScratch, kept, keptCount, cap);
+  dim3 grid(levelEnd - levelBegin, nframes);
+  launch_pdl(octree_kernel, grid, dim3(nframes >= kOctBatchFrames ? kOctThreadsBatch : kOctThreads), smem, s, dGeom, cand, candCount, nodeScratch, kept, keptCount, cap, levelBegin);
   return 0;
 }
 
