@@ -97,7 +97,7 @@ def build_host_mirror(force=False):
     out = host / "libmirror_test.so"
     srcs = [host / "ORBextractor.cc", host / "orbx_search.cc", host / "orbx_bow.cc", host / "mirror_capi.cc"]
     shim = HERE.parent / "oracle" / "ref_shim"
-    deps = srcs + [host / "ORBextractor.h", host / "orbx_search.h", host / "orbx_bow.h", HERE.parent / "include" / "orbx.h", shim / "opencv2" / "core" / "core.hpp", LIB]
+    deps = srcs + [host / "ORBextractor.h", host / "orbx_search.h", host / "orbx_bow.h", host / "orbx_shard.h", HERE.parent / "include" / "orbx.h", shim / "opencv2" / "core" / "core.hpp", LIB]
     if not (force or _stale(out, deps)):
         return out
     cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++11", "-fPIC", "-shared", "-Wall", "-Wno-stringop-overflow", "-Wno-array-bounds",

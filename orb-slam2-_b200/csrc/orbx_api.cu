@@ -189,7 +189,8 @@ int ensure_lane(orbx_extractor* h, Lane& L, int w, int hh, int cap) {
   ORBX_CUDA_TRY(cudaStreamSynchronize(L.stream));
   const int batchCap = (w == L.w && hh == L.h) ? std::max(cap, L.batchCap) : cap;
   FrameSetGeom g;
-  if ((rc = build_geometry(h->params, h->tables, w, hh, batchCap, &g))) return rc;
+  std::vector<FastCellDesc> cellTable;
+  if ((rc = build_geometry(h->params, h->tables, w, hh, batchCap, &g, &cellTable))) return rc;
   const int nl = g.nlevels;
   long long candTotal = 0, keptTotal = 0;
   for (int l = 0; l < nl; l++) {
@@ -203,8 +204,11 @@ int ensure_lane(orbx_extractor* h, Lane& L, int w, int hh, int cap) {
   if ((rc = L.keptArena.ensure((size_t)keptTotal * 4))) return rc;
   if ((rc = L.counts.ensure((size_t)(2 * batchCap * nl + 4) * sizeof(int)))) return rc;
   if ((rc = L.dGeom.ensure(sizeof(FrameSetGeom)))) return rc;
+  if ((rc = L.dCells.ensure(std::max<size_t>(cellTable.size(), 1) * sizeof(FastCellDesc)))) return rc;
   ORBX_CUDA_TRY(cudaMemcpyAsync(L.dGeom.p, &g, sizeof(g), cudaMemcpyHostToDevice, L.stream));
-  ORBX_CUDA_TRY(cudaStreamSynchronize(L.stream));  // `g` is a stack temporary
+  if (!cellTable.empty())
+    ORBX_CUDA_TRY(cudaMemcpyAsync(L.dCells.p, cellTable.data(), cellTable.size() * sizeof(FastCellDesc), cudaMemcpyHostToDevice, L.stream));
+  ORBX_CUDA_TRY(cudaStreamSynchronize(L.stream));  // `g` and the table are stack temporaries
   L.geom = g;
   L.w = w; L.h = hh; L.batchCap = batchCap;
   if (&L == &h->lane[0]) h->haveResult = false;
@@ -266,7 +270,7 @@ int enqueue_linear(orbx_extractor* h, Lane& L, const PipelineArgs& a, cudaStream
     h->launches++;
   }
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[1], s));
-  int fe = launch_fast(a.pyr, g, static_cast<uint32_t*>(L.candArena.p), candCount, overflow, count, s);
+  int fe = launch_fast(a.pyr, g, static_cast<const FastCellDesc*>(L.dCells.p), static_cast<uint32_t*>(L.candArena.p), candCount, overflow, count, s);
   if (fe) { set_error("FAST kernel configuration failed: %s", cudaGetErrorString((cudaError_t)fe)); return ORBX_ERR_CUDA; }
   h->launches++;
   if (prof) ORBX_CUDA_TRY(cudaEventRecord(L.ev[2], s));
@@ -313,7 +317,7 @@ int enqueue_forked(orbx_extractor* h, Lane& L, const PipelineArgs& a, cudaStream
     }
     ORBX_CUDA_TRY(cudaEventRecord(L.evFork[l], s));
     ORBX_CUDA_TRY(cudaStreamWaitEvent(L.aux[l], L.evFork[l], 0));
-    int fe = launch_fast(a.pyr, g, static_cast<uint32_t*>(L.candArena.p), candCount, overflow, count, L.aux[l], l, l + 1);
+    int fe = launch_fast(a.pyr, g, static_cast<const FastCellDesc*>(L.dCells.p), static_cast<uint32_t*>(L.candArena.p), candCount, overflow, count, L.aux[l], l, l + 1);
     if (fe) { set_error("FAST kernel configuration failed: %s", cudaGetErrorString((cudaError_t)fe)); return ORBX_ERR_CUDA; }
     int oe = launch_octree(dG, g, static_cast<const uint32_t*>(L.candArena.p), candCount, static_cast<uint16_t*>(L.nodeArena.p),
                            static_cast<uint32_t*>(L.keptArena.p), keptCount, count, L.aux[l], l, l + 1);
@@ -368,7 +372,7 @@ int run_pipeline(orbx_extractor* h, Lane& L, const uint8_t* dL0, int l0Pitch, lo
     // everything a captured launch set has baked in
     Lane::GraphKey key = {};
     const void* ptrs[12] = {dL0, dKps, dDesc, dN, L.pyrArena.p, L.blurArena.p, L.candArena.p, L.nodeArena.p, L.keptArena.p,
-                            L.counts.p, L.dGeom.p, h->tapArena.p};
+                            L.counts.p, L.dCells.p, h->tapArena.p};
     for (int i = 0; i < 12; i++) key.p[i] = ptrs[i];
     key.stride = l0FrameStride;
     const int vals[8] = {l0Pitch, count, cap, L.w, L.h, L.batchCap, h->tapW, h->tapH};
@@ -644,7 +648,7 @@ int collect_chunk(orbx_extractor* h, Lane& L, int count, const HostOut& out, int
 
 void orbx::Lane::release() {
   if (stream) cudaStreamSynchronize(stream);
-  dGeom.release(); pyrArena.release(); blurArena.release(); candArena.release(); nodeArena.release();
+  dGeom.release(); dCells.release(); pyrArena.release(); blurArena.release(); candArena.release(); nodeArena.release();
   keptArena.release(); counts.release(); outKps.release(); outDesc.release(); outN.release(); stereoBuf.release();
   if (hostStage) cudaFreeHost(hostStage);
   hostStage = nullptr; hostStageBytes = 0;

@@ -75,7 +75,7 @@ struct LevelGeom {
   float hX;            // root width (:580)
   int candCap;         // capacity of the candidate list of one (frame, level)
   int keptCap;         // capacity of the kept list of one (frame, level)
-  int cellBase;        // first flat cell id of this level in the FAST grid
+  int cellBase;        // first entry of this level in the FAST cell table (cells the reference skips are not listed)
   int tileBase;        // first flat tile id of this level in the blur grid
   int tilesX, tilesY;
   float scale;         // mvScaleFactor[level]
@@ -86,10 +86,20 @@ struct LevelGeom {
   long long keptOff;   // element offset in the kept arena
 };
 
+// One FAST cell the reference scans (R/src/ORBextractor.cpp:851-870), worked out once per frame shape on the host
+// instead of ~150 integer instructions per cell and launch in the kernel. Tile column 0 of the cell's patch is image
+// column gx0 (a multiple of 4); the first scanned pixel sits at tile column a (4..7), the last at b - 1.
+struct alignas(16) FastCellDesc {
+  uint8_t level, ch, a, b;   // ch = patch rows (scan rows = ch - 6)
+  uint16_t iniY, gx0;        // first patch row / tile column 0, in level coordinates
+  int16_t outX0, outY0;      // candidate x = outX0 + 4 * (q + 1) + i, y = outY0 + row (relative to minBorder)
+  uint32_t pad;
+};
+
 struct FrameSetGeom {
   int nlevels;
   int iniTh, minTh;
-  int totalCells;      // FAST grid x-dimension
+  int totalCells;      // entries of the FAST cell table
   int totalTiles;      // blur grid x-dimension
   long long pyrFrameStride;   // bytes between the same level of consecutive frames is planeBytes; arenas are [level][frame]
   int candPerFrame;    // sum of candCap
@@ -141,8 +151,8 @@ struct PyramidPtrs {
 
 // returns 0 or a cudaError_t
 // levels [levelBegin, levelEnd) only (levelEnd < 0: all levels)
-int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
-                int nframes, cudaStream_t s, int levelBegin = 0, int levelEnd = -1);
+int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, const FastCellDesc* cells, uint32_t* cand, int* candCount,
+                int* overflow, int nframes, cudaStream_t s, int levelBegin = 0, int levelEnd = -1);
 
 // returns 0 or a cudaError_t
 int launch_octree(const FrameSetGeom* dGeom, const FrameSetGeom& hGeom, const uint32_t* cand,

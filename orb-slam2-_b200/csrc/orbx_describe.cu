@@ -118,33 +118,40 @@ describe_kernel(const __grid_constant__ PyramidPtrs pyr, const uint8_t* __restri
     // stage rows y-19 .. y+19, bytes from the 8-byte boundary at or below x-19 (planes are 16-byte pitched)
     const int bp = L.pitch;
     const int x0 = (x - kPatchR) & ~7, xo = (x - kPatchR) - x0;
-    const uint8_t* brow = blurArena + L.planeOff + (long long)f * L.planeBytes + (long long)(y - kPatchR) * bp + x0;
     const int prow = lane / kPatchVecs, pvec = lane - prow * kPatchVecs;
     const bool pload = lane < kPatchRowsPerPass * kPatchVecs && pvec * 8 < xo + kPatchRows;
+    // this lane's first vector; every pass moves on by kPatchRowsPerPass rows (one 64-bit add instead of a fresh
+    // row * pitch product per pass)
+    const uint8_t* bsrc = blurArena + L.planeOff + (long long)f * L.planeBytes + (long long)(y - kPatchR + prow) * bp + x0 + pvec * 8;
+    const long long bstep = (long long)kPatchRowsPerPass * bp;
+    uint2* bdst = &sPatch[warp][prow * kPatchVecs + pvec];
     __syncwarp();  // the previous keypoint's gathers are done
 #pragma unroll
     for (int i = 0; i < kPatchPasses; i++) {
-      const int r = i * kPatchRowsPerPass + prow;
-      if (pload && r < kPatchRows)
-        sPatch[warp][r * kPatchVecs + pvec] = *reinterpret_cast<const uint2*>(brow + (long long)r * bp + pvec * 8);
+      if (pload && i * kPatchRowsPerPass + prow < kPatchRows)
+        bdst[i * kPatchRowsPerPass * kPatchVecs] = *reinterpret_cast<const uint2*>(bsrc);
+      bsrc += bstep;
     }
 
     // ---- IC_Angle ----
     const int pitch = pyr.pitch[level];
-    const uint8_t* center = pyr.lvl[level] + (long long)f * pyr.frameStride[level] + (long long)y * pitch + x;
     const int chunk = lane & 7, sub = lane >> 3;
+    // rows sub, sub+4, ... of the 31-row disc: one pointer, advanced by four rows per step
+    const uint8_t* ip = pyr.lvl[level] + (long long)f * pyr.frameStride[level] + (long long)(y + sub - kHalfPatch) * pitch + x +
+                        (4 * chunk - 16);
+    const long long istep = 4LL * pitch;
     int m10 = 0, m01 = 0;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
       const int r = 4 * i + sub;  // row index 0..31, v = r - 15
       if (r < 31) {
-        const uint8_t* p = center + (long long)(r - kHalfPatch) * pitch + (4 * chunk - 16);
-        const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(ip);
         const uint32_t* ap = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
         const uint32_t px = __funnelshift_r(ap[0], ap[1], (uint32_t)(addr & 3) * 8);
         m10 = dp4a_us(px, sWU[r * 8 + chunk], m10);
         m01 += (r - kHalfPatch) * (int)__dp4a(px, sWO[r * 8 + chunk], 0u);
       }
+      ip += istep;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

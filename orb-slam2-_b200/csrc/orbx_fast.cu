@@ -145,40 +145,24 @@ __host__ __device__ inline int fast_cell_words(int wCell, int hCell) {
 
 __global__ void __launch_bounds__(kFastThreads, ORBX_FAST_MINB)
 fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant__ FrameSetGeom g,
-                  uint32_t* __restrict__ cand, int* __restrict__ candCount, int* __restrict__ overflow,
-                  int wordsPerWarp, int cellBegin, int cellEnd) {
-  pdl_wait();
+                  const FastCellDesc* __restrict__ cells, uint32_t* __restrict__ cand, int* __restrict__ candCount,
+                  int* __restrict__ overflow, int wordsPerWarp, int cellBegin, int cellEnd) {
   extern __shared__ __align__(16) uint32_t smemFast[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = cellBegin + blockIdx.x * kFastWarps + warp;
   if (cell >= cellEnd) return;  // warps are independent: no block-wide barrier below
+  // the cell's rectangle comes from the table of the frame shape (host-built, the same for every frame)
+  const uint4 cd = __ldg(reinterpret_cast<const uint4*>(cells) + cell);
   const int nl = g.nlevels;
-  int level = 0;
-  while (level + 1 < nl && cell >= g.lv[level + 1].cellBase) level++;
+  const int level = cd.x & 0xff, ch = (cd.x >> 8) & 0xff, a = (cd.x >> 16) & 0xff, b = cd.x >> 24;
+  const int iniY = cd.y & 0xffff, gx0 = cd.y >> 16;
+  const int outX0 = (int)(short)(cd.z & 0xffff), outY0 = (int)(short)(cd.z >> 16);
   const LevelGeom& L = g.lv[level];
-  const int cidx = cell - L.cellBase;
-  const int ci = (L.nCols <= 64 && cidx < 1024) ? div_small(cidx, L.nCols) : cidx / L.nCols;
-  const int cj = cidx - ci * L.nCols;
   const int f = blockIdx.y;
-
-  // cell rectangle (R/src/ORBextractor.cpp:851-870)
-  const int iniY = kMinBorder + ci * L.hCell;
-  const int iniX = kMinBorder + cj * L.wCell;
-  if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6) return;
-  const int maxY = min(iniY + L.hCell + 6, L.maxBY);
-  const int maxX = min(iniX + L.wCell + 6, L.maxBX);
-  const int ch = maxY - iniY;
-  const int sw = maxX - iniX - 6, sh = ch - 6;  // cv::FAST scans [3,cw-3)x[3,ch-3)
-  if (sw <= 0 || sh <= 0) return;
-
-  // Tile column 0 is global column gx0 (a multiple of 4, <= iniX-1): the first scanned pixel sits at
-  // tile column a in 4..7, so every 4-pixel group starts on a word boundary and its ring (+-3) stays
-  // inside the 12-byte window of words q, q+1, q+2.
-  const int gx0 = ((iniX + 3) & ~3) - 4;
-  const int a = iniX + 3 - gx0;
-  const int b = a + sw;
+  const int sh = ch - 6;        // cv::FAST scans [3,cw-3)x[3,ch-3)
   const int nG = (b - 1) >> 2;  // groups q = 0..nG-1 cover tile words 1..nG
   const int nW = nG + 2;        // staged words per row
+  pdl_wait();
 
   uint32_t* tile = smemFast + warp * wordsPerWarp;  // ch rows x 2nW words: one 16-bit lane per pixel
   uint32_t* smap = tile + ch * 2 * nW;              // (sh+2) rows x nW words, rows 0 and sh+1 stay zero
@@ -411,15 +395,15 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
         // cv::FAST's cornerScore = sc + minTh - 1; coordinates relative to minBorder:
         // cell-local (x+3, y+3) + (j*wCell, i*hCell)  (:889-890)
         if (slot < L.candCap)
-          cand[slotBase + slot] = pack_cand(4 * (q + 1) + i - a + 3 + cj * L.wCell, y + 3 + ci * L.hCell, sc + minTh - 1);
+          cand[slotBase + slot] = pack_cand(outX0 + 4 * (q + 1) + i, outY0 + y, sc + minTh - 1);
         slot++;
       }
     }
   }
 }
 
-int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* cand, int* candCount, int* overflow,
-                int nframes, cudaStream_t s, int levelBegin, int levelEnd) {
+int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, const FastCellDesc* cells, uint32_t* cand, int* candCount,
+                int* overflow, int nframes, cudaStream_t s, int levelBegin, int levelEnd) {
   if (levelEnd < 0) levelEnd = hGeom.nlevels;
   int words = 0;
   for (int l = 0; l < hGeom.nlevels; l++) words = max(words, fast_cell_words(hGeom.lv[l].wCell, hGeom.lv[l].hCell));
@@ -427,12 +411,13 @@ int launch_fast(const PyramidPtrs& pyr, const FrameSetGeom& hGeom, uint32_t* can
   static SmemLimit limit;
   cudaError_t e = raise_dynamic_smem(reinterpret_cast<const void*>(fast_cells_kernel), smem, &limit);
   if (e != cudaSuccess) return (int)e;
-  // cells of levels [levelBegin, levelEnd): the flat cell ids of a level are contiguous
+  // cells of levels [levelBegin, levelEnd): the table entries of a level are contiguous
   const int cellBegin = hGeom.lv[levelBegin].cellBase;
   const int cellEnd = levelEnd < hGeom.nlevels ? hGeom.lv[levelEnd].cellBase : hGeom.totalCells;
   if (cellEnd <= cellBegin) return 0;
   dim3 grid((cellEnd - cellBegin + kFastWarps - 1) / kFastWarps, nframes);
-  launch_pdl(fast_cells_kernel, grid, dim3(kFastThreads), smem, s, pyr, hGeom, cand, candCount, overflow, words, cellBegin, cellEnd);
+  launch_pdl(fast_cells_kernel, grid, dim3(kFastThreads), smem, s, pyr, hGeom, cells, cand, candCount, overflow, words, cellBegin,
+             cellEnd);
   return 0;
 }
 

@@ -123,8 +123,10 @@ bool build_resize_groups(const std::vector<ResizeTap>& tx, const std::vector<Res
   return true;
 }
 
-int build_geometry(const orbx_params& p, const CtorTables& t, int w, int h, int batchCap, FrameSetGeom* g) {
+int build_geometry(const orbx_params& p, const CtorTables& t, int w, int h, int batchCap, FrameSetGeom* g,
+                   std::vector<FastCellDesc>* cellTable) {
   *g = FrameSetGeom();
+  if (cellTable) cellTable->clear();
   g->nlevels = p.nlevels;
   g->iniTh = std::min(std::max(p.ini_th_fast, 0), 255);  // cv::FAST clamps its threshold
   g->minTh = std::min(std::max(p.min_th_fast, 0), 255);
@@ -171,7 +173,25 @@ int build_geometry(const orbx_params& p, const CtorTables& t, int w, int h, int 
     }
     L.candCap = (int)(((long long)L.w * L.h) / 8) + 256;
     L.cellBase = cells;
-    cells += L.nCols * L.nRows;
+    for (int ci = 0; ci < L.nRows; ci++) {
+      for (int cj = 0; cj < L.nCols; cj++) {
+        // the cell rectangle and the reference's skip rules (:851-870); cv::FAST scans [3,cw-3) x [3,ch-3) of it
+        const int iniY = kMinBorder + ci * L.hCell, iniX = kMinBorder + cj * L.wCell;
+        if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6) continue;
+        const int maxY = std::min(iniY + L.hCell + 6, L.maxBY), maxX = std::min(iniX + L.wCell + 6, L.maxBX);
+        const int ch = maxY - iniY, sw = maxX - iniX - 6;
+        if (sw <= 0 || ch - 6 <= 0) continue;
+        cells++;
+        if (!cellTable) continue;
+        FastCellDesc d = {};
+        const int gx0 = ((iniX + 3) & ~3) - 4, a = iniX + 3 - gx0;
+        d.level = (uint8_t)l; d.ch = (uint8_t)ch; d.a = (uint8_t)a; d.b = (uint8_t)(a + sw);
+        d.iniY = (uint16_t)iniY; d.gx0 = (uint16_t)gx0;
+        d.outX0 = (int16_t)(cj * L.wCell + 3 - a);
+        d.outY0 = (int16_t)(ci * L.hCell + 3);
+        cellTable->push_back(d);
+      }
+    }
     blur_tiles_for(L.w, L.h, &L.tilesX, &L.tilesY);
     L.tileBase = tiles;
     tiles += L.tilesX * L.tilesY;

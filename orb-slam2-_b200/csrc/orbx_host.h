@@ -26,7 +26,9 @@ const char* last_error();
 
 // Fill the per-level geometry for a (w,h) frame and `batchCap` frames per arena.
 // Returns 0, or ORBX_ERR_ARG with set_error() when a level is too small for the reference's grid.
-int build_geometry(const orbx_params& p, const CtorTables& t, int w, int h, int batchCap, FrameSetGeom* g);
+// cellTable (optional): the FAST cell table of the shape, g->totalCells entries.
+int build_geometry(const orbx_params& p, const CtorTables& t, int w, int h, int batchCap, FrameSetGeom* g,
+                   std::vector<FastCellDesc>* cellTable = nullptr);
 
 struct DeviceBuf {
   void* p = nullptr;
@@ -51,6 +53,7 @@ struct Lane {
   int w = 0, h = 0, batchCap = 0;     // shape the arenas are laid out for
   FrameSetGeom geom;                  // host copy (plane/candidate offsets depend on batchCap)
   DeviceBuf dGeom;                    // FrameSetGeom on device (octree kernel)
+  DeviceBuf dCells;                   // FastCellDesc table of the shape (fast_cells_kernel)
   DeviceBuf pyrArena, blurArena, candArena, nodeArena, keptArena, counts;
   DeviceBuf outKps, outDesc, outN;    // device staging for the host-buffer entry points
   DeviceBuf stereoBuf;                // stereo sequences: uRight | depth | sad | nKept | row table of the chunk's pairs

@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "ORBextractor.h"
+#include "orbx_shard.h"
 
 struct mirror_keypoint { float x, y, size, angle, response; int32_t octave, class_id; };
 
@@ -170,3 +171,36 @@ int mirror_voc_transform(void* h, const unsigned char* desc, int n, int levelsup
 }
 
 }  // extern "C"
+
+// orbx_host::ShardGroup (host/orbx_shard.h) over `ndev` devices: sharded top-2 of nq queries against ndb rows, and a
+// sequence of `count` frames extracted by the group. Outputs are the caller's; returns 0, or -1 with the message in
+// err (the wrapper throws).
+extern "C" int mirror_shard_run(int ndev, const uint8_t* db, long long ndb, const uint8_t* q, int nq, float ratio, int th,
+                                int32_t* idx, int32_t* d1, int32_t* d2, uint8_t* accepted, const uint8_t* frames, int count,
+                                int w, int hgt, int nfeatures, mirror_keypoint* kps, uint8_t* desc, int cap, int32_t* n,
+                                char* err, int errCap) {
+  try {
+    std::vector<int> devices;
+    for (int i = 0; i < ndev; i++) devices.push_back(i);
+    orbx_host::ShardGroup group(devices);
+    if (group.Ranks() != ndev || group.LocalRanks() != ndev) throw std::runtime_error("group size");
+    group.SetDatabase(db, ndb);
+    const orbx_host::ShardGroup::Matches m = group.MatchBf2(q, nq, ratio, th);
+    std::memcpy(idx, &m.idx[0], (size_t)nq * 4);
+    std::memcpy(d1, &m.d1[0], (size_t)nq * 4);
+    std::memcpy(d2, &m.d2[0], (size_t)nq * 4);
+    std::memcpy(accepted, &m.accepted[0], (size_t)nq);
+    orbx_params p;
+    p.nfeatures = nfeatures; p.scale_factor = 1.2f; p.nlevels = 8; p.ini_th_fast = 20; p.min_th_fast = 7; p.device = 0;
+    p.max_width = w; p.max_height = hgt; p.max_batch = 8;
+    std::vector<const uint8_t*> imgs(count);
+    for (int f = 0; f < count; f++) imgs[f] = frames + (size_t)f * w * hgt;
+    group.ExtractSequence(p, &imgs[0], count, w, hgt, (size_t)w, reinterpret_cast<orbx_keypoint*>(kps), desc, cap, n);
+    return 0;
+  } catch (const std::exception& e) {
+    std::strncpy(err, e.what(), (size_t)errCap - 1);
+    err[errCap - 1] = 0;
+    return -1;
+  }
+}
+

@@ -74,3 +74,37 @@ def test_cpp_mirror_strided_roi_input(pkg, oracle, mirror):
         assert np.array_equal(gk.view(np.uint8), ok.view(np.uint8)) and np.array_equal(gd, od)
     finally:
         mirror.mirror_destroy(h)
+
+
+@pytest.mark.parametrize("ndev", [1, 2])
+def test_cpp_shard_group_wrapper(pkg, mirror, ndev):
+    """orbx_host::ShardGroup (host/orbx_shard.h, the C++ face of orbx_shard_*): sharded top-2 and a sequence extracted
+    by the group equal the single-GPU entry points."""
+    if pkg.device_count() < ndev:
+        pytest.skip(f"needs {ndev} GPUs")
+    ndb, nq = 60_000, 300
+    db = pkg.synth.descriptors(ndb, 51)
+    q = pkg.synth.planted_queries(db, nq, 52)
+    idx, d1, d2 = (np.empty(nq, np.int32) for _ in range(3))
+    acc = np.empty(nq, np.uint8)
+    w, h, nf, count = 320, 240, 300, 11
+    frames = np.stack([pkg.synth.frame(w, h, 500 + i) for i in range(count)])
+    cap = nf + 64
+    kps = pkg.pinned_empty((count, cap), pkg.KP_DTYPE)
+    desc = pkg.pinned_empty((count, cap, 32), np.uint8)
+    n = pkg.pinned_empty(count, np.int32)
+    err = C.create_string_buffer(512)
+    fn = mirror.mirror_shard_run
+    fn.argtypes = [C.c_int, C.c_void_p, C.c_longlong, C.c_void_p, C.c_int, C.c_float, C.c_int] + [C.c_void_p] * 5 + \
+                  [C.c_int] * 4 + [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_char_p, C.c_int]
+    rc = fn(ndev, db.ctypes.data, ndb, q.ctypes.data, nq, 0.6, 50, idx.ctypes.data, d1.ctypes.data, d2.ctypes.data,
+            acc.ctypes.data, frames.ctypes.data, count, w, h, nf, kps.ctypes.data, desc.ctypes.data, cap, n.ctypes.data,
+            err, 512)
+    assert rc == 0, err.value
+    exp = pkg.ORBmatcher(0.6).match_bf2(q, db)
+    for a, b in zip((idx, d1, d2, acc), exp):
+        assert np.array_equal(a, b)
+    one = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    for f in range(count):
+        k1, dd = one(frames[f])
+        assert n[f] == len(k1) and np.array_equal(kps[f, :n[f]].view(np.uint8), k1.view(np.uint8)) and np.array_equal(desc[f, :n[f]], dd)

@@ -22,6 +22,10 @@ timeout 900 ncu --set full --clock-control none --import-source on \
   -o $OUT/pipeline_full -f $CMD > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ncu -i $OUT/pipeline_full.ncu-rep --page raw --csv > $OUT/pipeline_full_raw.csv 2>/dev/null
+rm -f $OUT/pipeline_full.ncu-rep   # gpurun only brings back 64 MiB
+# per-line instruction / stall counters (source page) of the two heaviest kernels, one launch each
+bash tools/ncu_one.sh $TAG/fast fast_cells 3 > $OUT/ncu_one_fast.log 2>&1
+bash tools/ncu_one.sh $TAG/describe describe_kernel 3 > $OUT/ncu_one_describe.log 2>&1
 # matcher / stereo kernels: one small scripted pass (tools/match_probe.py), launch list + full capture
 MCMD="python tools/match_probe.py"
 timeout 300 $MCMD > $OUT/match_probe.log 2>&1
@@ -31,10 +35,12 @@ timeout 600 ncu --set full --clock-control none --import-source on \
   -o $OUT/match_full -f $MCMD > $OUT/ncu_match.log 2>&1
 echo "ncu match exit $?"
 ncu -i $OUT/match_full.ncu-rep --page raw --csv > $OUT/match_full_raw.csv 2>/dev/null
+rm -f $OUT/match_full.ncu-rep
 # the key-frame / frame-epilogue / vocabulary kernels come last in the probe: a capture of their own
 timeout 600 ncu --set full --clock-control none --import-source on \
   -k regex:'block_distance|distinctive_kernel|undistort_keys|voc_descend|stereo_' --launch-count 14 \
   -o $OUT/rows_full -f $MCMD > $OUT/ncu_rows.log 2>&1
 echo "ncu rows exit $?"
 ncu -i $OUT/rows_full.ncu-rep --page raw --csv > $OUT/rows_full_raw.csv 2>/dev/null
+rm -f $OUT/rows_full.ncu-rep
 ls -la $OUT

@@ -11,4 +11,7 @@ echo "ncu exit $?"
 ncu -i $OUT/one.ncu-rep --page raw --csv > $OUT/one_raw.csv 2>/dev/null
 ncu -i $OUT/one.ncu-rep --page details > $OUT/one_details.txt 2>/dev/null
 ncu -i $OUT/one.ncu-rep --page source --csv > $OUT/one_source.csv 2>/dev/null
+rm -f $OUT/one.ncu-rep   # gpurun only brings back 64 MiB
 python tools/ncu_summary.py $OUT/one_raw.csv
+python tools/sass_regions.py $OUT/one_source.csv 1.0 > $OUT/one_sass_regions.txt 2>&1
+gzip -f $OUT/one_source.csv
