@@ -16,8 +16,7 @@
 //    the FIRST max-response point of a node); it is a function of (cell row, cell col, y, x), which
 //    the octree kernel recomputes from the coordinates, so candidates are appended unordered.
 //
-// Kernel shape (v3): one WARP per cell, 8 cells per CTA, shared memory sized on the host for the
-// largest cell of the shape. The cell patch is staged word-aligned in shared memory; every lane scores
+// Kernel shape (v3): one WARP per cell, shared memory sized on the host for the largest cell of the shape. The cell patch is staged word-aligned in shared memory; every lane scores
 // 4 horizontally adjacent pixels per task with branch-free packed 16x2 min/max (VIMNMX3.U16x2):
 // the patch is staged as 16-bit lanes, so 6 of the 16 ring offsets are plain words and 10 cost one PRMT;
 // 72 packed min/max per PAIR of pixels, no divergence, no per-pixel early-outs -- the cost per pixel
@@ -30,11 +29,14 @@
 
 namespace orbx {
 
+// One warp per CTA: the warps of a CTA finish their cells at different times and a CTA's slot is only handed on when
+// its last warp is done; with single-warp CTAs (32 resident per SM at 64 registers) the SM stays full. Measured on
+// C1, 512 frames: 8 / 4 / 2 / 1 warps per CTA = 1.154 / 1.133 / 1.133 / 1.120 ms (register caps below 64 spill and lose).
 #ifndef ORBX_FAST_WARPS
-#define ORBX_FAST_WARPS 8
+#define ORBX_FAST_WARPS 1
 #endif
 #ifndef ORBX_FAST_MINB
-#define ORBX_FAST_MINB 4
+#define ORBX_FAST_MINB 32
 #endif
 constexpr int kFastWarps = ORBX_FAST_WARPS;   // cells per CTA
 constexpr int kFastThreads = kFastWarps * 32;
@@ -139,7 +141,8 @@ __device__ __forceinline__ uint32_t fast_compass_bound(uint32_t n, uint32_t s, u
 // stays 8-byte aligned
 __host__ __device__ inline int fast_cell_words(int wCell, int hCell) {
   const int nW = ((7 + wCell - 1) >> 2) + 2;  // worst alignment: a = 7
-  const int words = (hCell + 6) * 2 * nW + (hCell + 2) * nW + (hCell * (nW - 2) + 1) / 2 + 1;
+  const int rounds = (hCell * (nW - 2) + 31) / 32;  // one class-B ballot word per pass-1 round
+  const int words = (hCell + 6) * 2 * nW + (hCell + 2) * nW + (hCell * (nW - 2) + 1) / 2 + 1 + rounds;
   return (words + 1) & ~1;
 }
 
@@ -234,11 +237,13 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   //      (p0, p4, p8, p12), so  A >= Ac = min over adjacent compass pairs of their max  and
   //      B <= Bc = max over those pairs of their min, hence m <= max(v - Ac, Bc - v): a task whose four
   //      bounds are all <= minTh has an all-zero score word and is dropped after 12 instead of 92 packed
-  //      operations per pixel pair. The others are queued as y<<8 | q in two classes: list A (some bound
-  //      above iniTh) grows from the front of the queue, list B (bounds in (minTh, iniTh]) from its back.
-  //      B is only ever scored if the cell turns out empty at iniTh (phase 1 below). Rounds are warp-uniform
+  //      operations per pixel pair. The others fall in two classes: list A (some bound above iniTh) is queued as
+  //      y<<8 | q from the front of the queue; class B (bounds in (minTh, iniTh]) is only ever scored if the cell
+  //      turns out empty at iniTh (phase 1 below) and is kept as ballot words until then. Rounds are warp-uniform
   //      (lanes past the last task idle inside the round) so that the ballots are full-warp ones. ----
-  int nA = 0, backB = nTasks - 1;  // next free slot of list B
+  int nA = 0;
+  bool anyB = false;
+  uint32_t* bmask = reinterpret_cast<uint32_t*>(queue + ((nTasks + 1) & ~1));  // class-B ballots, one word per round
   {
     int y = y0, q = q0;
     for (int t0 = 0; t0 < nTasks; t0 += 32) {
@@ -253,22 +258,21 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
         any = b01 | b23;
         hi = __viaddmax_s16x2_relu(__vmaxu2(b01, b23), negIni, 0u);
       }
+      // Class A is compacted right away; class B is only remembered as the round's ballot word: its list is needed
+      // by a few per cent of the cells (those empty at iniTh) and is rebuilt from the ballots there.
       const uint32_t maskA = __ballot_sync(0xffffffffu, hi != 0u);
       const uint32_t maskB = __ballot_sync(0xffffffffu, any != 0u) & ~maskA;
-      if (any != 0u) {  // one store: front slot for class A, back slot for class B
-        const bool isA = hi != 0u;
-        const int rank = __popc((isA ? maskA : maskB) & below);
-        queue[isA ? nA + rank : backB - rank] = (uint16_t)((y << 8) | q);
-      }
+      if (hi != 0u) queue[nA + __popc(maskA & below)] = (uint16_t)((y << 8) | q);
+      if (lane == 0) bmask[t0 >> 5] = maskB;
       nA += __popc(maskA);
-      backB -= __popc(maskB);
+      anyB = anyB || maskB != 0u;
       y += dy; q += dq;
       if (q >= nG) { q -= nG; y++; }
     }
   }
   __syncwarp();
-  const int nB = nTasks - 1 - backB;
-  if (nA + nB == 0) return;
+  if (nA == 0 && !anyB) return;
+  int nB = 0;
 
   // Phase 0 scores list A and suppresses at iniTh. A pixel above iniTh can only lose to a neighbour whose margin
   // is also above iniTh, and such a neighbour's task is in A: the phase-0 result is exactly cv::FAST(cell, iniTh).
@@ -278,6 +282,20 @@ fast_cells_kernel(const __grid_constant__ PyramidPtrs pyr, const __grid_constant
   int nS = 0;             // tasks that keep a corner after suppression: queue[0 .. nS), kept[0 .. nS)
 #pragma unroll 1
   for (int phase = 0; phase < 2; phase++) {
+    if (phase == 1) {
+      // list B from the ballots, at the back of the queue (task t of round r is r*32 + lane = y*nG + q)
+      int back = nTasks - 1;
+      for (int t0 = 0; t0 < nTasks; t0 += 32) {
+        const uint32_t mb = bmask[t0 >> 5];
+        if ((mb >> lane) & 1u) {
+          const int t = t0 + lane, y = div_small(t, nG), q = t - y * nG;
+          queue[back - __popc(mb & below)] = (uint16_t)((y << 8) | q);
+        }
+        back -= __popc(mb);
+      }
+      nB = nTasks - 1 - back;
+      __syncwarp();
+    }
     const int srcBase = phase == 0 ? 0 : nTasks - nB;
     const int srcN = phase == 0 ? nA : nB;
     // ---- pass 2, listed tasks: score map max(m - minTh, 0) (0 = not a corner at minTh). Only a task whose
