@@ -29,6 +29,10 @@ constexpr unsigned kKeyNone = 0xFFFFFFFFu;
 #define ORBX_BF_GROUP 4
 #endif
 constexpr int kBfGroup = ORBX_BF_GROUP;         // rows per guarded group (even)
+#ifndef ORBX_BF_GUARD_MIN_ROWS
+#define ORBX_BF_GUARD_MIN_ROWS 8192
+#endif
+constexpr int kBfGuardMinRows = ORBX_BF_GUARD_MIN_ROWS;  // chunks shorter than this use the unguarded kernel
 
 __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
   return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
@@ -71,7 +75,9 @@ __device__ __forceinline__ unsigned hamming_key(const uint4& a0, const uint4& a1
   return imad(__popc(c4), km.m25, key);
 }
 
-// grid: (query groups, chunks). partial arrays are [chunk][nq].
+// grid: (query groups, chunks). partial arrays are [chunk][nq]. GUARD: the grouped fast path below; it pays once a
+// chunk's second-best keys have settled, i.e. for long chunks (launch_bf2 picks).
+template <bool GUARD>
 __global__ void __launch_bounds__(kBfThreads)
 bf2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, long long ndb, int rowsPerChunk,
            long long idxBase, int* __restrict__ pIdx, int* __restrict__ pD1, int* __restrict__ pD2, const KeyMul km) {
@@ -109,7 +115,7 @@ bf2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, lo
     // groups of 16 / 8 / 4 / 2: 863 / 874 / 868 / 798 Gpairs/s, and 726 / 784 / 807 / 808 on one 1.25M-row shard of the
     // 8-GPU split (shorter chunks spend more of their rows settling) -- with the ALU pipe relieved the 4 POPC per pair (a quarter-rate pipe: 32 issue cycles per pair against
     // 33 on the ALU pipe) co-limit the loop.
-    for (; r + kBfGroup <= rows; r += kBfGroup, rowKey += kBfGroup) {
+    for (; GUARD && r + kBfGroup <= rows; r += kBfGroup, rowKey += kBfGroup) {
       unsigned m[kBfQPT];
 #pragma unroll
       for (int k = 0; k < kBfQPT; k++) m[k] = kKeyNone;
@@ -225,8 +231,15 @@ void launch_bf2(const uint8_t* q, int nq, const uint8_t* db, long long ndb, int 
                 long long idxBase, int* pIdx, int* pD1, int* pD2, cudaStream_t s) {
   dim3 grid((nq + kBfQueriesPerCta - 1) / kBfQueriesPerCta, chunks);
   const KeyMul km = {1u << 23, 1u << 24, 1u << 25};
-  bf2_kernel<<<grid, kBfThreads, 0, s>>>(reinterpret_cast<const uint4*>(q), nq, reinterpret_cast<const uint4*>(db), ndb,
-                                         rowsPerChunk, idxBase, pIdx, pD1, pD2, km);
+  // A chunk runs the exact update until its second-best keys have settled (a thousand rows or so per warp): short
+  // chunks (small databases, or few query groups and hence many chunks) are faster without the guard -- 2048 x 1M
+  // rows in 592 chunks of 1.7 k rows: 2.64 ms unguarded, 3.13 ms guarded; 10 k x 10 M in 119 chunks of 84 k: 125 / 115 ms.
+  if (rowsPerChunk >= kBfGuardMinRows)
+    bf2_kernel<true><<<grid, kBfThreads, 0, s>>>(reinterpret_cast<const uint4*>(q), nq, reinterpret_cast<const uint4*>(db), ndb,
+                                                 rowsPerChunk, idxBase, pIdx, pD1, pD2, km);
+  else
+    bf2_kernel<false><<<grid, kBfThreads, 0, s>>>(reinterpret_cast<const uint4*>(q), nq, reinterpret_cast<const uint4*>(db), ndb,
+                                                  rowsPerChunk, idxBase, pIdx, pD1, pD2, km);
 }
 
 void launch_merge(const int* pIdx, const int* pD1, const int* pD2, int nshards, int nq, float ratio, int th,

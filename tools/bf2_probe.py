@@ -11,11 +11,10 @@ torch.cuda.set_device(0)
 st = torch.cuda.Stream()
 with torch.cuda.stream(st):
     g = torch.Generator(device="cuda"); g.manual_seed(1)
-    nq = 10_000
-    q = torch.randint(0, 256, (nq, 32), generator=g, device="cuda", dtype=torch.uint8)
     m = pkg.ORBmatcher(0.6)
-    out = torch.empty((3, nq), dtype=torch.int32, device="cuda")
-    for ndb in (10_000_000, 1_250_000):
+    for nq, ndb in ((10_000, 10_000_000), (10_000, 1_250_000), (2048, 1_000_000), (2000, 20_000), (10_000, 3_000_000)):
+        q = torch.randint(0, 256, (nq, 32), generator=g, device="cuda", dtype=torch.uint8)
+        out = torch.empty((3, nq), dtype=torch.int32, device="cuda")
         db = torch.randint(0, 256, (ndb, 32), generator=g, device="cuda", dtype=torch.uint8)
         s = st.cuda_stream
         for _ in range(2):
@@ -27,5 +26,5 @@ with torch.cuda.stream(st):
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 5
-        print(f"ndb {ndb}: {ms:.3f} ms  {nq * ndb / ms / 1e6:.1f} Gpairs/s  checksum {int(out.sum().item())}")
+        print(f"nq {nq} ndb {ndb}: {ms:.3f} ms  {nq * ndb / ms / 1e6:.1f} Gpairs/s  checksum {int(out.sum().item())}")
         del db

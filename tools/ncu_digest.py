@@ -14,9 +14,11 @@ ROOT = Path(__file__).resolve().parents[1]
 def csrc_hash():
     """the same hash bench.py computes over the kernel sources: the digest is only used for the build it describes"""
     h = hashlib.sha256()
-    for p in sorted((ROOT / "orb-slam2-_b200" / "csrc").glob("*.cu*")):
-        h.update(p.name.encode())
-        h.update(p.read_bytes())
+    # the sources of the extraction-pipeline kernels (the ones profiles/ncu_digest.json describes)
+    for name in ("orb_pattern.inc", "orbx_common.cuh", "orbx_describe.cu", "orbx_fast.cu", "orbx_math.cuh", "orbx_octree.cu",
+                 "orbx_pyramid.cu"):
+        h.update(name.encode())
+        h.update((ROOT / "orb-slam2-_b200" / "csrc" / name).read_bytes())
     return h.hexdigest()[:16]
 
 
@@ -35,7 +37,7 @@ def main(path, committed_as, frames):
     col = {h: i for i, h in enumerate(hdr)}
     acc = {}
     for r in rows[2:]:
-        name = r[col["Kernel Name"]].split("(")[0]
+        name = r[col["Kernel Name"]].split("(")[0].replace("void ", "").split("<")[0].strip()
         name = NAMES.get(name, name)
         f = lambda k: float(r[col[M[k]]].replace(",", ""))
         d = acc.setdefault(name, {"dram_bytes": 0.0, "launches": 0, "alu": [], "fma": [], "issue": [], "l1": []})
