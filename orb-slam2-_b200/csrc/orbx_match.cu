@@ -17,7 +17,10 @@
 
 namespace orbx {
 
-constexpr int kBfThreads = 256;
+#ifndef ORBX_BF_THREADS
+#define ORBX_BF_THREADS 256
+#endif
+constexpr int kBfThreads = ORBX_BF_THREADS;
 #ifndef ORBX_BF_QPT
 #define ORBX_BF_QPT 4
 #endif
