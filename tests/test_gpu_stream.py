@@ -205,3 +205,82 @@ def test_shard_group_sequence_in_order(pkg, ndev, stereo):
             assert np.array_equal(ur[f // 2, :len(k1)].view(np.uint32), u.view(np.uint32))
             assert np.array_equal(dp[f // 2, :len(k1)].view(np.uint32), z.view(np.uint32))
     g.close()
+
+
+def test_small_chunk_route_equals_batch_route(pkg):
+    """Up to 4 frames per call take the fork / join route (per-level streams, CUDA graph once the arguments repeat,
+    results written straight into page-locked memory); larger batches take the single-stream route with DMA copies.
+    Same frames through both, with the graph replayed several times, pinned and pageable destinations, a change of shape
+    in between and a capacity that is too small."""
+    w, h, nf = 640, 480, 1000
+    frames = np.stack([pkg.synth.frame(w, h, 900 + i) for i in range(8)])
+    cap = nf + 64
+    ex = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=800, max_height=600, max_batch=8)
+    bk, bd, bn = np.empty((8, cap), pkg.KP_DTYPE), np.empty((8, cap, 32), np.uint8), np.zeros(8, np.int32)
+    ex.extract_batch_into(frames, bk, bd, bn)                      # 8 frames: batch route
+    pk, pd = pkg.pinned_empty((1, cap), pkg.KP_DTYPE), pkg.pinned_empty((1, cap, 32), np.uint8)
+    pn = np.zeros(1, np.int32)
+    pimg = pkg.pinned_empty((1, h, w), np.uint8)
+    for rep in range(3):                                           # same arrays every call: capture, then replays
+        for f in range(8):
+            pimg[0] = frames[f]
+            pk[:] = 0
+            ex.extract_batch_into(pimg, pk, pd, pn)
+            assert pn[0] == bn[f] > 900
+            assert np.array_equal(pk[0, :pn[0]].view(np.uint8), bk[f, :bn[f]].view(np.uint8)), (rep, f)
+            assert np.array_equal(pd[0, :pn[0]], bd[f, :bn[f]]), (rep, f)
+    # pageable destinations (lane staging) and pairs of frames
+    for f in range(0, 8, 2):
+        k2, d2, n2 = np.empty((2, cap), pkg.KP_DTYPE), np.empty((2, cap, 32), np.uint8), np.zeros(2, np.int32)
+        ex.extract_batch_into(frames[f:f + 2], k2, d2, n2)
+        for j in range(2):
+            assert n2[j] == bn[f + j] and np.array_equal(k2[j, :n2[j]].view(np.uint8), bk[f + j, :n2[j]].view(np.uint8))
+            assert np.array_equal(d2[j, :n2[j]], bd[f + j, :n2[j]])
+    # another shape in between invalidates the captured set; coming back re-captures
+    other = pkg.synth.frame(800, 600, 5)
+    ko, do = ex(other)
+    one = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=800, max_height=600)
+    ko2, do2 = one(other)
+    assert np.array_equal(ko.view(np.uint8), ko2.view(np.uint8)) and np.array_equal(do, do2)
+    for _ in range(3):
+        pimg[0] = frames[3]
+        ex.extract_batch_into(pimg, pk, pd, pn)
+        assert pn[0] == bn[3] and np.array_equal(pd[0, :pn[0]], bd[3, :bn[3]])
+    # capacity too small: ORBX_ERR_CAPACITY with the needed count in n, nothing beyond the arrays written
+    sk, sd = pkg.pinned_empty((1, 100), pkg.KP_DTYPE), pkg.pinned_empty((1, 100, 32), np.uint8)
+    with pytest.raises(pkg.OrbxError) as e:
+        ex.extract_batch_into(pimg, sk, sd, pn)
+    assert e.value.code == -3 and pn[0] == bn[3]
+    assert np.array_equal(sk[0].view(np.uint8), bk[3, :100].view(np.uint8))
+
+
+def test_small_chunk_route_two_threads(pkg):
+    """Two extractor handles driven from two host threads at once (the stereo Frame constructor), both on the graph
+    route: results equal the batch route."""
+    import threading
+    w, h, nf = 752, 480, 1200
+    left, right = pkg.synth.stereo_pair(w, h, 77)
+    cap = nf + 64
+    ref = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=8)
+    both = np.stack([left, right] * 4)
+    bk, bd, bn = np.empty((8, cap), pkg.KP_DTYPE), np.empty((8, cap, 32), np.uint8), np.zeros(8, np.int32)
+    ref.extract_batch_into(both, bk, bd, bn)
+    out = {}
+
+    def work(name, img):
+        ex = pkg.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+        k, d, n = pkg.pinned_empty((1, cap), pkg.KP_DTYPE), pkg.pinned_empty((1, cap, 32), np.uint8), np.zeros(1, np.int32)
+        ok = True
+        for _ in range(20):
+            k[:] = 0
+            ex.extract_batch_into(img[None], k, d, n)
+            j = 0 if name == "L" else 1
+            ok = ok and n[0] == bn[j] and np.array_equal(k[0, :n[0]].view(np.uint8), bk[j, :bn[j]].view(np.uint8)) and \
+                np.array_equal(d[0, :n[0]], bd[j, :bn[j]])
+        out[name] = ok
+    ts = [threading.Thread(target=work, args=("L", left)), threading.Thread(target=work, args=("R", right))]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert out == {"L": True, "R": True}
